@@ -1,0 +1,104 @@
+// kernels.h — host-side launchers of the sm_100a kernels (internal header).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace rt {
+
+// One BVH2 node, 64 bytes: the boxes of both children plus their ids, so that
+// one node fetch (two 32-byte sectors) feeds two slab tests.
+//   lo0 = child0.min.xyz, child0 id bits     hi0 = child0.max.xyz, 0
+//   lo1 = child1.min.xyz, child1 id bits     hi1 = child1.max.xyz, 0
+// child id: >= 0 internal node index, < 0 leaf (~sorted position).
+struct __align__(64) Node {
+  float4 lo0, hi0, lo1, hi1;
+};
+
+// Reordered triangle, 48 bytes: v0.xyz + original primitive index, e1, e2.
+struct __align__(16) SortedTri {
+  float4 v0p, e1, e2;
+};
+
+// 16-float header living next to the node array (broadcast with it).
+struct BvhHeader {
+  float root_min[3];
+  uint32_t n_tris_lo;
+  float root_max[3];
+  uint32_t n_tris_hi;
+  uint32_t key_bits;
+  uint32_t pad[7];
+};
+
+// parent word: (parent internal index << 1) | slot; kNoParent for the root
+constexpr uint32_t kNoParent = 0xFFFFFFFFu;
+
+// ---- generators (scene_gen.cu, ray_gen.cu) ---------------------------------
+int launch_gen_scene(int kind, uint64_t p0, uint64_t p1, uint64_t seed, uint64_t first,
+                     uint64_t count, float4* out, cudaStream_t s);
+int launch_gen_primary(const float* cam12, uint32_t width, uint32_t height, uint64_t first,
+                       uint64_t count, float4* out, cudaStream_t s);
+int launch_gen_random(const float* box6, uint64_t seed, uint64_t first, uint64_t count,
+                      float4* out, cudaStream_t s);
+int launch_gen_ao(const float4* tris, const float4* rays, const float4* hits, uint64_t n,
+                  uint32_t spp, uint64_t seed, float radius, float4* out, cudaStream_t s);
+int launch_shade(const float4* tris, const float4* rays, const float4* hits,
+                 const float4* ao_hits, uint64_t n, uint32_t spp, float* rgb, cudaStream_t s);
+
+// ---- build (morton.cu, radix_sort.cu, karras.cu, refit.cu) -----------------
+// bounds_keys: 6 ordered-int keys, min.xyz then max.xyz; must be pre-set to
+// 0xFFFFFFFF x3, 0 x3 (launch_bounds does that itself).
+int launch_bounds(const float4* tris, uint64_t n, uint32_t* bounds_keys, cudaStream_t s);
+// keys: n u32 (30-bit) or n u64 (63-bit).  hist: [passes][256] u32, zeroed by
+// the launcher, receives the per-digit histograms of all keys.
+int launch_morton(const float4* tris, uint64_t n, const uint32_t* bounds_keys, uint32_t key_bits,
+                  void* keys, uint32_t* hist, cudaStream_t s);
+
+struct SortWorkspace {
+  void* keys_alt = nullptr;     // n keys, ping-pong partner of the input
+  uint32_t* vals_alt = nullptr; // n u32
+  uint32_t* vals = nullptr;     // n u32 (first pass writes it: payload starts as iota)
+  uint32_t* hist = nullptr;     // [passes][256]
+  uint32_t* lookback = nullptr; // [passes][tiles][256] + [passes] tile counters
+  uint64_t lookback_words = 0;
+};
+int sort_num_passes(uint32_t key_bits);
+uint64_t sort_lookback_words(uint64_t n, uint32_t key_bits);
+// Sorts (keys, iota) by key.  Result: *keys_out / *vals_out point at whichever
+// ping-pong buffer holds the sorted data.  hist must already hold the digit
+// histograms (launch_morton or launch_histogram).
+int launch_sort(void* keys, uint64_t n, uint32_t key_bits, const SortWorkspace& ws,
+                bool iota_payload, void** keys_out, uint32_t** vals_out, cudaStream_t s);
+int launch_histogram(const void* keys, uint64_t n, uint32_t key_bits, uint32_t* hist,
+                     cudaStream_t s);
+
+int launch_karras(const void* keys, uint64_t n, uint32_t key_bits, uint32_t* parent,
+                  cudaStream_t s);
+// flags: n-1 u32, zeroed by the launcher.  Writes nodes, sorted tris, header box.
+int launch_refit(const float4* tris, const uint32_t* sorted_idx, uint64_t n,
+                 const uint32_t* parent, uint32_t* flags, Node* nodes, SortedTri* stris,
+                 BvhHeader* header, cudaStream_t s);
+// refit with moved vertices: the primitive index comes from stris[j].v0p.w
+int launch_refit_update(const float4* tris, uint64_t n, const uint32_t* parent, uint32_t* flags,
+                        Node* nodes, SortedTri* stris, BvhHeader* header, cudaStream_t s);
+// canonical arrays for the parity accessors (device outputs, may be null)
+int launch_export_topology(const Node* nodes, const uint32_t* parent, uint64_t n, uint32_t* left,
+                           uint32_t* right, uint32_t* parent_out, float* boxes,
+                           const BvhHeader* header, cudaStream_t s);
+
+// ---- traversal (traverse.cu) -------------------------------------------------
+int launch_trace(const Node* nodes, const SortedTri* stris, uint64_t n_tris, const float4* rays,
+                 uint64_t n_rays, uint32_t flags, float4* hits, unsigned long long* ray_counter,
+                 cudaStream_t s);
+
+// tuning knobs (rt_set_param)
+struct Params {
+  int sort_variant = 0;
+  int trace_blocks_per_sm = 0;  // 0 = kernel default
+  int trace_variant = 0;
+  int num_sms = 0;              // filled at first use
+};
+Params& params();
+int num_sms();
+
+}  // namespace rt

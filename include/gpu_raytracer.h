@@ -1,0 +1,189 @@
+/* gpu_raytracer.h — C ABI of libgpu_raytracer_b200.so
+ *
+ * The drop-in boundary of the B200 ray-tracing core: scene in, hits out.
+ *
+ * What this replaces in the reference: nothing that exists.  The mounted
+ * reference (/root/reference) holds README.md:1-2 ("A learning project about
+ * GPU-accelerated raytracing") and test.txt:1 and no interface of any kind
+ * (SURVEY.md §8b).  The three entry points build_bvh / trace_rays / free_bvh are
+ * the ones BASELINE.json:5 names for the path ("a thin C-ABI (build_bvh /
+ * trace_rays / free_bvh) that mirrors the reference's scene-in, hits-out
+ * interface"); every other symbol here is an accessor, generator or multi-GPU
+ * helper around them.  Each declaration cites the SURVEY.md §8 row it serves.
+ *
+ * Conventions
+ *   - plain C types only; no exceptions cross the boundary; no exit().
+ *   - every int-returning call returns RT_OK (0) or a negative RT_ERR_* code;
+ *     bvh_last_error() gives the thread-local message of the last failure.
+ *   - pointer arguments marked [host|device] are classified with
+ *     cudaPointerGetAttributes; host data is staged through device memory by the
+ *     library, device data (on the handle's device) is used in place.
+ *   - all work runs on the CUDA device that is current when build_bvh is called
+ *     (or opts->device) and on the legacy default stream unless a stream is
+ *     given; calls are synchronous on return unless named *_async.
+ *   - there is no CPU fallback: without a CUDA device every compute call fails
+ *     with RT_ERR_NO_DEVICE.
+ *
+ * Data layouts
+ *   triangle  12 floats  v0.xyz,_, v1.xyz,_, v2.xyz,_      (3 x float4, w ignored)
+ *   ray        8 floats  o.xyz, tmin, d.xyz, tmax          (2 x float4)
+ *   hit        4 floats  t, u, v, prim                     (prim = int32 bits;
+ *                        -1 on miss with t = +inf; any-hit mode: prim =
+ *                        RT_ANY_HIT_PRIM, t = u = v = 0 when occluded)
+ */
+#ifndef GPU_RAYTRACER_H_
+#define GPU_RAYTRACER_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RT_OK 0
+#define RT_ERR_INVALID (-1)   /* bad argument */
+#define RT_ERR_CUDA (-2)      /* CUDA runtime error, see bvh_last_error() */
+#define RT_ERR_OOM (-3)       /* device or host allocation failed */
+#define RT_ERR_NO_DEVICE (-4) /* no usable CUDA device */
+#define RT_ERR_LIMIT (-5)     /* size beyond a documented limit */
+
+/* trace_rays flags (A6) */
+#define RT_TRACE_CLOSEST 0u
+#define RT_TRACE_ANY 1u
+#define RT_ANY_HIT_PRIM 0x7FFFFFFF
+
+/* build flags */
+#define RT_BUILD_KEEP_KEYS 1u /* keep the sorted Morton codes for bvh_read_sorted */
+#define RT_BUILD_TIMINGS 2u   /* record per-stage CUDA events (bvh_build_times) */
+
+/* scene kinds for rt_gen_scene */
+#define RT_SCENE_CORNELL 0     /* config 1: 1,024 triangles, no parameters       */
+#define RT_SCENE_SOUP 1        /* config 2: p0 = triangle count                  */
+#define RT_SCENE_SPHEREFLAKE 2 /* config 3/5: p0 = depth, p1 = segments per edge */
+#define RT_SCENE_TERRAIN 3     /* config 4: p0 = cells per side, p1 = base noise spacing (0 = 1024) */
+
+/* maximum triangle count of one BVH: node ids and look-back words are 30-bit */
+#define RT_MAX_TRIS ((1ull << 30) - 1)
+
+typedef struct rt_bvh rt_bvh; /* opaque; immutable after build_bvh returns */
+
+typedef struct rt_build_opts {
+  uint32_t key_bits; /* 30 (default when 0) or 63: Morton code width (A2) */
+  uint32_t flags;    /* RT_BUILD_* */
+  int32_t device;    /* CUDA device ordinal, -1 = current device */
+  int32_t reserved;
+  void* stream;      /* cudaStream_t, NULL = legacy default stream */
+} rt_build_opts;
+
+typedef struct rt_bvh_info {
+  uint64_t n_tris;
+  uint64_t n_nodes;      /* 2 n - 1 (0 when empty) */
+  uint32_t key_bits;
+  int32_t device;
+  float bounds[6];       /* scene AABB min.xyz max.xyz (A1) */
+  uint64_t device_bytes; /* memory held by the handle */
+} rt_bvh_info;
+
+/* build stages reported by bvh_build_times, in milliseconds */
+enum {
+  RT_STAGE_BOUNDS = 0, /* A1 */
+  RT_STAGE_MORTON = 1, /* A2 + digit histograms */
+  RT_STAGE_SORT = 2,   /* A3 */
+  RT_STAGE_TOPOLOGY = 3, /* A4 */
+  RT_STAGE_REFIT = 4,  /* A5 (leaf boxes, triangle reorder, bottom-up unions) */
+  RT_STAGE_TOTAL = 5,
+  RT_STAGE_COUNT = 6
+};
+
+/* ---- the three entry points (BASELINE.json:5) ------------- */
+
+/* Builds an LBVH over n_tris triangles.  tris: [host|device] n_tris x 12
+ * floats; the caller keeps ownership, the handle holds its own reordered copy.
+ * opts may be NULL.  n_tris == 0 gives a valid empty handle (every ray misses). */
+int build_bvh(const float* tris, uint64_t n_tris, const rt_build_opts* opts, rt_bvh** out);
+
+/* Traces n_rays rays.  rays: [host|device] n_rays x 8 floats; hits:
+ * [host|device] n_rays x 4 floats.  Safe to call concurrently on one handle. */
+int trace_rays(const rt_bvh* h, const float* rays, uint64_t n_rays, uint32_t flags, float* hits);
+
+/* Frees every device allocation of the handle.  NULL is a no-op. */
+void free_bvh(rt_bvh* h);
+
+/* Thread-local message of the last failing call ("" if none). */
+const char* bvh_last_error(void);
+
+/* ---- stream variant ------------------------------------------------------ */
+
+/* Device pointers only; enqueues on stream (cudaStream_t) and returns. */
+int trace_rays_async(const rt_bvh* h, const float* rays, uint64_t n_rays, uint32_t flags,
+                     float* hits, void* stream);
+
+/* ---- accessors used by the parity tests (T2-T4) -------------------------- */
+
+int bvh_info(const rt_bvh* h, rt_bvh_info* out);
+/* keys: n u64 (needs RT_BUILD_KEEP_KEYS), prim_idx: n u32; host, may be NULL */
+int bvh_read_sorted(const rt_bvh* h, uint64_t* keys, uint32_t* prim_idx);
+/* canonical node ids: internal i in [0,n-1), leaf j at n-1+j; left/right: n-1
+ * u32 each, parent: 2n-1 u32 (0xFFFFFFFF for the root); host, may be NULL */
+int bvh_read_topology(const rt_bvh* h, uint32_t* left, uint32_t* right, uint32_t* parent);
+/* boxes: (2n-1) x 6 floats min.xyz max.xyz in canonical node order; host */
+int bvh_read_boxes(const rt_bvh* h, float* boxes);
+/* ms: RT_STAGE_COUNT floats (needs RT_BUILD_TIMINGS) */
+int bvh_build_times(const rt_bvh* h, float* ms);
+
+/* ---- refit: same topology, moved vertices -------------- */
+int refit_bvh(rt_bvh* h, const float* tris);
+
+/* ---- multi-GPU helpers ----------------------------------- */
+
+/* Device buffers that make up a built BVH, for a broadcast between ranks:
+ * ptrs[0]/bytes[0] = node array, ptrs[1]/bytes[1] = reordered triangles,
+ * ptrs[2]/bytes[2] = 16-float header (root box, counts). */
+int bvh_device_buffers(const rt_bvh* h, void** ptrs, uint64_t* bytes);
+/* Allocates a handle with uninitialised buffers of the right size for n_tris,
+ * to be filled through bvh_device_buffers (receiver side of the broadcast). */
+int bvh_alloc_empty(uint64_t n_tris, uint32_t key_bits, rt_bvh** out);
+/* Re-reads the header buffer after it was filled by a broadcast. */
+int bvh_commit(rt_bvh* h);
+
+/* ---- on-device generators (A8 and the §8d synthetic scenes) -------------- */
+
+uint64_t rt_scene_size(int kind, uint64_t p0, uint64_t p1);
+/* triangles [first, first+count) of the scene; out: [host|device] count x 12 */
+int rt_gen_scene(int kind, uint64_t p0, uint64_t p1, uint64_t seed, uint64_t first,
+                 uint64_t count, float* out);
+/* cam: host, 12 floats eye.xyz corner.xyz du.xyz dv.xyz; row-major pixel order */
+int rt_gen_primary_rays(const float* cam, uint32_t width, uint32_t height, uint64_t first,
+                        uint64_t count, float* out);
+/* box: host, 6 floats; ray i depends on (seed, first + i) only */
+int rt_gen_random_rays(const float* box, uint64_t seed, uint64_t first, uint64_t count, float* out);
+/* spp rays per primary ray from its hit point; tris in ORIGINAL order; all
+ * pointers [host|device] but of one kind; out: n x spp x 8 floats */
+int rt_gen_ao_rays(const float* tris, const float* rays, const float* hits, uint64_t n,
+                   uint32_t spp, uint64_t seed, float radius, float* out);
+
+/* ---- shading and image output --------------------------- */
+
+/* rgb: [host|device] n x 3 floats.  Lambert-ish: |n.d| * (1 - occluded/spp);
+ * ao_hits may be NULL (spp = 0).  Misses are black. */
+int rt_shade(const float* tris, const float* rays, const float* hits, const float* ao_hits,
+             uint64_t n, uint32_t spp, float* rgb);
+
+/* ---- runtime --------------------------------------------------------------*/
+
+int rt_device_count(void);
+/* number of CUDA kernels this library has launched in this process */
+uint64_t rt_kernel_launches(void);
+/* tuning knobs for experiments: name = "sort.variant", "trace.blocks_per_sm" … */
+int rt_set_param(const char* name, int64_t value);
+/* sorts n (key,value) pairs already on the device with the build's radix sort;
+ * used by tests and the sort micro-benchmark.  key_bits 30 -> u32 keys, 63 ->
+ * u64 keys.  keys/vals are overwritten with the sorted result. ms (may be
+ * NULL) receives the device time of the sort alone. */
+int rt_sort_pairs(void* keys, uint32_t* vals, uint64_t n, uint32_t key_bits, float* ms);
+const char* rt_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GPU_RAYTRACER_H_ */

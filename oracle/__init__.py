@@ -1,0 +1,195 @@
+"""ctypes binding of the spec-derived CPU oracle (oracle/oracle.cpp).
+
+TEST INFRASTRUCTURE ONLY.  Import this from ``tests/``, from
+``__graft_entry__.smoke()`` and from the ``cpu_baseline`` / ``--impl reference``
+legs of ``bench.py`` — never from ``gpu_raytracer_b200``.
+
+PARITY UNPINNED: /root/reference holds no code and no golden vectors
+(README.md:1-2, test.txt:1), so this oracle is a scalar C++ statement of the
+algorithm in BASELINE.json:5 / SURVEY.md §8(a), pinned by a brute-force
+intersector, Morton known-answer vectors and std::stable_sort (see oracle.cpp).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_HERE, "liblbvh_oracle.so")
+
+SCENE_CORNELL, SCENE_SOUP, SCENE_SPHEREFLAKE, SCENE_TERRAIN = 0, 1, 2, 3
+TRACE_CLOSEST, TRACE_ANY = 0, 1
+ANY_HIT_PRIM = 0x7FFFFFFF
+
+
+def build(force: bool = False) -> str:
+    """Compile oracle.cpp with the committed Makefile; returns the .so path."""
+    src = os.path.join(_HERE, "oracle.cpp")
+    stale = (not os.path.exists(_SO)) or os.path.getmtime(_SO) < os.path.getmtime(src)
+    if force or stale:
+        env = dict(os.environ)
+        try:
+            with open("/proc/cpuinfo") as f:
+                if " fma" not in f.read():
+                    env["NOFMA"] = "1"
+        except OSError:
+            pass
+        subprocess.run(["make", "-C", _HERE, "-B", "liblbvh_oracle.so"], check=True, env=env,
+                       stdout=subprocess.DEVNULL)
+    return _SO
+
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    global _lib
+    if _lib is None:
+        build()
+        L = C.CDLL(_SO)
+        u64, u32, i32, f32p, vp = C.c_uint64, C.c_uint32, C.c_int, C.POINTER(C.c_float), C.c_void_p
+        L.orc_set_threads.argtypes = [i32]
+        L.orc_max_threads.restype = i32
+        L.orc_morton30.argtypes = [u32, u32, u32]
+        L.orc_morton30.restype = u32
+        L.orc_morton63.argtypes = [u32, u32, u32]
+        L.orc_morton63.restype = u64
+        L.orc_scene_size.argtypes = [i32, u64, u64]
+        L.orc_scene_size.restype = u64
+        L.orc_gen_scene.argtypes = [i32, u64, u64, u64, u64, u64, vp]
+        L.orc_gen_scene.restype = i32
+        L.orc_gen_primary_rays.argtypes = [vp, u32, u32, u64, u64, vp]
+        L.orc_gen_random_rays.argtypes = [vp, u64, u64, u64, vp]
+        L.orc_gen_ao_rays.argtypes = [vp, vp, vp, u64, u32, u64, C.c_float, vp]
+        L.orc_build.argtypes = [vp, u64, u32]
+        L.orc_build.restype = vp
+        L.orc_free.argtypes = [vp]
+        L.orc_read.argtypes = [vp] * 8
+        L.orc_build_times.argtypes = [vp, vp]
+        L.orc_trace.argtypes = [vp, vp, u64, u32, vp, vp]
+        L.orc_brute.argtypes = [vp, u64, vp, u64, u32, vp]
+        _lib = L
+    return _lib
+
+
+def _p(a: np.ndarray):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def set_threads(n: int) -> None:
+    lib().orc_set_threads(int(n))
+
+
+def max_threads() -> int:
+    return int(lib().orc_max_threads())
+
+
+def morton30(x, y, z) -> int:
+    return int(lib().orc_morton30(x, y, z))
+
+
+def morton63(x, y, z) -> int:
+    return int(lib().orc_morton63(x, y, z))
+
+
+def scene_size(kind: int, p0: int = 0, p1: int = 0) -> int:
+    return int(lib().orc_scene_size(kind, p0, p1))
+
+
+def gen_scene(kind: int, p0: int = 0, p1: int = 0, seed: int = 0, first: int = 0,
+              count: int | None = None) -> np.ndarray:
+    """Triangles [first, first+count) as float32 [count, 12]."""
+    if count is None:
+        count = scene_size(kind, p0, p1) - first
+    out = np.empty((count, 12), dtype=np.float32)
+    rc = lib().orc_gen_scene(kind, p0, p1, seed, first, count, _p(out))
+    if rc != 0:
+        raise ValueError(f"orc_gen_scene failed ({rc})")
+    return out
+
+
+def gen_primary_rays(cam: np.ndarray, width: int, height: int, first: int = 0,
+                     count: int | None = None) -> np.ndarray:
+    cam = np.ascontiguousarray(cam, dtype=np.float32).reshape(12)
+    if count is None:
+        count = width * height - first
+    out = np.empty((count, 8), dtype=np.float32)
+    lib().orc_gen_primary_rays(_p(cam), width, height, first, count, _p(out))
+    return out
+
+
+def gen_random_rays(box: np.ndarray, seed: int, first: int, count: int) -> np.ndarray:
+    box = np.ascontiguousarray(box, dtype=np.float32).reshape(6)
+    out = np.empty((count, 8), dtype=np.float32)
+    lib().orc_gen_random_rays(_p(box), seed, first, count, _p(out))
+    return out
+
+
+def gen_ao_rays(tris: np.ndarray, rays: np.ndarray, hits: np.ndarray, spp: int, seed: int,
+                radius: float) -> np.ndarray:
+    n = rays.shape[0]
+    out = np.empty((n * spp, 8), dtype=np.float32)
+    lib().orc_gen_ao_rays(_p(tris), _p(rays), _p(hits), n, spp, seed, C.c_float(radius), _p(out))
+    return out
+
+
+class OracleBvh:
+    """Result of the oracle's build: canonical arrays."""
+
+    def __init__(self, tris: np.ndarray, key_bits: int = 30):
+        tris = np.ascontiguousarray(tris, dtype=np.float32).reshape(-1, 12)
+        self.n = int(tris.shape[0])
+        self.key_bits = key_bits
+        self._tris = tris
+        self._h = lib().orc_build(_p(tris), self.n, key_bits)
+        if not self._h:
+            raise ValueError("orc_build failed")
+        n = self.n
+        nodes = max(2 * n - 1, 0)
+        self.keys = np.empty(n, dtype=np.uint64)
+        self.idx = np.empty(n, dtype=np.uint32)
+        self.left = np.empty(max(n - 1, 0), dtype=np.uint32)
+        self.right = np.empty(max(n - 1, 0), dtype=np.uint32)
+        self.parent = np.empty(nodes, dtype=np.uint32)
+        self.boxes = np.empty((nodes, 6), dtype=np.float32)
+        self.bounds = np.zeros(6, dtype=np.float32)
+        lib().orc_read(self._h, _p(self.keys), _p(self.idx), _p(self.left), _p(self.right),
+                       _p(self.parent), _p(self.boxes), _p(self.bounds))
+        t = np.zeros(4, dtype=np.float64)
+        lib().orc_build_times(self._h, _p(t))
+        self.times = dict(morton=t[0], sort=t[1], topology=t[2], refit=t[3], total=float(t.sum()))
+
+    def trace(self, rays: np.ndarray, flags: int = TRACE_CLOSEST, counters: bool = False):
+        rays = np.ascontiguousarray(rays, dtype=np.float32).reshape(-1, 8)
+        hits = np.empty((rays.shape[0], 4), dtype=np.float32)
+        cnt = np.zeros(2, dtype=np.uint64)
+        lib().orc_trace(self._h, _p(rays), rays.shape[0], flags, _p(hits), _p(cnt))
+        if counters:
+            return hits, (int(cnt[0]), int(cnt[1]))
+        return hits
+
+    def close(self):
+        if self._h:
+            lib().orc_free(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def brute(tris: np.ndarray, rays: np.ndarray, flags: int = TRACE_CLOSEST) -> np.ndarray:
+    tris = np.ascontiguousarray(tris, dtype=np.float32).reshape(-1, 12)
+    rays = np.ascontiguousarray(rays, dtype=np.float32).reshape(-1, 8)
+    hits = np.empty((rays.shape[0], 4), dtype=np.float32)
+    lib().orc_brute(_p(tris), tris.shape[0], _p(rays), rays.shape[0], flags, _p(hits))
+    return hits
+
+
+def hit_prims(hits: np.ndarray) -> np.ndarray:
+    return np.ascontiguousarray(hits[:, 3]).view(np.int32)
