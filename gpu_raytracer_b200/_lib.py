@@ -1,0 +1,91 @@
+"""ctypes loader for libgpu_raytracer_b200.so (include/gpu_raytracer.h).
+
+The library is the product; this module only declares its C ABI.  If the shared
+object is missing it raises — there is no Python or CPU fallback.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+SO_PATH = os.path.join(_HERE, "libgpu_raytracer_b200.so")
+
+RT_OK, RT_ERR_INVALID, RT_ERR_CUDA, RT_ERR_OOM, RT_ERR_NO_DEVICE, RT_ERR_LIMIT = 0, -1, -2, -3, -4, -5
+RT_TRACE_CLOSEST, RT_TRACE_ANY = 0, 1
+RT_ANY_HIT_PRIM = 0x7FFFFFFF
+RT_BUILD_KEEP_KEYS, RT_BUILD_TIMINGS = 1, 2
+RT_SCENE_CORNELL, RT_SCENE_SOUP, RT_SCENE_SPHEREFLAKE, RT_SCENE_TERRAIN = 0, 1, 2, 3
+RT_STAGE_NAMES = ("bounds", "morton", "sort", "topology", "refit", "total")
+RT_MAX_TRIS = (1 << 30) - 1
+
+
+class BuildOpts(C.Structure):
+    _fields_ = [("key_bits", C.c_uint32), ("flags", C.c_uint32), ("device", C.c_int32),
+                ("reserved", C.c_int32), ("stream", C.c_void_p)]
+
+
+class BvhInfo(C.Structure):
+    _fields_ = [("n_tris", C.c_uint64), ("n_nodes", C.c_uint64), ("key_bits", C.c_uint32),
+                ("device", C.c_int32), ("bounds", C.c_float * 6), ("device_bytes", C.c_uint64)]
+
+
+# name -> (restype, argtypes); every symbol include/gpu_raytracer.h declares
+_u64, _u32, _i32, _vp, _f = C.c_uint64, C.c_uint32, C.c_int, C.c_void_p, C.c_float
+SIGNATURES = {
+    "build_bvh": (_i32, [_vp, _u64, C.POINTER(BuildOpts), C.POINTER(_vp)]),
+    "trace_rays": (_i32, [_vp, _vp, _u64, _u32, _vp]),
+    "free_bvh": (None, [_vp]),
+    "bvh_last_error": (C.c_char_p, []),
+    "trace_rays_async": (_i32, [_vp, _vp, _u64, _u32, _vp, _vp]),
+    "bvh_info": (_i32, [_vp, C.POINTER(BvhInfo)]),
+    "bvh_read_sorted": (_i32, [_vp, _vp, _vp]),
+    "bvh_read_topology": (_i32, [_vp, _vp, _vp, _vp]),
+    "bvh_read_boxes": (_i32, [_vp, _vp]),
+    "bvh_build_times": (_i32, [_vp, _vp]),
+    "refit_bvh": (_i32, [_vp, _vp]),
+    "bvh_device_buffers": (_i32, [_vp, C.POINTER(_vp), C.POINTER(_u64)]),
+    "bvh_alloc_empty": (_i32, [_u64, _u32, C.POINTER(_vp)]),
+    "bvh_commit": (_i32, [_vp]),
+    "rt_scene_size": (_u64, [_i32, _u64, _u64]),
+    "rt_gen_scene": (_i32, [_i32, _u64, _u64, _u64, _u64, _u64, _vp]),
+    "rt_gen_primary_rays": (_i32, [_vp, _u32, _u32, _u64, _u64, _vp]),
+    "rt_gen_random_rays": (_i32, [_vp, _u64, _u64, _u64, _vp]),
+    "rt_gen_ao_rays": (_i32, [_vp, _vp, _vp, _u64, _u32, _u64, _f, _vp]),
+    "rt_shade": (_i32, [_vp, _vp, _vp, _vp, _u64, _u32, _vp]),
+    "rt_device_count": (_i32, []),
+    "rt_kernel_launches": (_u64, []),
+    "rt_set_param": (_i32, [C.c_char_p, C.c_int64]),
+    "rt_sort_pairs": (_i32, [_vp, _vp, _u64, _u32, _vp]),
+    "rt_version": (C.c_char_p, []),
+}
+
+_lib = None
+
+
+class RtError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"gpu_raytracer_b200 error {code}: {msg}")
+        self.code = code
+
+
+def lib() -> C.CDLL:
+    """Loads the CUDA library; raises if it has not been built (no fallback)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(SO_PATH):
+            raise ImportError(
+                f"{SO_PATH} is missing: build it with `python -m gpu_raytracer_b200.build` "
+                "(or __graft_entry__.build()); gpu_raytracer_b200 has no CPU/PyTorch fallback")
+        L = C.CDLL(SO_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(L, name)  # AttributeError if the ABI is incomplete
+            fn.restype = res
+            fn.argtypes = args
+        _lib = L
+    return _lib
+
+
+def check(rc: int) -> None:
+    if rc != RT_OK:
+        raise RtError(rc, lib().bvh_last_error().decode("utf-8", "replace"))

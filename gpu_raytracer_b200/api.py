@@ -1,0 +1,253 @@
+"""Host-side mirror of the scene-in / hits-out interface (BASELINE.json:5).
+
+Thin Python over the C ABI in include/gpu_raytracer.h: ``Bvh.build`` →
+``build_bvh``, ``Bvh.trace`` → ``trace_rays``, ``Bvh.close`` → ``free_bvh``.
+Buffers may be numpy arrays (host) or torch tensors (host, pinned or CUDA); the
+library decides per pointer whether to stage or to use memory in place.  torch
+is only a device-memory allocator here.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import numpy as np
+
+from . import _lib as L
+
+try:  # torch is plumbing (device memory, streams), not a dependency of the ABI
+    import torch
+except Exception:  # pragma: no cover
+    torch = None
+
+
+def _is_tensor(x) -> bool:
+    return torch is not None and isinstance(x, torch.Tensor)
+
+
+def _ptr(x, dtype=np.float32) -> int:
+    """Raw address of a contiguous numpy array or torch tensor."""
+    if _is_tensor(x):
+        if not x.is_contiguous():
+            raise ValueError("tensor must be contiguous")
+        return x.data_ptr()
+    if isinstance(x, np.ndarray):
+        if not x.flags["C_CONTIGUOUS"]:
+            raise ValueError("array must be C-contiguous")
+        if dtype is not None and x.dtype != dtype:
+            raise ValueError(f"array must be {dtype}, got {x.dtype}")
+        return x.ctypes.data
+    raise TypeError(f"expected numpy array or torch tensor, got {type(x)}")
+
+
+def _rows(x, width: int) -> int:
+    n = int(np.prod(x.shape))
+    if n % width:
+        raise ValueError(f"buffer size {n} is not a multiple of {width}")
+    return n // width
+
+
+def _empty_like_kind(ref, shape, device: Optional[str]):
+    """Output buffer of the same kind as ``ref`` (or on ``device`` when given)."""
+    if device is not None or _is_tensor(ref):
+        dev = device if device is not None else ref.device
+        return torch.empty(shape, dtype=torch.float32, device=dev)
+    return np.empty(shape, dtype=np.float32)
+
+
+# ---------------------------------------------------------------------------
+# generators
+# ---------------------------------------------------------------------------
+def scene_size(kind: int, p0: int = 0, p1: int = 0) -> int:
+    return int(L.lib().rt_scene_size(kind, p0, p1))
+
+
+def gen_scene(kind: int, p0: int = 0, p1: int = 0, seed: int = 0, first: int = 0,
+              count: Optional[int] = None, device: Optional[str] = "cuda"):
+    """Triangles [first, first+count) of a synthetic scene as float32 [count, 12].
+
+    device="cuda" returns a CUDA tensor (generated in place, never on the host);
+    device=None returns a numpy array (generated on the GPU, copied back)."""
+    if count is None:
+        count = scene_size(kind, p0, p1) - first
+    out = (torch.empty((count, 12), dtype=torch.float32, device=device) if device is not None
+           else np.empty((count, 12), dtype=np.float32))
+    L.check(L.lib().rt_gen_scene(kind, p0, p1, seed, first, count, _ptr(out)))
+    return out
+
+
+def gen_primary_rays(cam, width: int, height: int, first: int = 0, count: Optional[int] = None,
+                     device: Optional[str] = "cuda"):
+    cam = np.ascontiguousarray(cam, dtype=np.float32).reshape(12)
+    if count is None:
+        count = width * height - first
+    out = (torch.empty((count, 8), dtype=torch.float32, device=device) if device is not None
+           else np.empty((count, 8), dtype=np.float32))
+    L.check(L.lib().rt_gen_primary_rays(cam.ctypes.data, width, height, first, count, _ptr(out)))
+    return out
+
+
+def gen_random_rays(box, seed: int, first: int, count: int, device: Optional[str] = "cuda",
+                    out=None):
+    box = np.ascontiguousarray(box, dtype=np.float32).reshape(6)
+    if out is None:
+        out = (torch.empty((count, 8), dtype=torch.float32, device=device) if device is not None
+               else np.empty((count, 8), dtype=np.float32))
+    L.check(L.lib().rt_gen_random_rays(box.ctypes.data, seed, first, count, _ptr(out)))
+    return out
+
+
+def gen_ao_rays(tris, rays, hits, spp: int, seed: int, radius: float, out=None):
+    """spp occlusion rays per primary ray; tris (original order) must be on the device."""
+    n = _rows(rays, 8)
+    if out is None:
+        out = _empty_like_kind(rays, (n * spp, 8), None)
+    L.check(L.lib().rt_gen_ao_rays(_ptr(tris), _ptr(rays), _ptr(hits), n, spp, seed,
+                                   C.c_float(radius), _ptr(out)))
+    return out
+
+
+def shade(tris, rays, hits, ao_hits=None, spp: int = 0):
+    n = _rows(rays, 8)
+    out = _empty_like_kind(rays, (n, 3), None)
+    L.check(L.lib().rt_shade(_ptr(tris), _ptr(rays), _ptr(hits),
+                             _ptr(ao_hits) if ao_hits is not None else None, n, spp, _ptr(out)))
+    return out
+
+
+# ---------------------------------------------------------------------------
+# the BVH handle
+# ---------------------------------------------------------------------------
+class Bvh:
+    """An LBVH on one GPU.  Immutable after build; ``trace`` is thread-safe."""
+
+    def __init__(self, handle: int):
+        self._h = C.c_void_p(handle)
+
+    # -- build_bvh -----------------------------------------------------------
+    @classmethod
+    def build(cls, tris, key_bits: int = 30, keep_keys: bool = False, timings: bool = False,
+              device: int = -1, stream: int = 0) -> "Bvh":
+        n = _rows(tris, 12)
+        opts = L.BuildOpts(key_bits=key_bits,
+                           flags=(L.RT_BUILD_KEEP_KEYS if keep_keys else 0) |
+                                 (L.RT_BUILD_TIMINGS if timings else 0),
+                           device=device, reserved=0, stream=stream or None)
+        h = C.c_void_p()
+        L.check(L.lib().build_bvh(_ptr(tris) if n else None, n, C.byref(opts), C.byref(h)))
+        return cls(h.value)
+
+    @classmethod
+    def alloc_empty(cls, n_tris: int, key_bits: int = 30) -> "Bvh":
+        h = C.c_void_p()
+        L.check(L.lib().bvh_alloc_empty(n_tris, key_bits, C.byref(h)))
+        return cls(h.value)
+
+    # -- trace_rays ------------------------------------------------------------
+    def trace(self, rays, flags: int = L.RT_TRACE_CLOSEST, out=None):
+        """hits float32 [n, 4]: t, u, v, prim (int32 bits).  Same kind as ``rays``."""
+        n = _rows(rays, 8)
+        if out is None:
+            out = _empty_like_kind(rays, (n, 4), None)
+        L.check(L.lib().trace_rays(self._h, _ptr(rays), n, flags, _ptr(out)))
+        return out
+
+    def trace_async(self, rays, out, flags: int = L.RT_TRACE_CLOSEST, stream: int = 0):
+        n = _rows(rays, 8)
+        L.check(L.lib().trace_rays_async(self._h, _ptr(rays), n, flags, _ptr(out), stream or None))
+        return out
+
+    def refit(self, tris) -> None:
+        L.check(L.lib().refit_bvh(self._h, _ptr(tris)))
+
+    # -- accessors ---------------------------------------------------------------
+    def info(self) -> L.BvhInfo:
+        info = L.BvhInfo()
+        L.check(L.lib().bvh_info(self._h, C.byref(info)))
+        return info
+
+    @property
+    def n_tris(self) -> int:
+        return int(self.info().n_tris)
+
+    @property
+    def bounds(self) -> np.ndarray:
+        return np.array(list(self.info().bounds), dtype=np.float32)
+
+    def read_sorted(self, keys: bool = True):
+        n = self.n_tris
+        k = np.empty(n, dtype=np.uint64) if keys else None
+        idx = np.empty(n, dtype=np.uint32)
+        L.check(L.lib().bvh_read_sorted(self._h, k.ctypes.data if keys else None, idx.ctypes.data))
+        return k, idx
+
+    def read_topology(self):
+        n = self.n_tris
+        left = np.empty(max(n - 1, 0), dtype=np.uint32)
+        right = np.empty(max(n - 1, 0), dtype=np.uint32)
+        parent = np.empty(max(2 * n - 1, 0), dtype=np.uint32)
+        L.check(L.lib().bvh_read_topology(self._h, left.ctypes.data, right.ctypes.data,
+                                          parent.ctypes.data))
+        return left, right, parent
+
+    def read_boxes(self) -> np.ndarray:
+        n = self.n_tris
+        boxes = np.empty((max(2 * n - 1, 0), 6), dtype=np.float32)
+        L.check(L.lib().bvh_read_boxes(self._h, boxes.ctypes.data))
+        return boxes
+
+    def build_times(self) -> dict:
+        ms = (C.c_float * 6)()
+        L.check(L.lib().bvh_build_times(self._h, ms))
+        return dict(zip(L.RT_STAGE_NAMES, [float(x) for x in ms]))
+
+    def device_buffers(self):
+        """[(ptr, bytes)] of nodes, reordered triangles, header (for a broadcast)."""
+        ptrs = (C.c_void_p * 3)()
+        sizes = (C.c_uint64 * 3)()
+        L.check(L.lib().bvh_device_buffers(self._h, ptrs, sizes))
+        return [(int(ptrs[i] or 0), int(sizes[i])) for i in range(3)]
+
+    def commit(self) -> None:
+        L.check(L.lib().bvh_commit(self._h))
+
+    # -- free_bvh ----------------------------------------------------------------
+    def close(self) -> None:
+        if self._h:
+            L.lib().free_bvh(self._h)
+            self._h = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def hit_prims(hits):
+    """int32 view of the prim column."""
+    if _is_tensor(hits):
+        return hits[:, 3].contiguous().view(torch.int32)
+    return np.ascontiguousarray(hits[:, 3]).view(np.int32)
+
+
+def sort_pairs(keys, vals, key_bits: int = 30) -> float:
+    """In-place device radix sort of (keys, vals); returns the device ms."""
+    ms = C.c_float()
+    n = int(keys.numel())
+    L.check(L.lib().rt_sort_pairs(keys.data_ptr(), vals.data_ptr(), n, key_bits, C.byref(ms)))
+    return float(ms.value)
+
+
+def set_param(name: str, value: int) -> None:
+    L.check(L.lib().rt_set_param(name.encode(), value))
+
+
+def kernel_launches() -> int:
+    return int(L.lib().rt_kernel_launches())

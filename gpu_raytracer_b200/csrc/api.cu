@@ -1,0 +1,809 @@
+// api.cu — host runtime and C ABI of libgpu_raytracer_b200.so
+// (include/gpu_raytracer.h).
+//
+// The runtime owns device buffers (stream-ordered pool allocations, so repeated
+// builds do not pay cudaMalloc), sequences the build stages on one stream,
+// pipelines host-resident ray batches through pinned-or-pageable copies on
+// three streams, and keeps no global mutable state besides tuning knobs and a
+// launch counter.  There is no CPU fallback: every entry point fails with
+// RT_ERR_NO_DEVICE when no CUDA device is usable.
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <new>
+#include <vector>
+
+#include "../../include/gpu_raytracer.h"
+#include "common.cuh"
+#include "kernels.h"
+
+namespace rt {
+
+std::atomic<uint64_t> g_kernel_launches{0};
+
+namespace {
+thread_local char t_error[512] = "";
+}
+
+int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(t_error, sizeof(t_error), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+int fail_cuda(cudaError_t e, const char* what, const char* file, int line) {
+  const char* base = strrchr(file, '/');
+  snprintf(t_error, sizeof(t_error), "CUDA error %d (%s) at %s:%d: %s", (int)e,
+           cudaGetErrorString(e), base ? base + 1 : file, line, what);
+  cudaGetLastError();  // clear the sticky-less error state
+  if (e == cudaErrorMemoryAllocation) return RT_ERR_OOM;
+  if (e == cudaErrorNoDevice || e == cudaErrorInsufficientDriver) return RT_ERR_NO_DEVICE;
+  return RT_ERR_CUDA;
+}
+
+Params& params() {
+  static Params p;
+  return p;
+}
+
+int num_sms() {
+  Params& p = params();
+  if (p.num_sms == 0) {
+    int dev = 0, sms = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess &&
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && sms > 0)
+      p.num_sms = sms;
+    else
+      p.num_sms = kNumSMsB200;
+  }
+  return p.num_sms;
+}
+
+namespace {
+
+int ensure_device() {
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  if (e != cudaSuccess || count == 0) {
+    cudaGetLastError();
+    return fail(RT_ERR_NO_DEVICE, "no CUDA device available (%s); this library has no CPU path",
+                e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+  }
+  return 0;
+}
+
+// keeps pool memory cached between calls (set once per device)
+int tune_pool(int device) {
+  static std::mutex mu;
+  static std::vector<int> done;
+  std::lock_guard<std::mutex> lock(mu);
+  for (int d : done)
+    if (d == device) return 0;
+  cudaMemPool_t pool;
+  RT_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
+  uint64_t thr = UINT64_MAX;
+  RT_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr));
+  done.push_back(device);
+  return 0;
+}
+
+// 0 = host (or unregistered), 1 = device/managed memory; *dev = owning device
+int classify(const void* p, int* dev) {
+  cudaPointerAttributes a;
+  cudaError_t e = cudaPointerGetAttributes(&a, p);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  if (a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged) {
+    if (dev) *dev = a.device;
+    return 1;
+  }
+  return 0;
+}
+
+struct DeviceScope {
+  int prev = -1;
+  bool switched = false;
+  int enter(int device) {
+    RT_CUDA(cudaGetDevice(&prev));
+    if (device >= 0 && device != prev) {
+      RT_CUDA(cudaSetDevice(device));
+      switched = true;
+    }
+    return 0;
+  }
+  ~DeviceScope() {
+    if (switched) cudaSetDevice(prev);
+  }
+};
+
+// stream-ordered temporary allocations, released on scope exit
+struct TempPool {
+  cudaStream_t s;
+  std::vector<void*> ptrs;
+  explicit TempPool(cudaStream_t stream) : s(stream) {}
+  int alloc(void** out, size_t bytes) {
+    if (bytes == 0) bytes = 16;
+    RT_CUDA(cudaMallocAsync(out, bytes, s));
+    ptrs.push_back(*out);
+    return 0;
+  }
+  ~TempPool() {
+    for (void* p : ptrs) cudaFreeAsync(p, s);
+  }
+};
+
+}  // namespace
+}  // namespace rt
+
+using namespace rt;
+
+struct rt_bvh {
+  uint64_t n = 0;
+  uint32_t key_bits = 30;
+  int device = 0;
+  Node* nodes = nullptr;
+  SortedTri* stris = nullptr;
+  BvhHeader* header = nullptr;
+  uint32_t* parent = nullptr;
+  void* keys = nullptr;  // only with RT_BUILD_KEEP_KEYS
+  float bounds[6] = {0, 0, 0, 0, 0, 0};
+  float times[RT_STAGE_COUNT] = {0, 0, 0, 0, 0, 0};
+  bool has_times = false;
+  uint64_t bytes = 0;
+};
+
+namespace {
+
+size_t key_size(uint32_t key_bits) { return key_bits == 30 ? 4 : 8; }
+
+void release(rt_bvh* h) {
+  if (!h) return;
+  int prev = -1;
+  cudaGetDevice(&prev);
+  if (prev != h->device) cudaSetDevice(h->device);
+  if (h->nodes) cudaFreeAsync(h->nodes, 0);
+  if (h->stris) cudaFreeAsync(h->stris, 0);
+  if (h->header) cudaFreeAsync(h->header, 0);
+  if (h->parent) cudaFreeAsync(h->parent, 0);
+  if (h->keys) cudaFreeAsync(h->keys, 0);
+  if (prev != h->device && prev >= 0) cudaSetDevice(prev);
+  delete h;
+}
+
+int alloc_handle_buffers(rt_bvh* h, bool keep_keys, cudaStream_t s) {
+  const uint64_t n = h->n;
+  const size_t node_bytes = (n > 1 ? (n - 1) : 1) * sizeof(Node);
+  const size_t tri_bytes = (n ? n : 1) * sizeof(SortedTri);
+  const size_t parent_bytes = (n ? (2 * n - 1) : 1) * sizeof(uint32_t);
+  RT_CUDA(cudaMallocAsync((void**)&h->nodes, node_bytes, s));
+  RT_CUDA(cudaMallocAsync((void**)&h->stris, tri_bytes, s));
+  RT_CUDA(cudaMallocAsync((void**)&h->header, sizeof(BvhHeader), s));
+  RT_CUDA(cudaMallocAsync((void**)&h->parent, parent_bytes, s));
+  h->bytes = node_bytes + tri_bytes + sizeof(BvhHeader) + parent_bytes;
+  if (keep_keys) {
+    RT_CUDA(cudaMallocAsync(&h->keys, (n ? n : 1) * key_size(h->key_bits), s));
+    h->bytes += (n ? n : 1) * key_size(h->key_bits);
+  }
+  return 0;
+}
+
+}  // namespace
+
+// ===========================================================================
+// build_bvh  (call stack 1 of §3)
+// ===========================================================================
+namespace {
+
+int build_impl(rt_bvh* h, const float* tris_in, uint32_t flags, cudaStream_t s) {
+  const uint64_t n = h->n;
+  TempPool tmp(s);
+  RT_TRY(alloc_handle_buffers(h, (flags & RT_BUILD_KEEP_KEYS) != 0, s));
+
+  BvhHeader hdr;
+  memset(&hdr, 0, sizeof(hdr));
+  hdr.n_tris_lo = (uint32_t)n;
+  hdr.n_tris_hi = (uint32_t)(n >> 32);
+  hdr.key_bits = h->key_bits;
+  RT_CUDA(cudaMemcpyAsync(h->header, &hdr, sizeof(hdr), cudaMemcpyHostToDevice, s));
+  if (n == 0) {
+    RT_CUDA(cudaStreamSynchronize(s));
+    return 0;
+  }
+
+  // triangles: use device memory in place, stage host memory
+  const float4* tris = nullptr;
+  int pdev = -1;
+  if (classify(tris_in, &pdev)) {
+    if (pdev != h->device)
+      return fail(RT_ERR_INVALID, "build_bvh: tris live on device %d, build runs on device %d",
+                  pdev, h->device);
+    tris = reinterpret_cast<const float4*>(tris_in);
+  } else {
+    void* d = nullptr;
+    RT_TRY(tmp.alloc(&d, n * 48));
+    RT_CUDA(cudaMemcpyAsync(d, tris_in, n * 48, cudaMemcpyHostToDevice, s));
+    tris = reinterpret_cast<const float4*>(d);
+  }
+
+  const size_t ksz = key_size(h->key_bits);
+  const int passes = sort_num_passes(h->key_bits);
+  void *keys = nullptr, *bkeys = nullptr, *flags_buf = nullptr;
+  SortWorkspace ws;
+  RT_TRY(tmp.alloc(&keys, n * ksz));
+  RT_TRY(tmp.alloc(&ws.keys_alt, n * ksz));
+  RT_TRY(tmp.alloc((void**)&ws.vals, n * 4));
+  RT_TRY(tmp.alloc((void**)&ws.vals_alt, n * 4));
+  RT_TRY(tmp.alloc((void**)&ws.hist, (size_t)2 * passes * 256 * 4));
+  ws.lookback_words = sort_lookback_words(n, h->key_bits);
+  RT_TRY(tmp.alloc((void**)&ws.lookback, ws.lookback_words * 4));
+  RT_TRY(tmp.alloc(&bkeys, 32));
+  RT_TRY(tmp.alloc(&flags_buf, (n > 1 ? n - 1 : 1) * 4));
+
+  const bool timed = (flags & RT_BUILD_TIMINGS) != 0;
+  cudaEvent_t ev[RT_STAGE_COUNT];
+  if (timed)
+    for (int i = 0; i < RT_STAGE_COUNT; ++i) RT_CUDA(cudaEventCreate(&ev[i]));
+  auto mark = [&](int i) -> int {
+    if (timed) RT_CUDA(cudaEventRecord(ev[i], s));
+    return 0;
+  };
+
+  RT_TRY(mark(0));
+  RT_TRY(launch_bounds(tris, n, (uint32_t*)bkeys, s));
+  RT_TRY(mark(1));
+  RT_TRY(launch_morton(tris, n, (const uint32_t*)bkeys, h->key_bits, keys, ws.hist, s));
+  RT_TRY(mark(2));
+  void* skeys = nullptr;
+  uint32_t* svals = nullptr;
+  RT_TRY(launch_sort(keys, n, h->key_bits, ws, /*iota_payload=*/true, &skeys, &svals, s));
+  RT_TRY(mark(3));
+  RT_TRY(launch_karras(skeys, n, h->key_bits, h->parent, s));
+  RT_TRY(mark(4));
+  RT_TRY(launch_refit(tris, svals, n, h->parent, (uint32_t*)flags_buf, h->nodes, h->stris,
+                      h->header, s));
+  RT_TRY(mark(5));
+  if (h->keys) RT_CUDA(cudaMemcpyAsync(h->keys, skeys, n * ksz, cudaMemcpyDeviceToDevice, s));
+  RT_CUDA(cudaMemcpyAsync(&hdr, h->header, sizeof(hdr), cudaMemcpyDeviceToHost, s));
+  RT_CUDA(cudaStreamSynchronize(s));
+  for (int k = 0; k < 3; ++k) {
+    h->bounds[k] = hdr.root_min[k];
+    h->bounds[3 + k] = hdr.root_max[k];
+  }
+  if (timed) {
+    for (int i = 0; i < 5; ++i) RT_CUDA(cudaEventElapsedTime(&h->times[i], ev[i], ev[i + 1]));
+    RT_CUDA(cudaEventElapsedTime(&h->times[RT_STAGE_TOTAL], ev[0], ev[5]));
+    for (int i = 0; i < RT_STAGE_COUNT; ++i) cudaEventDestroy(ev[i]);
+    h->has_times = true;
+  }
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int build_bvh(const float* tris, uint64_t n_tris, const rt_build_opts* opts,
+                         rt_bvh** out) {
+  if (!out) return fail(RT_ERR_INVALID, "build_bvh: out is NULL");
+  *out = nullptr;
+  if (n_tris && !tris) return fail(RT_ERR_INVALID, "build_bvh: tris is NULL");
+  if (n_tris > RT_MAX_TRIS)
+    return fail(RT_ERR_LIMIT, "build_bvh: %llu triangles exceed RT_MAX_TRIS",
+                (unsigned long long)n_tris);
+  uint32_t key_bits = (opts && opts->key_bits) ? opts->key_bits : 30;
+  if (key_bits != 30 && key_bits != 63)
+    return fail(RT_ERR_INVALID, "build_bvh: key_bits must be 30 or 63, got %u", key_bits);
+  RT_TRY(ensure_device());
+  DeviceScope scope;
+  RT_TRY(scope.enter(opts ? opts->device : -1));
+  int dev = 0;
+  RT_CUDA(cudaGetDevice(&dev));
+  RT_TRY(tune_pool(dev));
+  rt_bvh* h = new (std::nothrow) rt_bvh;
+  if (!h) return fail(RT_ERR_OOM, "build_bvh: host allocation failed");
+  h->n = n_tris;
+  h->key_bits = key_bits;
+  h->device = dev;
+  cudaStream_t s = opts ? (cudaStream_t)opts->stream : (cudaStream_t)0;
+  int rc = build_impl(h, tris, opts ? opts->flags : 0u, s);
+  if (rc != 0) {
+    release(h);
+    return rc;
+  }
+  *out = h;
+  return RT_OK;
+}
+
+extern "C" void free_bvh(rt_bvh* h) { release(h); }
+
+extern "C" const char* bvh_last_error(void) { return rt::t_error; }
+
+extern "C" int refit_bvh(rt_bvh* h, const float* tris_in) {
+  if (!h) return fail(RT_ERR_INVALID, "refit_bvh: handle is NULL");
+  if (h->n == 0) return RT_OK;
+  if (!tris_in) return fail(RT_ERR_INVALID, "refit_bvh: tris is NULL");
+  DeviceScope scope;
+  RT_TRY(scope.enter(h->device));
+  cudaStream_t s = 0;
+  TempPool tmp(s);
+  const float4* tris = nullptr;
+  int pdev = -1;
+  if (classify(tris_in, &pdev)) {
+    tris = reinterpret_cast<const float4*>(tris_in);
+  } else {
+    void* d = nullptr;
+    RT_TRY(tmp.alloc(&d, h->n * 48));
+    RT_CUDA(cudaMemcpyAsync(d, tris_in, h->n * 48, cudaMemcpyHostToDevice, s));
+    tris = reinterpret_cast<const float4*>(d);
+  }
+  void* flags_buf = nullptr;
+  RT_TRY(tmp.alloc(&flags_buf, (h->n > 1 ? h->n - 1 : 1) * 4));
+  RT_TRY(launch_refit_update(tris, h->n, h->parent, (uint32_t*)flags_buf, h->nodes, h->stris,
+                             h->header, s));
+  BvhHeader hdr;
+  RT_CUDA(cudaMemcpyAsync(&hdr, h->header, sizeof(hdr), cudaMemcpyDeviceToHost, s));
+  RT_CUDA(cudaStreamSynchronize(s));
+  for (int k = 0; k < 3; ++k) {
+    h->bounds[k] = hdr.root_min[k];
+    h->bounds[3 + k] = hdr.root_max[k];
+  }
+  return RT_OK;
+}
+
+// ===========================================================================
+// trace_rays  (call stack 2 of §3)
+// ===========================================================================
+namespace {
+
+// per-thread, per-device resources of the host-buffer pipeline: three streams
+// (H2D, compute, D2H), two staging slots, events.  Created on first use.
+struct Pipeline {
+  static constexpr uint64_t kChunk = 1ull << 20;  // rays per chunk: 32 MiB in, 16 MiB out
+  int device = -1;
+  cudaStream_t s_in = nullptr, s_run = nullptr, s_out = nullptr;
+  float4* rays[2] = {nullptr, nullptr};
+  float4* hits[2] = {nullptr, nullptr};
+  unsigned long long* counters = nullptr;  // 2
+  cudaEvent_t ev_in[2], ev_run[2], ev_out[2];
+  bool ready = false;
+  int init(int dev) {
+    if (ready && device == dev) return 0;
+    device = dev;
+    RT_CUDA(cudaStreamCreateWithFlags(&s_in, cudaStreamNonBlocking));
+    RT_CUDA(cudaStreamCreateWithFlags(&s_run, cudaStreamNonBlocking));
+    RT_CUDA(cudaStreamCreateWithFlags(&s_out, cudaStreamNonBlocking));
+    for (int b = 0; b < 2; ++b) {
+      RT_CUDA(cudaMalloc((void**)&rays[b], kChunk * 32));
+      RT_CUDA(cudaMalloc((void**)&hits[b], kChunk * 16));
+      RT_CUDA(cudaEventCreateWithFlags(&ev_in[b], cudaEventDisableTiming));
+      RT_CUDA(cudaEventCreateWithFlags(&ev_run[b], cudaEventDisableTiming));
+      RT_CUDA(cudaEventCreateWithFlags(&ev_out[b], cudaEventDisableTiming));
+    }
+    RT_CUDA(cudaMalloc((void**)&counters, 2 * sizeof(unsigned long long)));
+    ready = true;
+    return 0;
+  }
+};
+thread_local Pipeline t_pipe;
+
+int trace_device(const rt_bvh* h, const float4* rays, uint64_t n_rays, uint32_t flags,
+                 float4* hits, cudaStream_t s) {
+  unsigned long long* counter = nullptr;
+  RT_CUDA(cudaMallocAsync((void**)&counter, sizeof(unsigned long long), s));
+  int rc = launch_trace(h->nodes, h->stris, h->n, rays, n_rays, flags, hits, counter, s);
+  cudaFreeAsync(counter, s);
+  return rc;
+}
+
+// host rays and/or host hits: chunked, copies overlap the traversal
+int trace_staged(const rt_bvh* h, const float* rays, bool rays_dev, uint64_t n_rays, uint32_t flags,
+                 float* hits, bool hits_dev) {
+  Pipeline& p = t_pipe;
+  RT_TRY(p.init(h->device));
+  // the legacy default stream may still be producing the inputs
+  RT_CUDA(cudaStreamSynchronize(0));
+  const uint64_t chunks = (n_rays + Pipeline::kChunk - 1) / Pipeline::kChunk;
+  for (uint64_t c = 0; c < chunks; ++c) {
+    const int b = (int)(c & 1);
+    const uint64_t first = c * Pipeline::kChunk;
+    const uint64_t cnt = (n_rays - first < Pipeline::kChunk) ? (n_rays - first) : Pipeline::kChunk;
+    const float4* rsrc;
+    if (rays_dev) {
+      rsrc = reinterpret_cast<const float4*>(rays) + 2 * first;
+    } else {
+      if (c >= 2) RT_CUDA(cudaStreamWaitEvent(p.s_in, p.ev_run[b], 0));  // slot's last reader
+      RT_CUDA(cudaMemcpyAsync(p.rays[b], rays + 8 * first, cnt * 32, cudaMemcpyHostToDevice, p.s_in));
+      RT_CUDA(cudaEventRecord(p.ev_in[b], p.s_in));
+      RT_CUDA(cudaStreamWaitEvent(p.s_run, p.ev_in[b], 0));
+      rsrc = p.rays[b];
+    }
+    float4* hdst;
+    if (hits_dev) {
+      hdst = reinterpret_cast<float4*>(hits) + first;
+    } else {
+      if (c >= 2) RT_CUDA(cudaStreamWaitEvent(p.s_run, p.ev_out[b], 0));  // slot drained
+      hdst = p.hits[b];
+    }
+    RT_TRY(launch_trace(h->nodes, h->stris, h->n, rsrc, cnt, flags, hdst, p.counters + b, p.s_run));
+    RT_CUDA(cudaEventRecord(p.ev_run[b], p.s_run));
+    if (!hits_dev) {
+      RT_CUDA(cudaStreamWaitEvent(p.s_out, p.ev_run[b], 0));
+      RT_CUDA(cudaMemcpyAsync(hits + 4 * first, p.hits[b], cnt * 16, cudaMemcpyDeviceToHost, p.s_out));
+      RT_CUDA(cudaEventRecord(p.ev_out[b], p.s_out));
+    }
+  }
+  RT_CUDA(cudaStreamSynchronize(p.s_run));
+  RT_CUDA(cudaStreamSynchronize(p.s_out));
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int trace_rays_async(const rt_bvh* h, const float* rays, uint64_t n_rays, uint32_t flags,
+                                float* hits, void* stream) {
+  if (!h) return fail(RT_ERR_INVALID, "trace_rays: handle is NULL");
+  if (n_rays == 0) return RT_OK;
+  if (!rays || !hits) return fail(RT_ERR_INVALID, "trace_rays: rays or hits is NULL");
+  if (flags > 1u) return fail(RT_ERR_INVALID, "trace_rays: unknown flags 0x%x", flags);
+  DeviceScope scope;
+  RT_TRY(scope.enter(h->device));
+  return trace_device(h, reinterpret_cast<const float4*>(rays), n_rays, flags,
+                      reinterpret_cast<float4*>(hits), (cudaStream_t)stream);
+}
+
+extern "C" int trace_rays(const rt_bvh* h, const float* rays, uint64_t n_rays, uint32_t flags,
+                          float* hits) {
+  if (!h) return fail(RT_ERR_INVALID, "trace_rays: handle is NULL");
+  if (n_rays == 0) return RT_OK;
+  if (!rays || !hits) return fail(RT_ERR_INVALID, "trace_rays: rays or hits is NULL");
+  if (flags > 1u) return fail(RT_ERR_INVALID, "trace_rays: unknown flags 0x%x", flags);
+  DeviceScope scope;
+  RT_TRY(scope.enter(h->device));
+  int d0 = -1, d1 = -1;
+  const bool rays_dev = classify(rays, &d0) != 0, hits_dev = classify(hits, &d1) != 0;
+  if ((rays_dev && d0 != h->device) || (hits_dev && d1 != h->device))
+    return fail(RT_ERR_INVALID, "trace_rays: buffers are not on the handle's device %d", h->device);
+  if (rays_dev && hits_dev) {
+    RT_TRY(trace_device(h, reinterpret_cast<const float4*>(rays), n_rays, flags,
+                        reinterpret_cast<float4*>(hits), 0));
+    RT_CUDA(cudaStreamSynchronize(0));
+    return RT_OK;
+  }
+  return trace_staged(h, rays, rays_dev, n_rays, flags, hits, hits_dev);
+}
+
+// ===========================================================================
+// accessors (parity tests T2-T4)
+// ===========================================================================
+extern "C" int bvh_info(const rt_bvh* h, rt_bvh_info* out) {
+  if (!h || !out) return fail(RT_ERR_INVALID, "bvh_info: NULL argument");
+  out->n_tris = h->n;
+  out->n_nodes = h->n ? 2 * h->n - 1 : 0;
+  out->key_bits = h->key_bits;
+  out->device = h->device;
+  memcpy(out->bounds, h->bounds, sizeof(h->bounds));
+  out->device_bytes = h->bytes;
+  return RT_OK;
+}
+
+extern "C" int bvh_read_sorted(const rt_bvh* h, uint64_t* keys, uint32_t* prim_idx) {
+  if (!h) return fail(RT_ERR_INVALID, "bvh_read_sorted: handle is NULL");
+  if (h->n == 0) return RT_OK;
+  DeviceScope scope;
+  RT_TRY(scope.enter(h->device));
+  cudaStream_t s = 0;
+  TempPool tmp(s);
+  if (keys) {
+    if (!h->keys) return fail(RT_ERR_INVALID, "bvh_read_sorted: built without RT_BUILD_KEEP_KEYS");
+    if (h->key_bits == 30) {
+      void* wide = nullptr;
+      RT_TRY(tmp.alloc(&wide, h->n * 8));
+      RT_TRY(launch_widen_keys((const uint32_t*)h->keys, h->n, (uint64_t*)wide, s));
+      RT_CUDA(cudaMemcpyAsync(keys, wide, h->n * 8, cudaMemcpyDeviceToHost, s));
+    } else {
+      RT_CUDA(cudaMemcpyAsync(keys, h->keys, h->n * 8, cudaMemcpyDeviceToHost, s));
+    }
+  }
+  if (prim_idx) {
+    void* idx = nullptr;
+    RT_TRY(tmp.alloc(&idx, h->n * 4));
+    RT_TRY(launch_unpack_sorted(h->stris, h->n, (uint32_t*)idx, s));
+    RT_CUDA(cudaMemcpyAsync(prim_idx, idx, h->n * 4, cudaMemcpyDeviceToHost, s));
+  }
+  RT_CUDA(cudaStreamSynchronize(s));
+  return RT_OK;
+}
+
+namespace {
+int read_canonical(const rt_bvh* h, uint32_t* left, uint32_t* right, uint32_t* parent,
+                   float* boxes) {
+  if (h->n == 0) return RT_OK;
+  DeviceScope scope;
+  RT_TRY(scope.enter(h->device));
+  cudaStream_t s = 0;
+  TempPool tmp(s);
+  const uint64_t n = h->n, nodes = 2 * n - 1;
+  void *dl = nullptr, *dr = nullptr, *dp = nullptr, *db = nullptr;
+  if (left) RT_TRY(tmp.alloc(&dl, (n - 1) * 4));
+  if (right) RT_TRY(tmp.alloc(&dr, (n - 1) * 4));
+  if (parent) RT_TRY(tmp.alloc(&dp, nodes * 4));
+  if (boxes) RT_TRY(tmp.alloc(&db, nodes * 24));
+  RT_TRY(launch_export_topology(h->nodes, h->parent, n, (uint32_t*)dl, (uint32_t*)dr,
+                                (uint32_t*)dp, (float*)db, h->header, s));
+  if (left && n > 1) RT_CUDA(cudaMemcpyAsync(left, dl, (n - 1) * 4, cudaMemcpyDeviceToHost, s));
+  if (right && n > 1) RT_CUDA(cudaMemcpyAsync(right, dr, (n - 1) * 4, cudaMemcpyDeviceToHost, s));
+  if (parent) RT_CUDA(cudaMemcpyAsync(parent, dp, nodes * 4, cudaMemcpyDeviceToHost, s));
+  if (boxes) RT_CUDA(cudaMemcpyAsync(boxes, db, nodes * 24, cudaMemcpyDeviceToHost, s));
+  RT_CUDA(cudaStreamSynchronize(s));
+  return RT_OK;
+}
+}  // namespace
+
+extern "C" int bvh_read_topology(const rt_bvh* h, uint32_t* left, uint32_t* right,
+                                 uint32_t* parent) {
+  if (!h) return fail(RT_ERR_INVALID, "bvh_read_topology: handle is NULL");
+  return read_canonical(h, left, right, parent, nullptr);
+}
+
+extern "C" int bvh_read_boxes(const rt_bvh* h, float* boxes) {
+  if (!h) return fail(RT_ERR_INVALID, "bvh_read_boxes: handle is NULL");
+  return read_canonical(h, nullptr, nullptr, nullptr, boxes);
+}
+
+extern "C" int bvh_build_times(const rt_bvh* h, float* ms) {
+  if (!h || !ms) return fail(RT_ERR_INVALID, "bvh_build_times: NULL argument");
+  if (!h->has_times) return fail(RT_ERR_INVALID, "bvh_build_times: built without RT_BUILD_TIMINGS");
+  memcpy(ms, h->times, sizeof(h->times));
+  return RT_OK;
+}
+
+// ===========================================================================
+// multi-GPU helpers: expose the buffers a rank broadcasts
+// ===========================================================================
+extern "C" int bvh_device_buffers(const rt_bvh* h, void** ptrs, uint64_t* bytes) {
+  if (!h || !ptrs || !bytes) return fail(RT_ERR_INVALID, "bvh_device_buffers: NULL argument");
+  ptrs[0] = h->nodes;
+  bytes[0] = (h->n > 1 ? h->n - 1 : 0) * sizeof(Node);
+  ptrs[1] = h->stris;
+  bytes[1] = h->n * sizeof(SortedTri);
+  ptrs[2] = h->header;
+  bytes[2] = sizeof(BvhHeader);
+  return RT_OK;
+}
+
+extern "C" int bvh_alloc_empty(uint64_t n_tris, uint32_t key_bits, rt_bvh** out) {
+  if (!out) return fail(RT_ERR_INVALID, "bvh_alloc_empty: out is NULL");
+  *out = nullptr;
+  if (n_tris > RT_MAX_TRIS) return fail(RT_ERR_LIMIT, "bvh_alloc_empty: too many triangles");
+  if (key_bits == 0) key_bits = 30;
+  if (key_bits != 30 && key_bits != 63) return fail(RT_ERR_INVALID, "bvh_alloc_empty: key_bits");
+  RT_TRY(ensure_device());
+  int dev = 0;
+  RT_CUDA(cudaGetDevice(&dev));
+  RT_TRY(tune_pool(dev));
+  rt_bvh* h = new (std::nothrow) rt_bvh;
+  if (!h) return fail(RT_ERR_OOM, "bvh_alloc_empty: host allocation failed");
+  h->n = n_tris;
+  h->key_bits = key_bits;
+  h->device = dev;
+  int rc = alloc_handle_buffers(h, false, 0);
+  if (rc == 0 && cudaStreamSynchronize(0) != cudaSuccess) rc = RT_ERR_CUDA;
+  if (rc != 0) {
+    release(h);
+    return rc;
+  }
+  *out = h;
+  return RT_OK;
+}
+
+extern "C" int bvh_commit(rt_bvh* h) {
+  if (!h) return fail(RT_ERR_INVALID, "bvh_commit: handle is NULL");
+  DeviceScope scope;
+  RT_TRY(scope.enter(h->device));
+  BvhHeader hdr;
+  RT_CUDA(cudaMemcpy(&hdr, h->header, sizeof(hdr), cudaMemcpyDeviceToHost));
+  const uint64_t n = ((uint64_t)hdr.n_tris_hi << 32) | hdr.n_tris_lo;
+  if (n != h->n)
+    return fail(RT_ERR_INVALID, "bvh_commit: header says %llu triangles, handle was sized for %llu",
+                (unsigned long long)n, (unsigned long long)h->n);
+  h->key_bits = hdr.key_bits;
+  for (int k = 0; k < 3; ++k) {
+    h->bounds[k] = hdr.root_min[k];
+    h->bounds[3 + k] = hdr.root_max[k];
+  }
+  return RT_OK;
+}
+
+// ===========================================================================
+// generators and shading
+// ===========================================================================
+namespace {
+
+// runs fn(device_out) and, when out is host memory, copies the result back
+template <typename Fn>
+int with_output(void* out, size_t bytes, Fn fn) {
+  RT_TRY(ensure_device());
+  if (bytes == 0) return RT_OK;
+  if (!out) return fail(RT_ERR_INVALID, "output pointer is NULL");
+  cudaStream_t s = 0;
+  if (classify(out, nullptr)) {
+    RT_TRY(fn(out, s));
+    RT_CUDA(cudaStreamSynchronize(s));
+    return RT_OK;
+  }
+  TempPool tmp(s);
+  void* d = nullptr;
+  RT_TRY(tmp.alloc(&d, bytes));
+  RT_TRY(fn(d, s));
+  RT_CUDA(cudaMemcpyAsync(out, d, bytes, cudaMemcpyDeviceToHost, s));
+  RT_CUDA(cudaStreamSynchronize(s));
+  return RT_OK;
+}
+
+// device view of an input: in place when already on the device, staged otherwise
+int stage_input(TempPool& tmp, const void* p, size_t bytes, const void** out) {
+  if (classify(p, nullptr)) {
+    *out = p;
+    return 0;
+  }
+  void* d = nullptr;
+  RT_TRY(tmp.alloc(&d, bytes));
+  RT_CUDA(cudaMemcpyAsync(d, p, bytes, cudaMemcpyHostToDevice, tmp.s));
+  *out = d;
+  return 0;
+}
+
+}  // namespace
+
+extern "C" uint64_t rt_scene_size(int kind, uint64_t p0, uint64_t p1) {
+  switch (kind) {
+    case RT_SCENE_CORNELL: return 1024;
+    case RT_SCENE_SOUP: return p0;
+    case RT_SCENE_SPHEREFLAKE: {
+      uint64_t spheres = 0, p = 1;
+      for (uint64_t l = 0; l <= p0 && l < 16; ++l) {
+        spheres += p;
+        p *= 9;
+      }
+      return spheres * 8ull * p1 * p1;
+    }
+    case RT_SCENE_TERRAIN: return 2ull * p0 * p0;
+  }
+  return 0;
+}
+
+extern "C" int rt_gen_scene(int kind, uint64_t p0, uint64_t p1, uint64_t seed, uint64_t first,
+                            uint64_t count, float* out) {
+  if (kind < 0 || kind > 3) return fail(RT_ERR_INVALID, "rt_gen_scene: unknown scene kind %d", kind);
+  if (first + count > rt_scene_size(kind, p0, p1))
+    return fail(RT_ERR_INVALID, "rt_gen_scene: range beyond the scene's %llu triangles",
+                (unsigned long long)rt_scene_size(kind, p0, p1));
+  if (kind == RT_SCENE_SPHEREFLAKE && (p0 > 8 || p1 == 0 || p1 > 1024))
+    return fail(RT_ERR_INVALID, "rt_gen_scene: sphereflake depth <= 8, 1 <= segments <= 1024");
+  if (kind == RT_SCENE_TERRAIN && p0 >= (1u << 23))
+    return fail(RT_ERR_INVALID, "rt_gen_scene: terrain side too large");
+  return with_output(out, count * 48, [&](void* d, cudaStream_t s) {
+    return launch_gen_scene(kind, p0, p1, seed, first, count, (float4*)d, s);
+  });
+}
+
+extern "C" int rt_gen_primary_rays(const float* cam, uint32_t width, uint32_t height,
+                                   uint64_t first, uint64_t count, float* out) {
+  if (!cam || width == 0 || height == 0)
+    return fail(RT_ERR_INVALID, "rt_gen_primary_rays: bad camera or image size");
+  if (first + count > (uint64_t)width * height)
+    return fail(RT_ERR_INVALID, "rt_gen_primary_rays: range beyond the image");
+  return with_output(out, count * 32, [&](void* d, cudaStream_t s) {
+    return launch_gen_primary(cam, width, height, first, count, (float4*)d, s);
+  });
+}
+
+extern "C" int rt_gen_random_rays(const float* box, uint64_t seed, uint64_t first, uint64_t count,
+                                  float* out) {
+  if (!box) return fail(RT_ERR_INVALID, "rt_gen_random_rays: box is NULL");
+  return with_output(out, count * 32, [&](void* d, cudaStream_t s) {
+    return launch_gen_random(box, seed, first, count, (float4*)d, s);
+  });
+}
+
+extern "C" int rt_gen_ao_rays(const float* tris, const float* rays, const float* hits, uint64_t n,
+                              uint32_t spp, uint64_t seed, float radius, float* out) {
+  if (!tris || !rays || !hits) return fail(RT_ERR_INVALID, "rt_gen_ao_rays: NULL input");
+  return with_output(out, n * spp * 32, [&](void* d, cudaStream_t s) {
+    // tris is indexed by primitive id: its extent is unknown here, so it must
+    // already be on the device unless rays/hits are host too (small cases):
+    TempPool tmp(s);
+    const void *dr = nullptr, *dh = nullptr;
+    if (!classify(tris, nullptr))
+      return fail(RT_ERR_INVALID, "rt_gen_ao_rays: tris must be device memory");
+    RT_TRY(stage_input(tmp, rays, n * 32, &dr));
+    RT_TRY(stage_input(tmp, hits, n * 16, &dh));
+    return launch_gen_ao((const float4*)tris, (const float4*)dr, (const float4*)dh, n, spp, seed,
+                         radius, (float4*)d, s);
+  });
+}
+
+extern "C" int rt_shade(const float* tris, const float* rays, const float* hits,
+                        const float* ao_hits, uint64_t n, uint32_t spp, float* rgb) {
+  if (!tris || !rays || !hits) return fail(RT_ERR_INVALID, "rt_shade: NULL input");
+  return with_output(rgb, n * 12, [&](void* d, cudaStream_t s) {
+    TempPool tmp(s);
+    const void *dr = nullptr, *dh = nullptr, *da = nullptr;
+    if (!classify(tris, nullptr)) return fail(RT_ERR_INVALID, "rt_shade: tris must be device memory");
+    RT_TRY(stage_input(tmp, rays, n * 32, &dr));
+    RT_TRY(stage_input(tmp, hits, n * 16, &dh));
+    if (ao_hits && spp) RT_TRY(stage_input(tmp, ao_hits, n * spp * 16, &da));
+    return launch_shade((const float4*)tris, (const float4*)dr, (const float4*)dh,
+                        (const float4*)da, n, spp, (float*)d, s);
+  });
+}
+
+// ===========================================================================
+// runtime
+// ===========================================================================
+extern "C" int rt_device_count(void) {
+  int count = 0;
+  if (cudaGetDeviceCount(&count) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return count;
+}
+
+extern "C" uint64_t rt_kernel_launches(void) { return g_kernel_launches.load(); }
+
+extern "C" int rt_set_param(const char* name, int64_t value) {
+  if (!name) return fail(RT_ERR_INVALID, "rt_set_param: name is NULL");
+  Params& p = params();
+  if (!strcmp(name, "sort.variant")) p.sort_variant = (int)value;
+  else if (!strcmp(name, "trace.blocks_per_sm")) p.trace_blocks_per_sm = (int)value;
+  else if (!strcmp(name, "trace.variant")) p.trace_variant = (int)value;
+  else return fail(RT_ERR_INVALID, "rt_set_param: unknown parameter '%s'", name);
+  return RT_OK;
+}
+
+extern "C" int rt_sort_pairs(void* keys, uint32_t* vals, uint64_t n, uint32_t key_bits, float* ms) {
+  if (key_bits != 30 && key_bits != 63) return fail(RT_ERR_INVALID, "rt_sort_pairs: key_bits");
+  if (n == 0) return RT_OK;
+  if (!keys || !vals) return fail(RT_ERR_INVALID, "rt_sort_pairs: NULL buffer");
+  RT_TRY(ensure_device());
+  if (!classify(keys, nullptr) || !classify(vals, nullptr))
+    return fail(RT_ERR_INVALID, "rt_sort_pairs: keys and vals must be device memory");
+  int dev = 0;
+  RT_CUDA(cudaGetDevice(&dev));
+  RT_TRY(tune_pool(dev));
+  cudaStream_t s = 0;
+  TempPool tmp(s);
+  const size_t ksz = key_size(key_bits);
+  const int passes = sort_num_passes(key_bits);
+  SortWorkspace ws;
+  ws.vals = vals;
+  RT_TRY(tmp.alloc(&ws.keys_alt, n * ksz));
+  RT_TRY(tmp.alloc((void**)&ws.vals_alt, n * 4));
+  RT_TRY(tmp.alloc((void**)&ws.hist, (size_t)2 * passes * 256 * 4));
+  ws.lookback_words = sort_lookback_words(n, key_bits);
+  RT_TRY(tmp.alloc((void**)&ws.lookback, ws.lookback_words * 4));
+  RT_TRY(launch_histogram(keys, n, key_bits, ws.hist, s));
+  cudaEvent_t e0, e1;
+  RT_CUDA(cudaEventCreate(&e0));
+  RT_CUDA(cudaEventCreate(&e1));
+  RT_CUDA(cudaEventRecord(e0, s));
+  void* ko = nullptr;
+  uint32_t* vo = nullptr;
+  int rc = launch_sort(keys, n, key_bits, ws, /*iota_payload=*/false, &ko, &vo, s);
+  cudaEventRecord(e1, s);
+  cudaError_t e = cudaStreamSynchronize(s);
+  float t = 0.0f;
+  cudaEventElapsedTime(&t, e0, e1);
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  if (rc != 0) return rc;
+  RT_CUDA(e);
+  if (ms) *ms = t;
+  return RT_OK;
+}
+
+extern "C" const char* rt_version(void) { return "gpu_raytracer_b200 0.1.0 (sm_100a)"; }

@@ -86,6 +86,9 @@ int launch_export_topology(const Node* nodes, const uint32_t* parent, uint64_t n
                            uint32_t* right, uint32_t* parent_out, float* boxes,
                            const BvhHeader* header, cudaStream_t s);
 
+int launch_unpack_sorted(const SortedTri* stris, uint64_t n, uint32_t* idx, cudaStream_t s);
+int launch_widen_keys(const uint32_t* in, uint64_t n, uint64_t* out, cudaStream_t s);
+
 // ---- traversal (traverse.cu) -------------------------------------------------
 int launch_trace(const Node* nodes, const SortedTri* stris, uint64_t n_tris, const float4* rays,
                  uint64_t n_rays, uint32_t flags, float4* hits, unsigned long long* ray_counter,

@@ -1,0 +1,179 @@
+// refit.cu — A5: leaf boxes, triangle reorder and the atomic-flag bottom-up
+// AABB refit, plus the kernels that turn the traversal
+// layout back into the canonical arrays the parity tests compare.
+//
+// One thread per leaf.  It gathers its triangle through the sorted index,
+// stores it in traversal form {v0 | prim, e1, e2} at its sorted position, then
+// walks up: it writes the box it carries (and its own child id) into its slot
+// of the parent's 64-byte node — one full 32-byte sector — fences, and bumps
+// the parent's counter.  The first arriver stops; the second reads the
+// sibling's slot from L2 (ld.cg: the line may be stale in this SM's L1), unions
+// and continues.  Every node slot is written exactly once and read at most
+// once: ~96 B per internal node against the 112 B of the textbook layout.
+// The walker that leaves the root stores the scene box in the header.
+//
+// min/max use the total order on bit patterns, so boxes are exact and
+// independent of which thread arrives first.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace rt {
+namespace {
+
+__device__ __forceinline__ float4 ld_cg(const float4* p) {
+  float4 r;
+  asm volatile("ld.global.cg.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+               : "l"(p)
+               : "memory");
+  return r;
+}
+
+struct Box {
+  float lx, ly, lz, hx, hy, hz;
+};
+
+__device__ __forceinline__ void walk_up(Box b, int child_enc, uint32_t pword,
+                                        const uint32_t* __restrict__ parent,
+                                        uint32_t* __restrict__ flags, Node* __restrict__ nodes,
+                                        BvhHeader* __restrict__ header) {
+  while (pword != kNoParent) {
+    const uint32_t p = pword >> 1, slot = pword & 1u;
+    float4* np = reinterpret_cast<float4*>(nodes + p);
+    np[2 * slot] = make_float4(b.lx, b.ly, b.lz, __int_as_float(child_enc));
+    np[2 * slot + 1] = make_float4(b.hx, b.hy, b.hz, 0.0f);
+    __threadfence();
+    if (atomicAdd(flags + p, 1u) == 0u) return;  // first arriver: sibling not ready
+    __threadfence();
+    const float4 slo = ld_cg(np + 2 * (slot ^ 1u));
+    const float4 shi = ld_cg(np + 2 * (slot ^ 1u) + 1);
+    b.lx = omin(b.lx, slo.x); b.ly = omin(b.ly, slo.y); b.lz = omin(b.lz, slo.z);
+    b.hx = omax(b.hx, shi.x); b.hy = omax(b.hy, shi.y); b.hz = omax(b.hz, shi.z);
+    child_enc = (int)p;
+    pword = parent[p];
+  }
+  // left the root: b is the scene box
+  header->root_min[0] = b.lx; header->root_min[1] = b.ly; header->root_min[2] = b.lz;
+  header->root_max[0] = b.hx; header->root_max[1] = b.hy; header->root_max[2] = b.hz;
+}
+
+// FROM_INDEX: prim comes from sorted_idx (build); else from stris[j].v0p.w (refit_bvh)
+template <bool FROM_INDEX>
+__global__ void __launch_bounds__(256)
+refit_kernel(const float4* __restrict__ tris, const uint32_t* __restrict__ sorted_idx, uint32_t n,
+             const uint32_t* __restrict__ parent, uint32_t* __restrict__ flags,
+             Node* __restrict__ nodes, SortedTri* __restrict__ stris,
+             BvhHeader* __restrict__ header) {
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n) return;
+  uint32_t prim;
+  if (FROM_INDEX) prim = sorted_idx[j];
+  else prim = __float_as_uint(stris[j].v0p.w);
+  const float4 a = __ldg(tris + 3 * (uint64_t)prim), b = __ldg(tris + 3 * (uint64_t)prim + 1),
+               c = __ldg(tris + 3 * (uint64_t)prim + 2);
+  float4* st = reinterpret_cast<float4*>(stris + j);
+  st[0] = make_float4(a.x, a.y, a.z, __uint_as_float(prim));
+  st[1] = make_float4(b.x - a.x, b.y - a.y, b.z - a.z, 0.0f);
+  st[2] = make_float4(c.x - a.x, c.y - a.y, c.z - a.z, 0.0f);
+  Box bx;
+  bx.lx = omin(omin(a.x, b.x), c.x); bx.ly = omin(omin(a.y, b.y), c.y); bx.lz = omin(omin(a.z, b.z), c.z);
+  bx.hx = omax(omax(a.x, b.x), c.x); bx.hy = omax(omax(a.y, b.y), c.y); bx.hz = omax(omax(a.z, b.z), c.z);
+  walk_up(bx, ~(int)j, parent[(n - 1) + j], parent, flags, nodes, header);
+}
+
+// canonical arrays from the traversal layout (parity accessors T3/T4)
+__global__ void __launch_bounds__(256)
+export_kernel(const Node* __restrict__ nodes, const uint32_t* __restrict__ parent, uint32_t n,
+              uint32_t* __restrict__ left, uint32_t* __restrict__ right,
+              uint32_t* __restrict__ parent_out, float* __restrict__ boxes,
+              const BvhHeader* __restrict__ header) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t n_nodes = 2 * n - 1, leaf0 = n - 1;
+  if (i >= n_nodes) return;
+  const uint32_t pw = parent[i];
+  if (parent_out) parent_out[i] = (pw == kNoParent) ? kNoParent : (pw >> 1);
+  if (boxes) {
+    float* o = boxes + 6 * (uint64_t)i;
+    if (pw == kNoParent) {
+      for (int k = 0; k < 3; ++k) {
+        o[k] = header->root_min[k];
+        o[3 + k] = header->root_max[k];
+      }
+    } else {
+      const float4* np = reinterpret_cast<const float4*>(nodes + (pw >> 1)) + 2 * (pw & 1u);
+      float4 lo = np[0], hi = np[1];
+      o[0] = lo.x; o[1] = lo.y; o[2] = lo.z; o[3] = hi.x; o[4] = hi.y; o[5] = hi.z;
+    }
+  }
+  if (i < leaf0) {
+    const int c0 = __float_as_int(nodes[i].lo0.w), c1 = __float_as_int(nodes[i].lo1.w);
+    if (left) left[i] = (c0 < 0) ? (leaf0 + (uint32_t)(~c0)) : (uint32_t)c0;
+    if (right) right[i] = (c1 < 0) ? (leaf0 + (uint32_t)(~c1)) : (uint32_t)c1;
+  }
+}
+
+__global__ void unpack_sorted_kernel(const SortedTri* __restrict__ stris, uint32_t n,
+                                     uint32_t* __restrict__ idx) {
+  uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j < n) idx[j] = __float_as_uint(stris[j].v0p.w);
+}
+__global__ void widen_keys_kernel(const uint32_t* __restrict__ in, uint32_t n,
+                                  uint64_t* __restrict__ out) {
+  uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j < n) out[j] = in[j];
+}
+
+}  // namespace
+
+int launch_unpack_sorted(const SortedTri* stris, uint64_t n, uint32_t* idx, cudaStream_t s) {
+  if (n == 0) return 0;
+  unpack_sorted_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(stris, (uint32_t)n, idx);
+  RT_LAUNCHED();
+  return 0;
+}
+int launch_widen_keys(const uint32_t* in, uint64_t n, uint64_t* out, cudaStream_t s) {
+  if (n == 0) return 0;
+  widen_keys_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(in, (uint32_t)n, out);
+  RT_LAUNCHED();
+  return 0;
+}
+
+static int refit_common(bool from_index, const float4* tris, const uint32_t* sorted_idx, uint64_t n,
+                        const uint32_t* parent, uint32_t* flags, Node* nodes, SortedTri* stris,
+                        BvhHeader* header, cudaStream_t s) {
+  if (n == 0) return 0;
+  if (n > 1) RT_CUDA(cudaMemsetAsync(flags, 0, (size_t)(n - 1) * sizeof(uint32_t), s));
+  const unsigned blocks = (unsigned)((n + 255) / 256);
+  if (from_index)
+    refit_kernel<true><<<blocks, 256, 0, s>>>(tris, sorted_idx, (uint32_t)n, parent, flags, nodes,
+                                              stris, header);
+  else
+    refit_kernel<false><<<blocks, 256, 0, s>>>(tris, sorted_idx, (uint32_t)n, parent, flags, nodes,
+                                               stris, header);
+  RT_LAUNCHED();
+  return 0;
+}
+
+int launch_refit(const float4* tris, const uint32_t* sorted_idx, uint64_t n,
+                 const uint32_t* parent, uint32_t* flags, Node* nodes, SortedTri* stris,
+                 BvhHeader* header, cudaStream_t s) {
+  return refit_common(true, tris, sorted_idx, n, parent, flags, nodes, stris, header, s);
+}
+
+int launch_refit_update(const float4* tris, uint64_t n, const uint32_t* parent, uint32_t* flags,
+                        Node* nodes, SortedTri* stris, BvhHeader* header, cudaStream_t s) {
+  return refit_common(false, tris, nullptr, n, parent, flags, nodes, stris, header, s);
+}
+
+int launch_export_topology(const Node* nodes, const uint32_t* parent, uint64_t n, uint32_t* left,
+                           uint32_t* right, uint32_t* parent_out, float* boxes,
+                           const BvhHeader* header, cudaStream_t s) {
+  if (n == 0) return 0;
+  const uint64_t n_nodes = 2 * n - 1;
+  export_kernel<<<(unsigned)((n_nodes + 255) / 256), 256, 0, s>>>(
+      nodes, parent, (uint32_t)n, left, right, parent_out, boxes, header);
+  RT_LAUNCHED();
+  return 0;
+}
+
+}  // namespace rt

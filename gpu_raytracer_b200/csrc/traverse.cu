@@ -1,0 +1,177 @@
+// traverse.cu — A6/A7: persistent-thread while-while stack traversal with
+// Moeller-Trumbore intersection (Aila & Laine 2009).
+//
+// Launch: a fixed grid of resident warps (SM count x CTAs per SM); each warp
+// pulls 32 consecutive rays at a time with one atomicAdd by lane 0 (warp-level
+// ray fetch), so the grid never depends on the batch size and long rays do not
+// hold a whole CTA hostage.
+//
+// Per ray: the inner loop walks internal nodes — one 64-byte node fetch (4 x
+// LDG.128, two sectors) carries both children's boxes and ids; near child
+// first, far child pushed on a per-thread stack in local memory — until it
+// reaches a leaf; the second loop intersects leaves (one triangle each, stored
+// as v0|prim, e1, e2 = 48 B) and pops.  Box tests cull with tnear <= tfar*pad
+// (<=, so equal-t candidates in other subtrees are still visited) and the
+// acceptance rule breaks equal-t ties towards the smaller primitive index, so
+// the result does not depend on traversal order.
+//
+// Bound: L2/HBM latency and divergence, not streaming bandwidth; algorithmic
+// bytes/ray = 48 + 64 x nodes fetched + 48 x triangles tested.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace rt {
+namespace {
+
+constexpr int kStack = 96;  // >= 63 key bits + 32 tie-break bits of tree depth
+constexpr int kEmpty = (int)0x80000000;
+constexpr float kSlabPad = 1.0000004f;
+constexpr int kTraceThreads = 256;
+
+struct RayState {
+  float ox, oy, oz, tmin;
+  float dx, dy, dz;
+  float ix, iy, iz;
+  float best_t, bu, bv;
+  int best_prim;
+};
+
+__device__ __forceinline__ bool slab(const float4 lo, const float4 hi, const RayState& r,
+                                     float& tn) {
+  const float t0x = (lo.x - r.ox) * r.ix, t1x = (hi.x - r.ox) * r.ix;
+  const float t0y = (lo.y - r.oy) * r.iy, t1y = (hi.y - r.oy) * r.iy;
+  const float t0z = (lo.z - r.oz) * r.iz, t1z = (hi.z - r.oz) * r.iz;
+  tn = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), r.tmin));
+  float tf = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fminf(fmaxf(t0z, t1z), r.best_t));
+  tf = tf * kSlabPad;
+  return tn <= tf;
+}
+
+// returns true when the hit was accepted
+__device__ __forceinline__ bool intersect(const SortedTri* __restrict__ stris, uint32_t j,
+                                          RayState& r) {
+  const float4* tp = reinterpret_cast<const float4*>(stris + j);
+  const float4 v0 = __ldg(tp), e1 = __ldg(tp + 1), e2 = __ldg(tp + 2);
+  const float px = fmaf(r.dy, e2.z, -(r.dz * e2.y));
+  const float py = fmaf(r.dz, e2.x, -(r.dx * e2.z));
+  const float pz = fmaf(r.dx, e2.y, -(r.dy * e2.x));
+  const float det = fmaf(e1.x, px, fmaf(e1.y, py, e1.z * pz));
+  if (det == 0.0f) return false;
+  const float inv = 1.0f / det;
+  const float sx = r.ox - v0.x, sy = r.oy - v0.y, sz = r.oz - v0.z;
+  const float u = fmaf(sx, px, fmaf(sy, py, sz * pz)) * inv;
+  const float qx = fmaf(sy, e1.z, -(sz * e1.y));
+  const float qy = fmaf(sz, e1.x, -(sx * e1.z));
+  const float qz = fmaf(sx, e1.y, -(sy * e1.x));
+  const float v = fmaf(r.dx, qx, fmaf(r.dy, qy, r.dz * qz)) * inv;
+  const float t = fmaf(e2.x, qx, fmaf(e2.y, qy, e2.z * qz)) * inv;
+  if (!((u >= 0.0f) && (v >= 0.0f) && ((u + v) <= 1.0f))) return false;
+  const int prim = __float_as_int(v0.w);
+  const bool ok = (t > r.tmin) &&
+                  ((t < r.best_t) || (t == r.best_t && r.best_prim >= 0 && prim < r.best_prim));
+  if (ok) {
+    r.best_t = t;
+    r.bu = u;
+    r.bv = v;
+    r.best_prim = prim;
+  }
+  return ok;
+}
+
+template <bool ANY>
+__device__ __forceinline__ void trace_one(const Node* __restrict__ nodes,
+                                          const SortedTri* __restrict__ stris, int root,
+                                          RayState& r) {
+  int stack[kStack];
+  int sp = 0;
+  int node = root;
+  while (node != kEmpty) {
+    // ---- internal nodes until a leaf (or nothing) is at hand ----------------
+    while (node >= 0) {
+      const float4* np = reinterpret_cast<const float4*>(nodes + node);
+      const float4 lo0 = __ldg(np), hi0 = __ldg(np + 1), lo1 = __ldg(np + 2), hi1 = __ldg(np + 3);
+      float tn0, tn1;
+      const bool h0 = slab(lo0, hi0, r, tn0);
+      const bool h1 = slab(lo1, hi1, r, tn1);
+      const int c0 = __float_as_int(lo0.w), c1 = __float_as_int(lo1.w);
+      if (h0 && h1) {
+        const bool swap = tn1 < tn0;
+        node = swap ? c1 : c0;
+        stack[sp++] = swap ? c0 : c1;
+      } else if (h0) {
+        node = c0;
+      } else if (h1) {
+        node = c1;
+      } else {
+        node = (sp > 0) ? stack[--sp] : kEmpty;
+      }
+    }
+    // ---- leaves ----------------------------------------------------------------
+    while (node < 0 && node != kEmpty) {
+      const bool hit = intersect(stris, (uint32_t)(~node), r);
+      if (ANY && hit) return;
+      node = (sp > 0) ? stack[--sp] : kEmpty;
+    }
+  }
+}
+
+template <bool ANY>
+__global__ void __launch_bounds__(kTraceThreads)
+trace_kernel(const Node* __restrict__ nodes, const SortedTri* __restrict__ stris, uint32_t n_tris,
+             const float4* __restrict__ rays, unsigned long long n_rays,
+             float4* __restrict__ hits, unsigned long long* __restrict__ ray_counter) {
+  const int lane = threadIdx.x & 31;
+  const int root = (n_tris == 1) ? ~0 : 0;
+  const float inf = __int_as_float(0x7f800000);
+  while (true) {
+    unsigned long long base = 0;
+    if (lane == 0) base = atomicAdd(ray_counter, 32ull);
+    base = __shfl_sync(0xFFFFFFFFu, base, 0);
+    if (base >= n_rays) break;
+    const unsigned long long i = base + lane;
+    if (i < n_rays) {
+      const float4 ro = ld_stream(rays + 2 * i), rd = ld_stream(rays + 2 * i + 1);
+      RayState r;
+      r.ox = ro.x; r.oy = ro.y; r.oz = ro.z; r.tmin = ro.w;
+      r.dx = rd.x; r.dy = rd.y; r.dz = rd.z;
+      // 1/d clamped to +-FLT_MAX: 0 * FLT_MAX = 0 instead of 0 * inf = NaN when
+      // the origin lies on a box face and the direction component is zero
+      const float fmx = 3.402823466e+38f;
+      r.ix = fminf(fmaxf(1.0f / rd.x, -fmx), fmx);
+      r.iy = fminf(fmaxf(1.0f / rd.y, -fmx), fmx);
+      r.iz = fminf(fmaxf(1.0f / rd.z, -fmx), fmx);
+      r.best_t = rd.w; r.bu = 0.0f; r.bv = 0.0f; r.best_prim = -1;
+      if (n_tris != 0) trace_one<ANY>(nodes, stris, root, r);
+      float4 h;
+      if (r.best_prim < 0) h = make_float4(inf, 0.0f, 0.0f, __int_as_float(-1));
+      else if (ANY) h = make_float4(0.0f, 0.0f, 0.0f, __int_as_float(0x7FFFFFFF));
+      else h = make_float4(r.best_t, r.bu, r.bv, __int_as_float(r.best_prim));
+      st_stream(hits + i, h);
+    }
+    __syncwarp();
+  }
+}
+
+}  // namespace
+
+int launch_trace(const Node* nodes, const SortedTri* stris, uint64_t n_tris, const float4* rays,
+                 uint64_t n_rays, uint32_t flags, float4* hits, unsigned long long* ray_counter,
+                 cudaStream_t s) {
+  if (n_rays == 0) return 0;
+  RT_CUDA(cudaMemsetAsync(ray_counter, 0, sizeof(unsigned long long), s));
+  int bps = params().trace_blocks_per_sm;
+  if (bps <= 0) bps = 8;
+  uint64_t blocks = (uint64_t)num_sms() * bps;
+  const uint64_t need = (n_rays + kTraceThreads - 1) / kTraceThreads;
+  if (blocks > need) blocks = need;
+  if (flags & 1u)
+    trace_kernel<true><<<(unsigned)blocks, kTraceThreads, 0, s>>>(
+        nodes, stris, (uint32_t)n_tris, rays, n_rays, hits, ray_counter);
+  else
+    trace_kernel<false><<<(unsigned)blocks, kTraceThreads, 0, s>>>(
+        nodes, stris, (uint32_t)n_tris, rays, n_rays, hits, ray_counter);
+  RT_LAUNCHED();
+  return 0;
+}
+
+}  // namespace rt

@@ -1,0 +1,102 @@
+"""Multi-GPU sharding of ray batches.
+
+One process per GPU (torch.distributed).  Rays are independent, so the batch is
+cut into contiguous ranges, one per rank, with no collective on the data path;
+each rank generates (or receives) only its range, and ray i depends on (seed, i)
+alone, so results do not depend on the number of GPUs.  The BVH is either built
+redundantly on every rank or built on rank 0 and broadcast (one NCCL broadcast
+of nodes + triangles + header over NVLink); ``bench.py`` measures both.
+"""
+from __future__ import annotations
+
+from typing import Callable, Optional, Tuple
+
+import numpy as np
+
+
+def shard_range(n: int, rank: int, world: int, align: int = 32) -> Tuple[int, int]:
+    """(first, count) of rank's contiguous range of [0, n).
+
+    Ranges are cut at multiples of ``align`` rays (a warp's fetch granule) except
+    for the last one; they tile [0, n) exactly and differ by less than two granules."""
+    if world <= 0 or not (0 <= rank < world):
+        raise ValueError("bad rank/world")
+    units = (n + align - 1) // align
+    base, rem = divmod(units, world)
+    u0 = rank * base + min(rank, rem)
+    u1 = u0 + base + (1 if rank < rem else 0)
+    first = min(u0 * align, n)
+    last = min(u1 * align, n)
+    return first, last - first
+
+
+class _DevBuf:
+    """Exposes a raw device pointer to torch through __cuda_array_interface__."""
+
+    def __init__(self, ptr: int, nbytes: int):
+        self.__cuda_array_interface__ = {
+            "shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 3, "strides": None}
+
+
+def _as_tensor(ptr: int, nbytes: int):
+    import torch
+    return torch.as_tensor(_DevBuf(ptr, nbytes), device="cuda")
+
+
+def broadcast_bvh(bvh, src: int = 0, group=None):
+    """Broadcasts a built BVH from ``src`` to every rank; returns the local handle.
+
+    ``bvh`` is the built handle on ``src`` and ignored (may be None) elsewhere."""
+    import torch
+    import torch.distributed as dist
+    from .api import Bvh
+
+    rank = dist.get_rank(group)
+    meta = torch.zeros(2, dtype=torch.int64, device="cuda")
+    if rank == src:
+        info = bvh.info()
+        meta[0], meta[1] = int(info.n_tris), int(info.key_bits)
+    dist.broadcast(meta, src=src, group=group)
+    n_tris, key_bits = int(meta[0].item()), int(meta[1].item())
+    if rank != src:
+        bvh = Bvh.alloc_empty(n_tris, key_bits)
+    for ptr, nbytes in bvh.device_buffers():
+        if nbytes:
+            dist.broadcast(_as_tensor(ptr, nbytes), src=src, group=group)
+    torch.cuda.synchronize()
+    if rank != src:
+        bvh.commit()
+    return bvh
+
+
+def trace_sharded(trace_fn: Callable, make_rays: Callable, n_rays: int, rank: int, world: int,
+                  batch: Optional[int] = None):
+    """Traces this rank's range of a global batch of ``n_rays`` rays.
+
+    make_rays(first, count) returns the rays of the global range; trace_fn(rays)
+    returns their hits.  Yields (first, count, hits) per batch so the caller
+    decides whether hits stay on the device, go to the host or are reduced."""
+    first, count = shard_range(n_rays, rank, world)
+    batch = batch or count or 1
+    done = 0
+    while done < count:
+        c = min(batch, count - done)
+        rays = make_rays(first + done, c)
+        yield first + done, c, trace_fn(rays)
+        done += c
+
+
+def gather_hits(local_hits: np.ndarray, n_rays: int, rank: int, world: int, group=None) -> np.ndarray:
+    """All ranks' hit ranges concatenated in ray order (host arrays; used by the
+    T6 test: concatenated shard outputs == single-GPU output, byte for byte)."""
+    import torch
+    import torch.distributed as dist
+
+    counts = [shard_range(n_rays, r, world)[1] for r in range(world)]
+    mx = max(counts) if counts else 0
+    pad = np.zeros((mx, 4), dtype=np.float32)
+    pad[:local_hits.shape[0]] = local_hits
+    mine = torch.from_numpy(pad)
+    outs = [torch.empty_like(mine) for _ in range(world)]
+    dist.all_gather(outs, mine, group=group)
+    return np.concatenate([outs[r].numpy()[:counts[r]] for r in range(world)], axis=0)

@@ -40,6 +40,12 @@
 extern "C" {
 #endif
 
+#if defined(__GNUC__)
+#define RT_API __attribute__((visibility("default")))
+#else
+#define RT_API
+#endif
+
 #define RT_OK 0
 #define RT_ERR_INVALID (-1)   /* bad argument */
 #define RT_ERR_CUDA (-2)      /* CUDA runtime error, see bvh_last_error() */
@@ -100,88 +106,88 @@ enum {
 /* Builds an LBVH over n_tris triangles.  tris: [host|device] n_tris x 12
  * floats; the caller keeps ownership, the handle holds its own reordered copy.
  * opts may be NULL.  n_tris == 0 gives a valid empty handle (every ray misses). */
-int build_bvh(const float* tris, uint64_t n_tris, const rt_build_opts* opts, rt_bvh** out);
+RT_API int build_bvh(const float* tris, uint64_t n_tris, const rt_build_opts* opts, rt_bvh** out);
 
 /* Traces n_rays rays.  rays: [host|device] n_rays x 8 floats; hits:
  * [host|device] n_rays x 4 floats.  Safe to call concurrently on one handle. */
-int trace_rays(const rt_bvh* h, const float* rays, uint64_t n_rays, uint32_t flags, float* hits);
+RT_API int trace_rays(const rt_bvh* h, const float* rays, uint64_t n_rays, uint32_t flags, float* hits);
 
 /* Frees every device allocation of the handle.  NULL is a no-op. */
-void free_bvh(rt_bvh* h);
+RT_API void free_bvh(rt_bvh* h);
 
 /* Thread-local message of the last failing call ("" if none). */
-const char* bvh_last_error(void);
+RT_API const char* bvh_last_error(void);
 
 /* ---- stream variant ------------------------------------------------------ */
 
 /* Device pointers only; enqueues on stream (cudaStream_t) and returns. */
-int trace_rays_async(const rt_bvh* h, const float* rays, uint64_t n_rays, uint32_t flags,
+RT_API int trace_rays_async(const rt_bvh* h, const float* rays, uint64_t n_rays, uint32_t flags,
                      float* hits, void* stream);
 
 /* ---- accessors used by the parity tests (T2-T4) -------------------------- */
 
-int bvh_info(const rt_bvh* h, rt_bvh_info* out);
+RT_API int bvh_info(const rt_bvh* h, rt_bvh_info* out);
 /* keys: n u64 (needs RT_BUILD_KEEP_KEYS), prim_idx: n u32; host, may be NULL */
-int bvh_read_sorted(const rt_bvh* h, uint64_t* keys, uint32_t* prim_idx);
+RT_API int bvh_read_sorted(const rt_bvh* h, uint64_t* keys, uint32_t* prim_idx);
 /* canonical node ids: internal i in [0,n-1), leaf j at n-1+j; left/right: n-1
  * u32 each, parent: 2n-1 u32 (0xFFFFFFFF for the root); host, may be NULL */
-int bvh_read_topology(const rt_bvh* h, uint32_t* left, uint32_t* right, uint32_t* parent);
+RT_API int bvh_read_topology(const rt_bvh* h, uint32_t* left, uint32_t* right, uint32_t* parent);
 /* boxes: (2n-1) x 6 floats min.xyz max.xyz in canonical node order; host */
-int bvh_read_boxes(const rt_bvh* h, float* boxes);
+RT_API int bvh_read_boxes(const rt_bvh* h, float* boxes);
 /* ms: RT_STAGE_COUNT floats (needs RT_BUILD_TIMINGS) */
-int bvh_build_times(const rt_bvh* h, float* ms);
+RT_API int bvh_build_times(const rt_bvh* h, float* ms);
 
 /* ---- refit: same topology, moved vertices -------------- */
-int refit_bvh(rt_bvh* h, const float* tris);
+RT_API int refit_bvh(rt_bvh* h, const float* tris);
 
 /* ---- multi-GPU helpers ----------------------------------- */
 
 /* Device buffers that make up a built BVH, for a broadcast between ranks:
  * ptrs[0]/bytes[0] = node array, ptrs[1]/bytes[1] = reordered triangles,
  * ptrs[2]/bytes[2] = 16-float header (root box, counts). */
-int bvh_device_buffers(const rt_bvh* h, void** ptrs, uint64_t* bytes);
+RT_API int bvh_device_buffers(const rt_bvh* h, void** ptrs, uint64_t* bytes);
 /* Allocates a handle with uninitialised buffers of the right size for n_tris,
  * to be filled through bvh_device_buffers (receiver side of the broadcast). */
-int bvh_alloc_empty(uint64_t n_tris, uint32_t key_bits, rt_bvh** out);
+RT_API int bvh_alloc_empty(uint64_t n_tris, uint32_t key_bits, rt_bvh** out);
 /* Re-reads the header buffer after it was filled by a broadcast. */
-int bvh_commit(rt_bvh* h);
+RT_API int bvh_commit(rt_bvh* h);
 
 /* ---- on-device generators (A8 and the §8d synthetic scenes) -------------- */
 
-uint64_t rt_scene_size(int kind, uint64_t p0, uint64_t p1);
+RT_API uint64_t rt_scene_size(int kind, uint64_t p0, uint64_t p1);
 /* triangles [first, first+count) of the scene; out: [host|device] count x 12 */
-int rt_gen_scene(int kind, uint64_t p0, uint64_t p1, uint64_t seed, uint64_t first,
+RT_API int rt_gen_scene(int kind, uint64_t p0, uint64_t p1, uint64_t seed, uint64_t first,
                  uint64_t count, float* out);
 /* cam: host, 12 floats eye.xyz corner.xyz du.xyz dv.xyz; row-major pixel order */
-int rt_gen_primary_rays(const float* cam, uint32_t width, uint32_t height, uint64_t first,
+RT_API int rt_gen_primary_rays(const float* cam, uint32_t width, uint32_t height, uint64_t first,
                         uint64_t count, float* out);
 /* box: host, 6 floats; ray i depends on (seed, first + i) only */
-int rt_gen_random_rays(const float* box, uint64_t seed, uint64_t first, uint64_t count, float* out);
+RT_API int rt_gen_random_rays(const float* box, uint64_t seed, uint64_t first, uint64_t count, float* out);
 /* spp rays per primary ray from its hit point; tris in ORIGINAL order; all
  * pointers [host|device] but of one kind; out: n x spp x 8 floats */
-int rt_gen_ao_rays(const float* tris, const float* rays, const float* hits, uint64_t n,
+RT_API int rt_gen_ao_rays(const float* tris, const float* rays, const float* hits, uint64_t n,
                    uint32_t spp, uint64_t seed, float radius, float* out);
 
 /* ---- shading and image output --------------------------- */
 
 /* rgb: [host|device] n x 3 floats.  Lambert-ish: |n.d| * (1 - occluded/spp);
  * ao_hits may be NULL (spp = 0).  Misses are black. */
-int rt_shade(const float* tris, const float* rays, const float* hits, const float* ao_hits,
+RT_API int rt_shade(const float* tris, const float* rays, const float* hits, const float* ao_hits,
              uint64_t n, uint32_t spp, float* rgb);
 
 /* ---- runtime --------------------------------------------------------------*/
 
-int rt_device_count(void);
+RT_API int rt_device_count(void);
 /* number of CUDA kernels this library has launched in this process */
-uint64_t rt_kernel_launches(void);
+RT_API uint64_t rt_kernel_launches(void);
 /* tuning knobs for experiments: name = "sort.variant", "trace.blocks_per_sm" … */
-int rt_set_param(const char* name, int64_t value);
+RT_API int rt_set_param(const char* name, int64_t value);
 /* sorts n (key,value) pairs already on the device with the build's radix sort;
  * used by tests and the sort micro-benchmark.  key_bits 30 -> u32 keys, 63 ->
  * u64 keys.  keys/vals are overwritten with the sorted result. ms (may be
  * NULL) receives the device time of the sort alone. */
-int rt_sort_pairs(void* keys, uint32_t* vals, uint64_t n, uint32_t key_bits, float* ms);
-const char* rt_version(void);
+RT_API int rt_sort_pairs(void* keys, uint32_t* vals, uint64_t n, uint32_t key_bits, float* ms);
+RT_API const char* rt_version(void);
 
 #ifdef __cplusplus
 }

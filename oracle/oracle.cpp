@@ -554,7 +554,11 @@ Hit trace_one(const Bvh& b, const Ray& r, uint32_t flags, uint64_t& nodes, uint6
   float best_t = r.tmax;
   int32_t best_prim = -1;
   float bu = 0, bv = 0;
-  const float idir[3] = {1.0f / r.d[0], 1.0f / r.d[1], 1.0f / r.d[2]};
+  // 1/d clamped to +-FLT_MAX: a zero direction component then gives 0 * FLT_MAX
+  // = 0 (not 0 * inf = NaN) for a ray origin lying on a box face
+  const float fmx = std::numeric_limits<float>::max();
+  const float idir[3] = {nmin(nmax(1.0f / r.d[0], -fmx), fmx), nmin(nmax(1.0f / r.d[1], -fmx), fmx),
+                         nmin(nmax(1.0f / r.d[2], -fmx), fmx)};
   const uint32_t leaf0 = (uint32_t)(n - 1);
   uint32_t stack[128];
   int sp = 0;
