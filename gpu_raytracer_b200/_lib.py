@@ -38,6 +38,7 @@ SIGNATURES = {
     "free_bvh": (None, [_vp]),
     "bvh_last_error": (C.c_char_p, []),
     "trace_rays_async": (_i32, [_vp, _vp, _u64, _u32, _vp, _vp]),
+    "trace_rays_stats": (_i32, [_vp, _vp, _u64, _u32, _vp, _vp]),
     "bvh_info": (_i32, [_vp, C.POINTER(BvhInfo)]),
     "bvh_read_sorted": (_i32, [_vp, _vp, _vp]),
     "bvh_read_topology": (_i32, [_vp, _vp, _vp, _vp]),

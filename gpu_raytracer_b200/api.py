@@ -157,6 +157,14 @@ class Bvh:
         L.check(L.lib().trace_rays_async(self._h, _ptr(rays), n, flags, _ptr(out), stream or None))
         return out
 
+    def trace_stats(self, rays, flags: int = L.RT_TRACE_CLOSEST):
+        """(hits, nodes_fetched, triangles_tested) for device rays; measurement only."""
+        n = _rows(rays, 8)
+        out = _empty_like_kind(rays, (n, 4), None)
+        cnt = (C.c_uint64 * 2)()
+        L.check(L.lib().trace_rays_stats(self._h, _ptr(rays), n, flags, _ptr(out), cnt))
+        return out, int(cnt[0]), int(cnt[1])
+
     def refit(self, tris) -> None:
         L.check(L.lib().refit_bvh(self._h, _ptr(tris)))
 

@@ -361,7 +361,7 @@ namespace {
 // per-thread, per-device resources of the host-buffer pipeline: three streams
 // (H2D, compute, D2H), two staging slots, events.  Created on first use.
 struct Pipeline {
-  static constexpr uint64_t kChunk = 1ull << 20;  // rays per chunk: 32 MiB in, 16 MiB out
+  static constexpr uint64_t kChunk = 1ull << 18;  // rays per chunk: 8 MiB in, 4 MiB out
   int device = -1;
   cudaStream_t s_in = nullptr, s_run = nullptr, s_out = nullptr;
   float4* rays[2] = {nullptr, nullptr};
@@ -473,6 +473,33 @@ extern "C" int trace_rays(const rt_bvh* h, const float* rays, uint64_t n_rays, u
     return RT_OK;
   }
   return trace_staged(h, rays, rays_dev, n_rays, flags, hits, hits_dev);
+}
+
+extern "C" int trace_rays_stats(const rt_bvh* h, const float* rays, uint64_t n_rays, uint32_t flags,
+                                float* hits, uint64_t* counters) {
+  if (!h || !rays || !hits || !counters)
+    return fail(RT_ERR_INVALID, "trace_rays_stats: NULL argument");
+  if (flags > 1u) return fail(RT_ERR_INVALID, "trace_rays_stats: unknown flags 0x%x", flags);
+  counters[0] = counters[1] = 0;
+  if (n_rays == 0) return RT_OK;
+  DeviceScope scope;
+  RT_TRY(scope.enter(h->device));
+  if (!classify(rays, nullptr) || !classify(hits, nullptr))
+    return fail(RT_ERR_INVALID, "trace_rays_stats: rays and hits must be device memory");
+  cudaStream_t s = 0;
+  TempPool tmp(s);
+  void* d = nullptr;
+  RT_TRY(tmp.alloc(&d, 3 * sizeof(unsigned long long)));
+  RT_CUDA(cudaMemsetAsync(d, 0, 3 * sizeof(unsigned long long), s));
+  unsigned long long* dc = (unsigned long long*)d;
+  RT_TRY(launch_trace(h->nodes, h->stris, h->n, reinterpret_cast<const float4*>(rays), n_rays,
+                      flags, reinterpret_cast<float4*>(hits), dc + 2, s, dc));
+  unsigned long long host[2] = {0, 0};
+  RT_CUDA(cudaMemcpyAsync(host, dc, sizeof(host), cudaMemcpyDeviceToHost, s));
+  RT_CUDA(cudaStreamSynchronize(s));
+  counters[0] = host[0];
+  counters[1] = host[1];
+  return RT_OK;
 }
 
 // ===========================================================================

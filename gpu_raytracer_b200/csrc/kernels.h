@@ -92,7 +92,7 @@ int launch_widen_keys(const uint32_t* in, uint64_t n, uint64_t* out, cudaStream_
 // ---- traversal (traverse.cu) -------------------------------------------------
 int launch_trace(const Node* nodes, const SortedTri* stris, uint64_t n_tris, const float4* rays,
                  uint64_t n_rays, uint32_t flags, float4* hits, unsigned long long* ray_counter,
-                 cudaStream_t s);
+                 cudaStream_t s, unsigned long long* stats = nullptr);
 
 // tuning knobs (rt_set_param)
 struct Params {

@@ -275,16 +275,16 @@ int dispatch_pass(int variant, const KeyT* kin, KeyT* kout, const uint32_t* vin,
   switch (variant) {
     default:
     case 0:
-      return launch_pass<KeyT, 512, k64 ? 10 : 15, 2, true>(kin, kout, vin, vout, base, lookback,
+      return launch_pass<KeyT, 512, k64 ? 10 : 15, 2, false>(kin, kout, vin, vout, base, lookback,
                                                             counter, n, shift, iota, s);
     case 1:
-      return launch_pass<KeyT, 384, k64 ? 13 : 18, 2, true>(kin, kout, vin, vout, base, lookback,
+      return launch_pass<KeyT, 384, k64 ? 13 : 18, 2, false>(kin, kout, vin, vout, base, lookback,
                                                             counter, n, shift, iota, s);
     case 2:
-      return launch_pass<KeyT, 256, k64 ? 16 : 23, 3, true>(kin, kout, vin, vout, base, lookback,
+      return launch_pass<KeyT, 256, k64 ? 16 : 23, 3, false>(kin, kout, vin, vout, base, lookback,
                                                             counter, n, shift, iota, s);
     case 3:
-      return launch_pass<KeyT, 512, k64 ? 10 : 15, 2, false>(kin, kout, vin, vout, base, lookback,
+      return launch_pass<KeyT, 512, k64 ? 10 : 15, 2, true>(kin, kout, vin, vout, base, lookback,
                                                              counter, n, shift, iota, s);
   }
 }

@@ -78,16 +78,17 @@ __device__ __forceinline__ bool intersect(const SortedTri* __restrict__ stris, u
   return ok;
 }
 
-template <bool ANY>
+template <bool ANY, bool STATS>
 __device__ __forceinline__ void trace_one(const Node* __restrict__ nodes,
                                           const SortedTri* __restrict__ stris, int root,
-                                          RayState& r) {
+                                          RayState& r, uint32_t& n_nodes, uint32_t& n_tests) {
   int stack[kStack];
   int sp = 0;
   int node = root;
   while (node != kEmpty) {
     // ---- internal nodes until a leaf (or nothing) is at hand ----------------
     while (node >= 0) {
+      if (STATS) ++n_nodes;
       const float4* np = reinterpret_cast<const float4*>(nodes + node);
       const float4 lo0 = __ldg(np), hi0 = __ldg(np + 1), lo1 = __ldg(np + 2), hi1 = __ldg(np + 3);
       float tn0, tn1;
@@ -108,6 +109,7 @@ __device__ __forceinline__ void trace_one(const Node* __restrict__ nodes,
     }
     // ---- leaves ----------------------------------------------------------------
     while (node < 0 && node != kEmpty) {
+      if (STATS) ++n_tests;
       const bool hit = intersect(stris, (uint32_t)(~node), r);
       if (ANY && hit) return;
       node = (sp > 0) ? stack[--sp] : kEmpty;
@@ -115,11 +117,15 @@ __device__ __forceinline__ void trace_one(const Node* __restrict__ nodes,
   }
 }
 
-template <bool ANY>
+// STATS: also counts node fetches and triangle tests into stats[0..1] (the
+// algorithmic-bytes figure of the roofline; never used on the timed path)
+template <bool ANY, bool STATS>
 __global__ void __launch_bounds__(kTraceThreads)
 trace_kernel(const Node* __restrict__ nodes, const SortedTri* __restrict__ stris, uint32_t n_tris,
              const float4* __restrict__ rays, unsigned long long n_rays,
-             float4* __restrict__ hits, unsigned long long* __restrict__ ray_counter) {
+             float4* __restrict__ hits, unsigned long long* __restrict__ ray_counter,
+             unsigned long long* __restrict__ stats) {
+  uint32_t n_nodes = 0, n_tests = 0;
   const int lane = threadIdx.x & 31;
   const int root = (n_tris == 1) ? ~0 : 0;
   const float inf = __int_as_float(0x7f800000);
@@ -141,7 +147,7 @@ trace_kernel(const Node* __restrict__ nodes, const SortedTri* __restrict__ stris
       r.iy = fminf(fmaxf(1.0f / rd.y, -fmx), fmx);
       r.iz = fminf(fmaxf(1.0f / rd.z, -fmx), fmx);
       r.best_t = rd.w; r.bu = 0.0f; r.bv = 0.0f; r.best_prim = -1;
-      if (n_tris != 0) trace_one<ANY>(nodes, stris, root, r);
+      if (n_tris != 0) trace_one<ANY, STATS>(nodes, stris, root, r, n_nodes, n_tests);
       float4 h;
       if (r.best_prim < 0) h = make_float4(inf, 0.0f, 0.0f, __int_as_float(-1));
       else if (ANY) h = make_float4(0.0f, 0.0f, 0.0f, __int_as_float(0x7FFFFFFF));
@@ -150,13 +156,21 @@ trace_kernel(const Node* __restrict__ nodes, const SortedTri* __restrict__ stris
     }
     __syncwarp();
   }
+  if (STATS) {
+    n_nodes = __reduce_add_sync(0xFFFFFFFFu, n_nodes);
+    n_tests = __reduce_add_sync(0xFFFFFFFFu, n_tests);
+    if (lane == 0) {
+      atomicAdd(stats, (unsigned long long)n_nodes);
+      atomicAdd(stats + 1, (unsigned long long)n_tests);
+    }
+  }
 }
 
 }  // namespace
 
 int launch_trace(const Node* nodes, const SortedTri* stris, uint64_t n_tris, const float4* rays,
                  uint64_t n_rays, uint32_t flags, float4* hits, unsigned long long* ray_counter,
-                 cudaStream_t s) {
+                 cudaStream_t s, unsigned long long* stats) {
   if (n_rays == 0) return 0;
   RT_CUDA(cudaMemsetAsync(ray_counter, 0, sizeof(unsigned long long), s));
   int bps = params().trace_blocks_per_sm;
@@ -164,12 +178,18 @@ int launch_trace(const Node* nodes, const SortedTri* stris, uint64_t n_tris, con
   uint64_t blocks = (uint64_t)num_sms() * bps;
   const uint64_t need = (n_rays + kTraceThreads - 1) / kTraceThreads;
   if (blocks > need) blocks = need;
-  if (flags & 1u)
-    trace_kernel<true><<<(unsigned)blocks, kTraceThreads, 0, s>>>(
-        nodes, stris, (uint32_t)n_tris, rays, n_rays, hits, ray_counter);
-  else
-    trace_kernel<false><<<(unsigned)blocks, kTraceThreads, 0, s>>>(
-        nodes, stris, (uint32_t)n_tris, rays, n_rays, hits, ray_counter);
+  const bool any = (flags & 1u) != 0;
+#define RT_TRACE_LAUNCH(A, S)                                          \
+  trace_kernel<A, S><<<(unsigned)blocks, kTraceThreads, 0, s>>>(       \
+      nodes, stris, (uint32_t)n_tris, rays, n_rays, hits, ray_counter, stats)
+  if (stats) {
+    if (any) RT_TRACE_LAUNCH(true, true);
+    else RT_TRACE_LAUNCH(false, true);
+  } else {
+    if (any) RT_TRACE_LAUNCH(true, false);
+    else RT_TRACE_LAUNCH(false, false);
+  }
+#undef RT_TRACE_LAUNCH
   RT_LAUNCHED();
   return 0;
 }

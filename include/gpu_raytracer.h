@@ -124,6 +124,13 @@ RT_API const char* bvh_last_error(void);
 RT_API int trace_rays_async(const rt_bvh* h, const float* rays, uint64_t n_rays, uint32_t flags,
                      float* hits, void* stream);
 
+/* Like trace_rays on device buffers, and also counts the work done: counters[0]
+ * = internal nodes fetched (64 B each), counters[1] = triangles tested (48 B
+ * each); these give the algorithmic bytes per ray of SURVEY.md §8(d).  Slower
+ * than trace_rays; for measurement only.  counters: host, 2 x u64. */
+RT_API int trace_rays_stats(const rt_bvh* h, const float* rays, uint64_t n_rays, uint32_t flags,
+                            float* hits, uint64_t* counters);
+
 /* ---- accessors used by the parity tests (T2-T4) -------------------------- */
 
 RT_API int bvh_info(const rt_bvh* h, rt_bvh_info* out);

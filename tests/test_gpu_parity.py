@@ -161,7 +161,7 @@ def test_ao_pipeline(rt, oracle):
     tris = oracle.gen_scene(oracle.SCENE_SPHEREFLAKE, 2, 6)
     v = tris.reshape(-1, 4)[:, :3]
     box = np.concatenate([v.min(0), v.max(0)])
-    cam = rt.camera.frame_box(box, 192, 128)
+    cam = rt.camera.frame_box(box, 192, 128, fill=1.8)
     ob = oracle.OracleBvh(tris)
     rays = oracle.gen_primary_rays(cam, 192, 128)
     hits = ob.trace(rays)
@@ -177,6 +177,10 @@ def test_ao_pipeline(rt, oracle):
         assert np.array_equal(bits(g_ao.cpu().numpy()), bits(ao))
         g_occ = gb.trace(g_ao, 1)
         assert np.array_equal(bits(g_occ.cpu().numpy()), bits(occ))
+        # the instrumented kernel returns the same hits and the oracle's counters
+        s_hits, nn, nt = gb.trace_stats(g_rays)
+        assert np.array_equal(bits(s_hits.cpu().numpy()), bits(hits))
+        assert (nn, nt) == ob.trace(rays, counters=True)[1]
         rgb = rt.shade(d_tris, g_rays, g_hits, g_occ, 4).cpu().numpy()
         assert rgb.shape == (192 * 128, 3) and np.isfinite(rgb).all()
         assert rgb.min() >= 0 and rgb.max() <= 1.0 + 1e-6 and rgb.max() > 0.5
