@@ -1,0 +1,63 @@
+"""Generates tests/golden/*.npz from the CPU oracle.
+
+The reference holds no golden vectors, so these fixtures pin the
+oracle's *own* outputs at the commit that produced them: a later change to the
+oracle or to the kernels that alters any byte fails tests/test_golden.py.  They
+travel to the GPU box, where the CUDA path is compared with them directly.
+
+    python tests/golden/make_golden.py        # rewrites the fixtures
+"""
+import hashlib
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
+import oracle as O  # noqa: E402
+from gpu_raytracer_b200 import camera  # noqa: E402
+
+
+def digest(a):
+    return np.frombuffer(hashlib.sha256(np.ascontiguousarray(a).tobytes()).digest(), dtype=np.uint8)
+
+
+def build_fixture(name, tris, key_bits, rays, extra=None):
+    b = O.OracleBvh(tris, key_bits)
+    hits = b.trace(rays)
+    occ = b.trace(rays, O.TRACE_ANY)
+    out = dict(key_bits=np.int32(key_bits), n=np.int64(b.n), bounds=b.bounds,
+               tris_sha=digest(tris), keys=b.keys, idx=b.idx, left=b.left, right=b.right,
+               parent=b.parent, boxes_sha=digest(b.boxes), boxes_head=b.boxes[:64],
+               rays_sha=digest(rays), hits=hits, any_prim=O.hit_prims(occ))
+    out.update(extra or {})
+    np.savez_compressed(os.path.join(HERE, name + ".npz"), **out)
+    print(name, b.n, "tris", rays.shape[0], "rays", int((O.hit_prims(hits) >= 0).sum()), "hits")
+
+
+def main():
+    # config 1, reduced image: Cornell box, 96 x 96 primary rays
+    cam = camera.cornell_camera(96, 96)
+    tris = O.gen_scene(O.SCENE_CORNELL)
+    build_fixture("cornell_96", tris, 30, O.gen_primary_rays(cam, 96, 96), dict(cam=cam))
+    # soup, both key widths, random rays
+    tris = O.gen_scene(O.SCENE_SOUP, 3000, 0, seed=1)
+    v = tris.reshape(-1, 4)[:, :3]
+    box = np.concatenate([v.min(0), v.max(0)])
+    rays = O.gen_random_rays(box, 4, 0, 4096)
+    build_fixture("soup3000_k30", tris, 30, rays, dict(box=box))
+    build_fixture("soup3000_k63", tris, 63, rays, dict(box=box))
+    # sphereflake and terrain slices
+    tris = O.gen_scene(O.SCENE_SPHEREFLAKE, 2, 3)
+    v = tris.reshape(-1, 4)[:, :3]
+    box = np.concatenate([v.min(0), v.max(0)])
+    build_fixture("flake_d2_m3", tris, 30, O.gen_random_rays(box, 4, 0, 4096), dict(box=box))
+    tris = O.gen_scene(O.SCENE_TERRAIN, 48, 16, seed=3)
+    v = tris.reshape(-1, 4)[:, :3]
+    box = np.concatenate([v.min(0), v.max(0)])
+    build_fixture("terrain_48", tris, 63, O.gen_random_rays(box, 4, 0, 4096), dict(box=box))
+
+
+if __name__ == "__main__":
+    main()
