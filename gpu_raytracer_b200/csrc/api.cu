@@ -788,6 +788,9 @@ extern "C" int rt_set_param(const char* name, int64_t value) {
   if (!strcmp(name, "sort.variant")) p.sort_variant = (int)value;
   else if (!strcmp(name, "trace.blocks_per_sm")) p.trace_blocks_per_sm = (int)value;
   else if (!strcmp(name, "trace.variant")) p.trace_variant = (int)value;
+  else if (!strcmp(name, "trace.chunk")) p.trace_chunk = (int)value;
+  else if (!strcmp(name, "trace.refill_min")) p.trace_refill_min = (int)value;
+  else if (!strcmp(name, "trace.leaf_min")) p.trace_leaf_min = (int)value;
   else return fail(RT_ERR_INVALID, "rt_set_param: unknown parameter '%s'", name);
   return RT_OK;
 }

@@ -98,7 +98,8 @@ int launch_trace(const Node* nodes, const SortedTri* stris, uint64_t n_tris, con
 struct Params {
   int sort_variant = 0;
   int trace_blocks_per_sm = 0;  // 0 = kernel default
-  int trace_variant = 0;
+  int trace_variant = 1;        // 0 = plain while-while, 1 = dynamic fetch + voted leaf loop
+  int trace_chunk = 0, trace_refill_min = 0, trace_leaf_min = 0;  // 0 = defaults
   int num_sms = 0;              // filled at first use
 };
 Params& params();
