@@ -105,6 +105,18 @@ int classify(const void* p, int* dev) {
   return 0;
 }
 
+// Pinned (page-locked, mapped) host memory can be read and written by kernels
+// directly over PCIe.  Returns the device-side alias, or nullptr.
+void* mapped_alias(const void* p) {
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+    cudaGetLastError();
+    return nullptr;
+  }
+  if (a.type == cudaMemoryTypeHost && a.devicePointer != nullptr) return a.devicePointer;
+  return nullptr;
+}
+
 struct DeviceScope {
   int prev = -1;
   bool switched = false;
@@ -361,7 +373,7 @@ namespace {
 // per-thread, per-device resources of the host-buffer pipeline: three streams
 // (H2D, compute, D2H), two staging slots, events.  Created on first use.
 struct Pipeline {
-  static constexpr uint64_t kChunk = 1ull << 18;  // rays per chunk: 8 MiB in, 4 MiB out
+  static constexpr uint64_t kChunk = 1ull << 20;  // staging slot capacity in rays (32 MiB in, 16 MiB out)
   int device = -1;
   cudaStream_t s_in = nullptr, s_run = nullptr, s_out = nullptr;
   float4* rays[2] = {nullptr, nullptr};
@@ -405,11 +417,13 @@ int trace_staged(const rt_bvh* h, const float* rays, bool rays_dev, uint64_t n_r
   RT_TRY(p.init(h->device));
   // the legacy default stream may still be producing the inputs
   RT_CUDA(cudaStreamSynchronize(0));
-  const uint64_t chunks = (n_rays + Pipeline::kChunk - 1) / Pipeline::kChunk;
+  uint64_t chunk = params().stage_chunk > 0 ? (uint64_t)params().stage_chunk : (1ull << 20);
+  if (chunk > Pipeline::kChunk) chunk = Pipeline::kChunk;
+  const uint64_t chunks = (n_rays + chunk - 1) / chunk;
   for (uint64_t c = 0; c < chunks; ++c) {
     const int b = (int)(c & 1);
-    const uint64_t first = c * Pipeline::kChunk;
-    const uint64_t cnt = (n_rays - first < Pipeline::kChunk) ? (n_rays - first) : Pipeline::kChunk;
+    const uint64_t first = c * chunk;
+    const uint64_t cnt = (n_rays - first < chunk) ? (n_rays - first) : chunk;
     const float4* rsrc;
     if (rays_dev) {
       rsrc = reinterpret_cast<const float4*>(rays) + 2 * first;
@@ -466,12 +480,23 @@ extern "C" int trace_rays(const rt_bvh* h, const float* rays, uint64_t n_rays, u
   const bool rays_dev = classify(rays, &d0) != 0, hits_dev = classify(hits, &d1) != 0;
   if ((rays_dev && d0 != h->device) || (hits_dev && d1 != h->device))
     return fail(RT_ERR_INVALID, "trace_rays: buffers are not on the handle's device %d", h->device);
-  if (rays_dev && hits_dev) {
-    RT_TRY(trace_device(h, reinterpret_cast<const float4*>(rays), n_rays, flags,
-                        reinterpret_cast<float4*>(hits), 0));
+  // Zero-copy: pinned host buffers are traversed in place.  The persistent
+  // kernel pulls each ray over PCIe when a lane needs it and stores the hit
+  // straight to host memory, so the transfers overlap the traversal at ray
+  // granularity and nothing is staged.
+  const int zc = params().zero_copy;
+  const void* rays_k = rays_dev ? (const void*)rays : ((zc & 1) ? mapped_alias(rays) : nullptr);
+  void* hits_k = hits_dev ? (void*)hits : ((zc & 2) ? mapped_alias(hits) : nullptr);
+  if (rays_k && hits_k) {
+    RT_TRY(trace_device(h, reinterpret_cast<const float4*>(rays_k), n_rays, flags,
+                        reinterpret_cast<float4*>(hits_k), 0));
     RT_CUDA(cudaStreamSynchronize(0));
     return RT_OK;
   }
+  // partial zero-copy: e.g. rays staged by the copy engine, hits stored by the
+  // kernel straight into pinned host memory (posted PCIe writes need no staging)
+  if (hits_k) return trace_staged(h, rays, rays_dev, n_rays, flags, (float*)hits_k, true);
+  if (rays_k) return trace_staged(h, (const float*)rays_k, true, n_rays, flags, hits, hits_dev);
   return trace_staged(h, rays, rays_dev, n_rays, flags, hits, hits_dev);
 }
 
@@ -788,6 +813,8 @@ extern "C" int rt_set_param(const char* name, int64_t value) {
   if (!strcmp(name, "sort.variant")) p.sort_variant = (int)value;
   else if (!strcmp(name, "trace.blocks_per_sm")) p.trace_blocks_per_sm = (int)value;
   else if (!strcmp(name, "trace.variant")) p.trace_variant = (int)value;
+  else if (!strcmp(name, "trace.zero_copy")) p.zero_copy = (int)value;
+  else if (!strcmp(name, "trace.stage_chunk")) p.stage_chunk = (int)value;
   else if (!strcmp(name, "trace.chunk")) p.trace_chunk = (int)value;
   else if (!strcmp(name, "trace.refill_min")) p.trace_refill_min = (int)value;
   else if (!strcmp(name, "trace.leaf_min")) p.trace_leaf_min = (int)value;

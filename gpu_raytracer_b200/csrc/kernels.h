@@ -100,6 +100,11 @@ struct Params {
   int trace_blocks_per_sm = 0;  // 0 = kernel default
   int trace_variant = 1;        // 0 = plain while-while, 1 = dynamic fetch + voted leaf loop
   int trace_chunk = 0, trace_refill_min = 0, trace_leaf_min = 0;  // 0 = defaults
+  // bit 0: kernels read pinned host rays in place, bit 1: store hits to pinned host in
+  // place.  Measured slower than the copy engines on B200/PCIe5 (profiles/r01b_e2e_modes.md),
+  // so the default stages both.
+  int zero_copy = 0;
+  int stage_chunk = 0;          // rays per staged chunk (0 = 1M)
   int num_sms = 0;              // filled at first use
 };
 Params& params();

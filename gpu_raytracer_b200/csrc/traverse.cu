@@ -319,7 +319,9 @@ int launch_trace(const Node* nodes, const SortedTri* stris, uint64_t n_tris, con
   const bool any = (flags & 1u) != 0;
   if (params().trace_variant != 0) {
     const Params& p = params();
-    const int chunk = p.trace_chunk > 0 ? p.trace_chunk : 64;
+    int chunk = p.trace_chunk > 0 ? p.trace_chunk : 64;
+    // small batches: keep every resident warp busy rather than a few warps long
+    if (p.trace_chunk <= 0 && n_rays < blocks * (kTraceThreads / 32) * (uint64_t)chunk * 2) chunk = 32;
     const int refill_min = p.trace_refill_min > 0 ? p.trace_refill_min : 16;
     const int leaf_min = p.trace_leaf_min > 0 ? p.trace_leaf_min : 8;
 #define RT_TRACE_DYN(A, S)                                                 \

@@ -285,8 +285,18 @@ def test_config2_million_triangles(rt, oracle):
         assert isinstance(got2, np.ndarray) and np.array_equal(bits(got2), bits(want))
         pinned = torch.from_numpy(host_rays).pin_memory()
         out = torch.empty((host_rays.shape[0], 4), dtype=torch.float32).pin_memory()
-        gb.trace(pinned, out=out)
+        gb.trace(pinned, out=out)          # zero-copy: the kernel reads/writes pinned memory
         assert np.array_equal(bits(out.numpy()), bits(want))
+        for zc in (0, 1, 2, 3):             # staged / zero-copy rays / zero-copy hits / both
+            rt.set_param("trace.zero_copy", zc)
+            try:
+                out.zero_()
+                gb.trace(pinned, out=out)
+            finally:
+                rt.set_param("trace.zero_copy", 0)
+            assert np.array_equal(bits(out.numpy()), bits(want)), zc
+        mixed = gb.trace(pinned)            # pinned rays -> hits of the same kind (host tensor)
+        assert np.array_equal(bits(mixed.numpy()), bits(want))
 
 
 def test_refit_after_moving_vertices(rt, oracle):
