@@ -30,8 +30,13 @@ struct BvhHeader {
   uint32_t pad[7];
 };
 
-// parent word: (parent internal index << 1) | slot; kNoParent for the root
+// parent word: (parent internal index << 2) | (local << 1) | slot; kNoParent for
+// the root.  slot 0 = left child.  local = 1 when the parent's whole leaf range
+// lies inside one aligned group of kRefitLeaves leaves, i.e. inside the CTA that
+// refits those leaves, which may then use shared memory and CTA-scope fences.
 constexpr uint32_t kNoParent = 0xFFFFFFFFu;
+constexpr int kRefitLeavesLog2 = 10;
+constexpr int kRefitLeaves = 1 << kRefitLeavesLog2;
 
 // ---- generators (scene_gen.cu, ray_gen.cu) ---------------------------------
 int launch_gen_scene(int kind, uint64_t p0, uint64_t p1, uint64_t seed, uint64_t first,

@@ -5,10 +5,15 @@
 // One thread per leaf.  It gathers its triangle through the sorted index,
 // stores it in traversal form {v0 | prim, e1, e2} at its sorted position, then
 // walks up: it writes the box it carries (and its own child id) into its slot
-// of the parent's 64-byte node — one full 32-byte sector — fences, and bumps
-// the parent's counter.  The first arriver stops; the second reads the
-// sibling's slot from L2 (ld.cg: the line may be stale in this SM's L1), unions
-// and continues.  Every node slot is written exactly once and read at most
+// of the parent's 64-byte node — one full 32-byte sector — and bumps the
+// parent's counter.  The first arriver stops; the second unions with the
+// sibling's box and continues.  A CTA owns kRefitLeaves = 1024 consecutive
+// leaves; ~97 % of all internal nodes have their whole leaf range inside one
+// CTA (karras.cu marks them), and for those the counter and the deposited boxes
+// live in shared memory with CTA-scope fences.  Only nodes that straddle CTAs
+// use the device-scope protocol: global counter, __threadfence, sibling slot
+// re-read from L2 (ld.cg).  ncu on the first version showed 55 % of the stall
+// samples on MEMBAR.GPU; this removes them from all but the top of the tree.  Every node slot is written exactly once and read at most
 // once: ~96 B per internal node against the 112 B of the textbook layout.
 // The walker that leaves the root stores the scene box in the header.
 //
@@ -33,38 +38,28 @@ struct Box {
   float lx, ly, lz, hx, hy, hz;
 };
 
-__device__ __forceinline__ void walk_up(Box b, int child_enc, uint32_t pword,
-                                        const uint32_t* __restrict__ parent,
-                                        uint32_t* __restrict__ flags, Node* __restrict__ nodes,
-                                        BvhHeader* __restrict__ header) {
-  while (pword != kNoParent) {
-    const uint32_t p = pword >> 1, slot = pword & 1u;
-    float4* np = reinterpret_cast<float4*>(nodes + p);
-    np[2 * slot] = make_float4(b.lx, b.ly, b.lz, __int_as_float(child_enc));
-    np[2 * slot + 1] = make_float4(b.hx, b.hy, b.hz, 0.0f);
-    __threadfence();
-    if (atomicAdd(flags + p, 1u) == 0u) return;  // first arriver: sibling not ready
-    __threadfence();
-    const float4 slo = ld_cg(np + 2 * (slot ^ 1u));
-    const float4 shi = ld_cg(np + 2 * (slot ^ 1u) + 1);
-    b.lx = omin(b.lx, slo.x); b.ly = omin(b.ly, slo.y); b.lz = omin(b.lz, slo.z);
-    b.hx = omax(b.hx, shi.x); b.hy = omax(b.hy, shi.y); b.hz = omax(b.hz, shi.z);
-    child_enc = (int)p;
-    pword = parent[p];
-  }
-  // left the root: b is the scene box
-  header->root_min[0] = b.lx; header->root_min[1] = b.ly; header->root_min[2] = b.lz;
-  header->root_max[0] = b.hx; header->root_max[1] = b.hy; header->root_max[2] = b.hz;
-}
+// Shared state of one CTA = kRefitLeaves consecutive leaves: arrival counters and
+// deposited child boxes of the internal nodes whose leaf range lies inside the
+// CTA (index = node id - first leaf of the CTA; a Karras node id is one end of
+// its own range, so it falls in the same window).
+struct RefitSmem {
+  uint32_t flag[kRefitLeaves];
+  float box[kRefitLeaves][2][6];
+};
 
 // FROM_INDEX: prim comes from sorted_idx (build); else from stris[j].v0p.w (refit_bvh)
 template <bool FROM_INDEX>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(kRefitLeaves)
 refit_kernel(const float4* __restrict__ tris, const uint32_t* __restrict__ sorted_idx, uint32_t n,
              const uint32_t* __restrict__ parent, uint32_t* __restrict__ flags,
              Node* __restrict__ nodes, SortedTri* __restrict__ stris,
              BvhHeader* __restrict__ header) {
-  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  extern __shared__ __align__(16) unsigned char refit_smem_raw[];
+  RefitSmem& sm = *reinterpret_cast<RefitSmem*>(refit_smem_raw);
+  const uint32_t base = blockIdx.x * kRefitLeaves;
+  const uint32_t j = base + threadIdx.x;
+  sm.flag[threadIdx.x] = 0;
+  __syncthreads();
   if (j >= n) return;
   uint32_t prim;
   if (FROM_INDEX) prim = sorted_idx[j];
@@ -78,7 +73,47 @@ refit_kernel(const float4* __restrict__ tris, const uint32_t* __restrict__ sorte
   Box bx;
   bx.lx = omin(omin(a.x, b.x), c.x); bx.ly = omin(omin(a.y, b.y), c.y); bx.lz = omin(omin(a.z, b.z), c.z);
   bx.hx = omax(omax(a.x, b.x), c.x); bx.hy = omax(omax(a.y, b.y), c.y); bx.hz = omax(omax(a.z, b.z), c.z);
-  walk_up(bx, ~(int)j, parent[(n - 1) + j], parent, flags, nodes, header);
+
+  int child_enc = ~(int)j;
+  uint32_t pword = parent[(n - 1) + j];
+  while (pword != kNoParent) {
+    const uint32_t p = pword >> 2, slot = pword & 1u;
+    // the grandparent link does not depend on who wins below: fetch it now so its
+    // latency overlaps the stores, the fence and the atomic
+    const uint32_t next_pword = parent[p];
+    float4* np = reinterpret_cast<float4*>(nodes + p);
+    np[2 * slot] = make_float4(bx.lx, bx.ly, bx.lz, __int_as_float(child_enc));
+    np[2 * slot + 1] = make_float4(bx.hx, bx.hy, bx.hz, 0.0f);
+    if (pword & 2u) {
+      // both children are refitted by this CTA: meet in shared memory
+      const uint32_t k = p - base;
+      float* mine = sm.box[k][slot];
+      mine[0] = bx.lx; mine[1] = bx.ly; mine[2] = bx.lz;
+      mine[3] = bx.hx; mine[4] = bx.hy; mine[5] = bx.hz;
+      __threadfence_block();
+      if (atomicAdd(&sm.flag[k], 1u) == 0u) return;  // first arriver stops
+      __threadfence_block();
+      const volatile float* sib = sm.box[k][slot ^ 1u];
+      bx.lx = omin(bx.lx, sib[0]); bx.ly = omin(bx.ly, sib[1]); bx.lz = omin(bx.lz, sib[2]);
+      bx.hx = omax(bx.hx, sib[3]); bx.hy = omax(bx.hy, sib[4]); bx.hz = omax(bx.hz, sib[5]);
+    } else {
+      // the sibling subtree belongs to another CTA: device-scope protocol
+      __threadfence();
+      if (atomicAdd(flags + p, 1u) == 0u) return;
+      // acquire side: the loads below are issued only after the atomic's result is
+      // known (control dependency) and go to L2 (ld.cg), where the sibling's
+      // fenced stores already are
+      const float4 slo = ld_cg(np + 2 * (slot ^ 1u));
+      const float4 shi = ld_cg(np + 2 * (slot ^ 1u) + 1);
+      bx.lx = omin(bx.lx, slo.x); bx.ly = omin(bx.ly, slo.y); bx.lz = omin(bx.lz, slo.z);
+      bx.hx = omax(bx.hx, shi.x); bx.hy = omax(bx.hy, shi.y); bx.hz = omax(bx.hz, shi.z);
+    }
+    child_enc = (int)p;
+    pword = next_pword;
+  }
+  // left the root: bx is the scene box
+  header->root_min[0] = bx.lx; header->root_min[1] = bx.ly; header->root_min[2] = bx.lz;
+  header->root_max[0] = bx.hx; header->root_max[1] = bx.hy; header->root_max[2] = bx.hz;
 }
 
 // canonical arrays from the traversal layout (parity accessors T3/T4)
@@ -91,7 +126,7 @@ export_kernel(const Node* __restrict__ nodes, const uint32_t* __restrict__ paren
   const uint32_t n_nodes = 2 * n - 1, leaf0 = n - 1;
   if (i >= n_nodes) return;
   const uint32_t pw = parent[i];
-  if (parent_out) parent_out[i] = (pw == kNoParent) ? kNoParent : (pw >> 1);
+  if (parent_out) parent_out[i] = (pw == kNoParent) ? kNoParent : (pw >> 2);
   if (boxes) {
     float* o = boxes + 6 * (uint64_t)i;
     if (pw == kNoParent) {
@@ -100,7 +135,7 @@ export_kernel(const Node* __restrict__ nodes, const uint32_t* __restrict__ paren
         o[3 + k] = header->root_max[k];
       }
     } else {
-      const float4* np = reinterpret_cast<const float4*>(nodes + (pw >> 1)) + 2 * (pw & 1u);
+      const float4* np = reinterpret_cast<const float4*>(nodes + (pw >> 2)) + 2 * (pw & 1u);
       float4 lo = np[0], hi = np[1];
       o[0] = lo.x; o[1] = lo.y; o[2] = lo.z; o[3] = hi.x; o[4] = hi.y; o[5] = hi.z;
     }
@@ -143,12 +178,15 @@ static int refit_common(bool from_index, const float4* tris, const uint32_t* sor
                         BvhHeader* header, cudaStream_t s) {
   if (n == 0) return 0;
   if (n > 1) RT_CUDA(cudaMemsetAsync(flags, 0, (size_t)(n - 1) * sizeof(uint32_t), s));
-  const unsigned blocks = (unsigned)((n + 255) / 256);
+  const unsigned blocks = (unsigned)((n + kRefitLeaves - 1) / kRefitLeaves);
+  const size_t smem = sizeof(RefitSmem);
+  RT_CUDA(cudaFuncSetAttribute(refit_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  RT_CUDA(cudaFuncSetAttribute(refit_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   if (from_index)
-    refit_kernel<true><<<blocks, 256, 0, s>>>(tris, sorted_idx, (uint32_t)n, parent, flags, nodes,
+    refit_kernel<true><<<blocks, kRefitLeaves, smem, s>>>(tris, sorted_idx, (uint32_t)n, parent, flags, nodes,
                                               stris, header);
   else
-    refit_kernel<false><<<blocks, 256, 0, s>>>(tris, sorted_idx, (uint32_t)n, parent, flags, nodes,
+    refit_kernel<false><<<blocks, kRefitLeaves, smem, s>>>(tris, sorted_idx, (uint32_t)n, parent, flags, nodes,
                                                stris, header);
   RT_LAUNCHED();
   return 0;
