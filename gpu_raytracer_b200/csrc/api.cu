@@ -255,6 +255,8 @@ int build_impl(rt_bvh* h, const float* tris_in, uint32_t flags, cudaStream_t s) 
   RT_TRY(tmp.alloc((void**)&ws.lookback, ws.lookback_words * 4));
   RT_TRY(tmp.alloc(&bkeys, 32));
   RT_TRY(tmp.alloc(&flags_buf, (n > 1 ? n - 1 : 1) * 4));
+  void* queue_buf = nullptr;
+  RT_TRY(tmp.alloc(&queue_buf, refit_queue_bytes(n)));
 
   const bool timed = (flags & RT_BUILD_TIMINGS) != 0;
   cudaEvent_t ev[RT_STAGE_COUNT];
@@ -277,7 +279,7 @@ int build_impl(rt_bvh* h, const float* tris_in, uint32_t flags, cudaStream_t s) 
   RT_TRY(launch_karras(skeys, n, h->key_bits, h->parent, s));
   RT_TRY(mark(4));
   RT_TRY(launch_refit(tris, svals, n, h->parent, (uint32_t*)flags_buf, h->nodes, h->stris,
-                      h->header, s));
+                      h->header, queue_buf, s));
   RT_TRY(mark(5));
   if (h->keys) RT_CUDA(cudaMemcpyAsync(h->keys, skeys, n * ksz, cudaMemcpyDeviceToDevice, s));
   RT_CUDA(cudaMemcpyAsync(&hdr, h->header, sizeof(hdr), cudaMemcpyDeviceToHost, s));
@@ -353,8 +355,10 @@ extern "C" int refit_bvh(rt_bvh* h, const float* tris_in) {
   }
   void* flags_buf = nullptr;
   RT_TRY(tmp.alloc(&flags_buf, (h->n > 1 ? h->n - 1 : 1) * 4));
+  void* queue_buf = nullptr;
+  RT_TRY(tmp.alloc(&queue_buf, refit_queue_bytes(h->n)));
   RT_TRY(launch_refit_update(tris, h->n, h->parent, (uint32_t*)flags_buf, h->nodes, h->stris,
-                             h->header, s));
+                             h->header, queue_buf, s));
   BvhHeader hdr;
   RT_CUDA(cudaMemcpyAsync(&hdr, h->header, sizeof(hdr), cudaMemcpyDeviceToHost, s));
   RT_CUDA(cudaStreamSynchronize(s));

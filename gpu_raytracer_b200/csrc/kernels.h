@@ -82,10 +82,13 @@ int launch_karras(const void* keys, uint64_t n, uint32_t key_bits, uint32_t* par
 // flags: n-1 u32, zeroed by the launcher.  Writes nodes, sorted tris, header box.
 int launch_refit(const float4* tris, const uint32_t* sorted_idx, uint64_t n,
                  const uint32_t* parent, uint32_t* flags, Node* nodes, SortedTri* stris,
-                 BvhHeader* header, cudaStream_t s);
+                 BvhHeader* header, void* queue_buf, cudaStream_t s);
+// bytes of the continuation queue launch_refit needs (queue_buf)
+size_t refit_queue_bytes(uint64_t n);
 // refit with moved vertices: the primitive index comes from stris[j].v0p.w
 int launch_refit_update(const float4* tris, uint64_t n, const uint32_t* parent, uint32_t* flags,
-                        Node* nodes, SortedTri* stris, BvhHeader* header, cudaStream_t s);
+                        Node* nodes, SortedTri* stris, BvhHeader* header, void* queue_buf,
+                        cudaStream_t s);
 // canonical arrays for the parity accessors (device outputs, may be null)
 int launch_export_topology(const Node* nodes, const uint32_t* parent, uint64_t n, uint32_t* left,
                            uint32_t* right, uint32_t* parent_out, float* boxes,
