@@ -243,16 +243,20 @@ int build_impl(rt_bvh* h, const float* tris_in, uint32_t flags, cudaStream_t s) 
   }
 
   const size_t ksz = key_size(h->key_bits);
-  const int passes = sort_num_passes(h->key_bits);
   void *keys = nullptr, *bkeys = nullptr, *flags_buf = nullptr;
   SortWorkspace ws;
   RT_TRY(tmp.alloc(&keys, n * ksz));
-  RT_TRY(tmp.alloc(&ws.keys_alt, n * ksz));
+  if (h->key_bits == 30) {
+    RT_TRY(tmp.alloc(&ws.rec_a, n * 8));
+    RT_TRY(tmp.alloc(&ws.rec_b, n * 8));
+  } else {
+    RT_TRY(tmp.alloc(&ws.keys_alt, n * ksz));
+    RT_TRY(tmp.alloc((void**)&ws.vals_alt, n * 4));
+  }
   RT_TRY(tmp.alloc((void**)&ws.vals, n * 4));
-  RT_TRY(tmp.alloc((void**)&ws.vals_alt, n * 4));
-  RT_TRY(tmp.alloc((void**)&ws.hist, (size_t)2 * passes * 256 * 4));
-  ws.lookback_words = sort_lookback_words(n, h->key_bits);
-  RT_TRY(tmp.alloc((void**)&ws.lookback, ws.lookback_words * 4));
+  RT_TRY(tmp.alloc((void**)&ws.hist, sort_hist_words(h->key_bits) * 4));
+  ws.chunk_words = sort_chunk_words(n, h->key_bits);
+  RT_TRY(tmp.alloc((void**)&ws.chunk_hist, ws.chunk_words * 4));
   RT_TRY(tmp.alloc(&bkeys, 32));
   RT_TRY(tmp.alloc(&flags_buf, (n > 1 ? n - 1 : 1) * 4));
   void* queue_buf = nullptr;
@@ -270,7 +274,7 @@ int build_impl(rt_bvh* h, const float* tris_in, uint32_t flags, cudaStream_t s) 
   RT_TRY(mark(0));
   RT_TRY(launch_bounds(tris, n, (uint32_t*)bkeys, s));
   RT_TRY(mark(1));
-  RT_TRY(launch_morton(tris, n, (const uint32_t*)bkeys, h->key_bits, keys, ws.hist, s));
+  RT_TRY(launch_morton(tris, n, (const uint32_t*)bkeys, h->key_bits, keys, s));
   RT_TRY(mark(2));
   void* skeys = nullptr;
   uint32_t* svals = nullptr;
@@ -815,6 +819,7 @@ extern "C" int rt_set_param(const char* name, int64_t value) {
   if (!name) return fail(RT_ERR_INVALID, "rt_set_param: name is NULL");
   Params& p = params();
   if (!strcmp(name, "sort.variant")) p.sort_variant = (int)value;
+  else if (!strcmp(name, "sort.bits")) p.sort_bits = (int)value;
   else if (!strcmp(name, "trace.blocks_per_sm")) p.trace_blocks_per_sm = (int)value;
   else if (!strcmp(name, "trace.variant")) p.trace_variant = (int)value;
   else if (!strcmp(name, "trace.zero_copy")) p.zero_copy = (int)value;
@@ -839,15 +844,18 @@ extern "C" int rt_sort_pairs(void* keys, uint32_t* vals, uint64_t n, uint32_t ke
   cudaStream_t s = 0;
   TempPool tmp(s);
   const size_t ksz = key_size(key_bits);
-  const int passes = sort_num_passes(key_bits);
   SortWorkspace ws;
   ws.vals = vals;
-  RT_TRY(tmp.alloc(&ws.keys_alt, n * ksz));
-  RT_TRY(tmp.alloc((void**)&ws.vals_alt, n * 4));
-  RT_TRY(tmp.alloc((void**)&ws.hist, (size_t)2 * passes * 256 * 4));
-  ws.lookback_words = sort_lookback_words(n, key_bits);
-  RT_TRY(tmp.alloc((void**)&ws.lookback, ws.lookback_words * 4));
-  RT_TRY(launch_histogram(keys, n, key_bits, ws.hist, s));
+  if (key_bits == 30) {
+    RT_TRY(tmp.alloc(&ws.rec_a, n * 8));
+    RT_TRY(tmp.alloc(&ws.rec_b, n * 8));
+  } else {
+    RT_TRY(tmp.alloc(&ws.keys_alt, n * ksz));
+    RT_TRY(tmp.alloc((void**)&ws.vals_alt, n * 4));
+  }
+  RT_TRY(tmp.alloc((void**)&ws.hist, sort_hist_words(key_bits) * 4));
+  ws.chunk_words = sort_chunk_words(n, key_bits);
+  RT_TRY(tmp.alloc((void**)&ws.chunk_hist, ws.chunk_words * 4));
   cudaEvent_t e0, e1;
   RT_CUDA(cudaEventCreate(&e0));
   RT_CUDA(cudaEventCreate(&e1));
@@ -863,6 +871,11 @@ extern "C" int rt_sort_pairs(void* keys, uint32_t* vals, uint64_t n, uint32_t ke
   cudaEventDestroy(e1);
   if (rc != 0) return rc;
   RT_CUDA(e);
+  if (ko != keys) {  // odd number of passes: bring the result back to the caller's buffers
+    RT_CUDA(cudaMemcpyAsync(keys, ko, n * ksz, cudaMemcpyDeviceToDevice, s));
+    RT_CUDA(cudaMemcpyAsync(vals, vo, n * 4, cudaMemcpyDeviceToDevice, s));
+    RT_CUDA(cudaStreamSynchronize(s));
+  }
   if (ms) *ms = t;
   return RT_OK;
 }

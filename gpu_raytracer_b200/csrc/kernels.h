@@ -54,28 +54,32 @@ int launch_shade(const float4* tris, const float4* rays, const float4* hits,
 // bounds_keys: 6 ordered-int keys, min.xyz then max.xyz; must be pre-set to
 // 0xFFFFFFFF x3, 0 x3 (launch_bounds does that itself).
 int launch_bounds(const float4* tris, uint64_t n, uint32_t* bounds_keys, cudaStream_t s);
-// keys: n u32 (30-bit) or n u64 (63-bit).  hist: [passes][256] u32, zeroed by
-// the launcher, receives the per-digit histograms of all keys.
+// keys: n u32 (30-bit) or n u64 (63-bit)
 int launch_morton(const float4* tris, uint64_t n, const uint32_t* bounds_keys, uint32_t key_bits,
-                  void* keys, uint32_t* hist, cudaStream_t s);
+                  void* keys, cudaStream_t s);
 
 struct SortWorkspace {
-  void* keys_alt = nullptr;     // n keys, ping-pong partner of the input
-  uint32_t* vals_alt = nullptr; // n u32
+  void* keys_alt = nullptr;     // 63-bit keys: n keys, ping-pong partner of the input
+  uint32_t* vals_alt = nullptr; // 63-bit keys: n u32
+  void* rec_a = nullptr;        // 30-bit keys: n packed 64-bit records (key << 32 | payload)
+  void* rec_b = nullptr;        // 30-bit keys: ping-pong partner of rec_a
   uint32_t* vals = nullptr;     // n u32 (first pass writes it: payload starts as iota)
-  uint32_t* hist = nullptr;     // [passes][256]
-  uint32_t* lookback = nullptr; // [passes][tiles][256] + [passes] tile counters
-  uint64_t lookback_words = 0;
+  uint32_t* hist = nullptr;       // [passes][bins] global bin totals (sort_hist_words)
+  uint32_t* chunk_hist = nullptr; // [chunks][bins] per-chunk counts, then offsets
+  uint64_t chunk_words = 0;       // sort_chunk_words
 };
-int sort_num_passes(uint32_t key_bits);
-uint64_t sort_lookback_words(uint64_t n, uint32_t key_bits);
+// digit schedule of the LSD sort: `passes` digits of `bits` bits, lowest first
+// (30-bit keys: 3 x 10; 63-bit keys: 7 x 9; rt_set_param("sort.bits") overrides)
+struct SortPlan {
+  int passes, bits;
+};
+SortPlan sort_plan(uint32_t key_bits);
+uint64_t sort_hist_words(uint32_t key_bits);
+uint64_t sort_chunk_words(uint64_t n, uint32_t key_bits);
 // Sorts (keys, iota) by key.  Result: *keys_out / *vals_out point at whichever
-// ping-pong buffer holds the sorted data.  hist must already hold the digit
-// histograms (launch_morton or launch_histogram).
+// ping-pong buffer holds the sorted data.
 int launch_sort(void* keys, uint64_t n, uint32_t key_bits, const SortWorkspace& ws,
                 bool iota_payload, void** keys_out, uint32_t** vals_out, cudaStream_t s);
-int launch_histogram(const void* keys, uint64_t n, uint32_t key_bits, uint32_t* hist,
-                     cudaStream_t s);
 
 int launch_karras(const void* keys, uint64_t n, uint32_t key_bits, uint32_t* parent,
                   cudaStream_t s);
@@ -105,6 +109,7 @@ int launch_trace(const Node* nodes, const SortedTri* stris, uint64_t n_tris, con
 // tuning knobs (rt_set_param)
 struct Params {
   int sort_variant = 0;
+  int sort_bits = 0;            // 0 = default digit width (sort_plan)
   int trace_blocks_per_sm = 0;  // 0 = kernel default
   int trace_variant = 1;        // 0 = plain while-while, 1 = dynamic fetch + voted leaf loop
   int trace_chunk = 0, trace_refill_min = 0, trace_leaf_min = 0;  // 0 = defaults

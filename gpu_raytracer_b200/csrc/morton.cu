@@ -5,11 +5,9 @@
 //     order-free), warps reduce with redux.sync (__reduce_min/max_sync), blocks
 //     reduce through shared memory and finish with 6 atomics per block.
 // A2  morton_kernel: one thread per triangle: centroid of the triangle's own
-//     box, quantised against the scene box, bit-interleaved (x highest).  The
-//     same kernel accumulates the 8-bit digit histograms of every radix pass in
-//     shared memory (the up-front histogram of onesweep), so the keys are never
-//     re-read for it.  Writes the key only; the payload of the first sort pass
-//     is the element position (iota), which needs no memory.
+//     box, quantised against the scene box, bit-interleaved (x highest).
+//     Writes the key only; the payload of the first sort pass is the element
+//     position (iota), which needs no memory.
 //
 // Roofline: both kernels are HBM-bound: 48 B/tri read (+4 or 8 B/tri written).
 #include "common.cuh"
@@ -102,12 +100,8 @@ constexpr int kMortonThreads = 256;
 template <int KEY_BITS>
 __global__ void __launch_bounds__(kMortonThreads)
 morton_kernel(const float4* __restrict__ tris, uint64_t n, const uint32_t* __restrict__ bkeys,
-              void* __restrict__ keys_out, uint32_t* __restrict__ hist) {
-  constexpr int kPasses = (KEY_BITS + 7) / 8;  // 4 or 8
+              void* __restrict__ keys_out) {
   constexpr float kCells = (KEY_BITS == 30) ? 1024.0f : 2097152.0f;
-  __shared__ uint32_t s_hist[kPasses * 256];
-  for (int i = threadIdx.x; i < kPasses * 256; i += kMortonThreads) s_hist[i] = 0;
-  __syncthreads();
 
   float smin[3], scale[3];
 #pragma unroll
@@ -131,42 +125,10 @@ morton_kernel(const float4* __restrict__ tris, uint64_t n, const uint32_t* __res
     if (KEY_BITS == 30) {
       uint32_t key = (expand10(qx) << 2) | (expand10(qy) << 1) | expand10(qz);
       reinterpret_cast<uint32_t*>(keys_out)[t] = key;
-#pragma unroll
-      for (int p = 0; p < kPasses; ++p) atomicAdd(&s_hist[p * 256 + ((key >> (8 * p)) & 255u)], 1u);
     } else {
       uint64_t key = (expand21(qx) << 2) | (expand21(qy) << 1) | expand21(qz);
       reinterpret_cast<uint64_t*>(keys_out)[t] = key;
-#pragma unroll
-      for (int p = 0; p < kPasses; ++p)
-        atomicAdd(&s_hist[p * 256 + (uint32_t)((key >> (8 * p)) & 255ull)], 1u);
     }
-  }
-  __syncthreads();
-  for (int i = threadIdx.x; i < kPasses * 256; i += kMortonThreads) {
-    uint32_t v = s_hist[i];
-    if (v) atomicAdd(&hist[i], v);
-  }
-}
-
-// stand-alone digit histogram (rt_sort_pairs on keys that did not come from
-// morton_kernel)
-template <typename KeyT, int PASSES>
-__global__ void __launch_bounds__(256)
-histogram_kernel(const KeyT* __restrict__ keys, uint64_t n, uint32_t* __restrict__ hist) {
-  __shared__ uint32_t s_hist[PASSES * 256];
-  for (int i = threadIdx.x; i < PASSES * 256; i += 256) s_hist[i] = 0;
-  __syncthreads();
-  for (uint64_t t = (uint64_t)blockIdx.x * 256 + threadIdx.x; t < n;
-       t += (uint64_t)gridDim.x * 256) {
-    KeyT key = keys[t];
-#pragma unroll
-    for (int p = 0; p < PASSES; ++p)
-      atomicAdd(&s_hist[p * 256 + (uint32_t)((key >> (8 * p)) & 255)], 1u);
-  }
-  __syncthreads();
-  for (int i = threadIdx.x; i < PASSES * 256; i += 256) {
-    uint32_t v = s_hist[i];
-    if (v) atomicAdd(&hist[i], v);
   }
 }
 
@@ -193,29 +155,13 @@ int launch_bounds(const float4* tris, uint64_t n, uint32_t* bounds_keys, cudaStr
 }
 
 int launch_morton(const float4* tris, uint64_t n, const uint32_t* bounds_keys, uint32_t key_bits,
-                  void* keys, uint32_t* hist, cudaStream_t s) {
-  const int passes = sort_num_passes(key_bits);
-  RT_CUDA(cudaMemsetAsync(hist, 0, (size_t)passes * 256 * sizeof(uint32_t), s));
+                  void* keys, cudaStream_t s) {
   if (n == 0) return 0;
   unsigned grid = persistent_grid(n, kMortonThreads, 8);
   if (key_bits == 30)
-    morton_kernel<30><<<grid, kMortonThreads, 0, s>>>(tris, n, bounds_keys, keys, hist);
+    morton_kernel<30><<<grid, kMortonThreads, 0, s>>>(tris, n, bounds_keys, keys);
   else
-    morton_kernel<63><<<grid, kMortonThreads, 0, s>>>(tris, n, bounds_keys, keys, hist);
-  RT_LAUNCHED();
-  return 0;
-}
-
-int launch_histogram(const void* keys, uint64_t n, uint32_t key_bits, uint32_t* hist,
-                     cudaStream_t s) {
-  const int passes = sort_num_passes(key_bits);
-  RT_CUDA(cudaMemsetAsync(hist, 0, (size_t)passes * 256 * sizeof(uint32_t), s));
-  if (n == 0) return 0;
-  unsigned grid = persistent_grid(n, 256, 8);
-  if (key_bits == 30)
-    histogram_kernel<uint32_t, 4><<<grid, 256, 0, s>>>((const uint32_t*)keys, n, hist);
-  else
-    histogram_kernel<uint64_t, 8><<<grid, 256, 0, s>>>((const uint64_t*)keys, n, hist);
+    morton_kernel<63><<<grid, kMortonThreads, 0, s>>>(tris, n, bounds_keys, keys);
   RT_LAUNCHED();
   return 0;
 }

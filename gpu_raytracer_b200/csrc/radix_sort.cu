@@ -1,305 +1,536 @@
-// radix_sort.cu — A3: onesweep least-significant-digit radix sort of
-// (Morton key, primitive index) pairs (Adinets & Merrill
-// 2022, decoupled look-back of Merrill & Garland 2016).
+// radix_sort.cu — A3: least-significant-digit radix sort of (Morton key,
+// primitive index) pairs.
 //
-// One kernel launch per 8-bit digit.  The digit histograms of all passes were
-// accumulated while the keys were produced (morton.cu), so each pass reads every
-// pair once and writes it once: 16 B/element/pass for 32-bit keys, 24 B for
-// 64-bit keys.  Per tile:
-//   1. take a tile id from an atomic counter (ids follow start order, so every
-//      predecessor a tile waits for is already running: forward progress);
-//   2. warp-striped coalesced key loads;
-//   3. per-warp ranking: lanes with equal digits find each other (match.any or
-//      an 8-ballot loop), the lowest such lane bumps the warp's private
-//      shared-memory counter — no shared atomics, stable by construction;
-//   4. one thread per bin folds the warp counters, publishes the tile's count
-//      (flag LOCAL), looks back over predecessors until it meets an INCLUSIVE
-//      word, then publishes its own inclusive prefix.  Count and flag share one
-//      32-bit word, so a single relaxed store/load is atomic;
-//   5. pairs are first placed in tile-sorted order in shared memory, then
-//      written out so consecutive threads write consecutive addresses of one bin.
+// B200 shape of the algorithm.  A decoupled look-back onesweep (Adinets &
+// Merrill 2022) was built and measured first (profiles/r01c_*): at ~0.05 us
+// between tile starts and ~0.7 us per L2 round trip every tile had to walk
+// 10-20 predecessors for each of its 256-1024 bins, and the look-back words
+// cost more L2 traffic than the pairs themselves.  This version has no
+// inter-CTA dependency at all:
 //
-// Bound: HBM (integer/byte work, no tensor cores).  Grid: one CTA per tile,
-// 2-3 CTAs resident per SM (shared memory sized for the 227 KB of sm_100a).
+//   chunk_hist_kernel    the input is cut into one contiguous chunk per resident
+//                        CTA; each CTA histograms the digit of its chunk in
+//                        shared memory and stores H[chunk][bin] (+ global bin
+//                        totals).  Keys only: 4 or 8 B/element, mostly L2 hits
+//                        because the previous pass has just written them.
+//   chunk_offsets_kernel O[chunk][bin] = (start of the bin) + (elements of that
+//                        bin in earlier chunks): one column scan per bin.
+//   scatter_kernel       persistent, one CTA per chunk, tiles of the chunk in
+//                        order.  Per tile: warp-striped key loads, per-warp
+//                        stable ranking against private 16-bit counters,
+//                        fold + scan of the tile's bin counts, placement in
+//                        shared memory in tile-sorted order, coalesced write-out.
+//                        The running output offset of every bin lives in the
+//                        registers of the bin's owner thread; the next tile's
+//                        keys are fetched while the current tile is written.
+//
+// Digits are wide (10 bits for 30-bit keys: 3 passes; 9 bits for 63-bit keys:
+// 7 passes): every pass saved is 16 or 24 B/element that never move.
+//
+// Ranking: every lane reads its digit's counter, writes back count+1 tagged
+// with its lane id and re-reads.  Lanes that find their own tag are alone with
+// their digit.  Otherwise the tag read back names one lane per digit group (5
+// bits), so five ballots on it give every lane its peer mask, instead of one
+// ballot per digit bit.  No shared atomics, stable by construction.
+//
+// Bound: HBM by the byte count (integer/byte work, no tensor cores); the
+// measured limiter is instruction issue (profiles/).
+#include <type_traits>
+
 #include "common.cuh"
 #include "kernels.h"
 
 namespace rt {
 namespace {
 
-constexpr int kRadix = 256;
-constexpr uint32_t kFlagLocal = 1u << 30;
-constexpr uint32_t kFlagIncl = 2u << 30;
-constexpr uint32_t kValueMask = (1u << 30) - 1;
+constexpr uint32_t kFull = 0xFFFFFFFFu;
 
-__device__ __forceinline__ void st_relaxed(uint32_t* p, uint32_t v) {
-  asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-__device__ __forceinline__ uint32_t ld_relaxed(const uint32_t* p) {
-  uint32_t v;
-  asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-
-template <bool USE_MATCH>
-__device__ __forceinline__ uint32_t peers_of(uint32_t digit) {
-  if (USE_MATCH) {
-    return __match_any_sync(0xFFFFFFFFu, digit);
-  } else {
-    uint32_t mask = 0xFFFFFFFFu;
-#pragma unroll
-    for (int b = 0; b < 8; ++b) {
-      bool bit = (digit >> b) & 1u;
-      uint32_t vote = __ballot_sync(0xFFFFFFFFu, bit);
-      mask &= bit ? vote : ~vote;
-    }
-    return mask;
+// where chunk c of the pass starts and ends (host and device agree on this)
+struct ChunkGeom {
+  uint32_t n, chunk_size, chunks;
+  __host__ __device__ uint32_t begin(uint32_t c) const { return c * chunk_size; }
+  __host__ __device__ uint32_t end(uint32_t c) const {
+    const uint32_t e = (c + 1u) * chunk_size;
+    return (e < n && c + 1u < chunks) ? e : n;
   }
-}
-
-// exclusive prefix sums of the per-pass digit histograms: base[p][b]
-__global__ void __launch_bounds__(kRadix) scan_hist_kernel(const uint32_t* __restrict__ hist,
-                                                           uint32_t* __restrict__ base) {
-  __shared__ uint32_t s_warp[8];
-  const int b = threadIdx.x, lane = b & 31, warp = b >> 5;
-  uint32_t v = hist[blockIdx.x * kRadix + b];
-  uint32_t incl = v;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
-    if (lane >= o) incl += t;
-  }
-  if (lane == 31) s_warp[warp] = incl;
-  __syncthreads();
-  uint32_t off = 0;
-  for (int w = 0; w < warp; ++w) off += s_warp[w];
-  base[blockIdx.x * kRadix + b] = off + incl - v;
-}
-
-template <typename KeyT, int THREADS, int IPT>
-struct SortSmem {
-  static constexpr int kWarps = THREADS / 32;
-  static constexpr int kTile = THREADS * IPT;
-  uint32_t warp_hist[kWarps][kRadix];
-  uint32_t local_start[kRadix];
-  uint32_t bin_base[kRadix];
-  uint32_t scan_warp[8];
-  uint32_t tile;
-  KeyT keys[kTile];
-  uint32_t vals[kTile];
 };
 
-template <typename KeyT, int THREADS, int IPT, int MIN_BLOCKS, bool IOTA, bool USE_MATCH>
+// ---- per-chunk digit histogram ------------------------------------------------
+constexpr int kHistThreads = 1024;
+
+template <int BITS>
+__device__ __forceinline__ void hist_add(uint32_t* sh, uint32_t d, bool valid) {
+  // coherent input: a warp often holds one digit only; count it with one atomic
+  const uint32_t d0 = __shfl_sync(kFull, d, 0);
+  if (__all_sync(kFull, valid && d == d0)) {
+    if ((threadIdx.x & 31) == 0) atomicAdd(&sh[d], 32u);
+  } else if (valid) {
+    atomicAdd(&sh[d], 1u);
+  }
+}
+
+template <typename KeyT, int BITS>
+__global__ void __launch_bounds__(kHistThreads)
+chunk_hist_kernel(const KeyT* __restrict__ keys, ChunkGeom g, int shift,
+                  uint32_t* __restrict__ chunk_hist, uint32_t* __restrict__ totals) {
+  constexpr int kBins = 1 << BITS;
+  __shared__ uint32_t sh[kBins];
+  for (int b = threadIdx.x; b < kBins; b += kHistThreads) sh[b] = 0u;
+  __syncthreads();
+  const uint32_t c = blockIdx.x, begin = g.begin(c), end = g.end(c);
+  constexpr uint32_t kUnroll = 4;
+  uint32_t base = begin;
+  for (; base + kUnroll * kHistThreads <= end; base += kUnroll * kHistThreads) {
+    KeyT k[kUnroll];
+#pragma unroll
+    for (uint32_t u = 0; u < kUnroll; ++u) k[u] = keys[base + u * kHistThreads + threadIdx.x];
+#pragma unroll
+    for (uint32_t u = 0; u < kUnroll; ++u)
+      hist_add<BITS>(sh, (uint32_t)(k[u] >> shift) & (kBins - 1), true);
+  }
+  for (; base < end; base += kHistThreads) {
+    const uint32_t i = base + threadIdx.x;
+    const bool valid = i < end;
+    const KeyT k = valid ? keys[i] : KeyT(0);
+    hist_add<BITS>(sh, (uint32_t)(k >> shift) & (kBins - 1), valid);
+  }
+  __syncthreads();
+  for (int b = threadIdx.x; b < kBins; b += kHistThreads) {
+    const uint32_t v = sh[b];
+    chunk_hist[(size_t)c * kBins + b] = v;
+    if (v) atomicAdd(&totals[b], v);
+  }
+}
+
+// ---- chunk offsets ---------------------------------------------------------------
+// in place: chunk_hist[c][b] <- start of bin b + elements of bin b in chunks < c.
+// One warp per bin: lanes stride over the chunks, warp-shuffle scan with carry.
+constexpr int kOffWarps = 8;
+constexpr int kOffMaxRounds = 24;  // chunks <= 32 * 24
+
+template <int BITS>
+__global__ void __launch_bounds__(kOffWarps * 32)
+chunk_offsets_kernel(uint32_t* __restrict__ chunk_hist, const uint32_t* __restrict__ totals,
+                     uint32_t chunks) {
+  constexpr int kBins = 1 << BITS;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int bin = blockIdx.x * kOffWarps + warp;
+  const int rounds = (int)((chunks + 31) / 32);
+  uint32_t v[kOffMaxRounds];
+#pragma unroll
+  for (int j = 0; j < kOffMaxRounds; ++j) {
+    const uint32_t c = (uint32_t)lane + 32u * j;
+    v[j] = (j < rounds && c < chunks) ? chunk_hist[(size_t)c * kBins + bin] : 0u;
+  }
+  // start of the bin: totals of all lower bins
+  uint32_t run = 0;
+  for (int b = lane; b < bin; b += 32) run += totals[b];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) run += __shfl_xor_sync(kFull, run, o);
+#pragma unroll
+  for (int j = 0; j < kOffMaxRounds; ++j) {
+    if (j < rounds) {  // warp-uniform
+      uint32_t incl = v[j];
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        uint32_t t = __shfl_up_sync(kFull, incl, o);
+        if (lane >= o) incl += t;
+      }
+      const uint32_t c = (uint32_t)lane + 32u * j;
+      if (c < chunks) chunk_hist[(size_t)c * kBins + bin] = run + incl - v[j];
+      run += __shfl_sync(kFull, incl, 31);
+    }
+  }
+}
+
+// ---- scatter -----------------------------------------------------------------------
+template <typename KeyT, int BITS, int THREADS, int IPT>
+struct SortCfg {
+  static constexpr int kBins = 1 << BITS;
+  static constexpr int kWarps = THREADS / 32;
+  static constexpr int kTile = THREADS * IPT;
+  // bin owners: each owns kBPT consecutive bins (an even number, handled as
+  // kPPT packed pairs of 16-bit counters)
+  static constexpr int kOwners = (THREADS < kBins / 2) ? THREADS : kBins / 2;
+  static constexpr int kBPT = kBins / kOwners;
+  static constexpr int kPPT = kBPT / 2;
+  static_assert(kBPT % 2 == 0 && kBPT >= 2, "bin owners handle packed pairs");
+  static_assert(IPT * 32 < 2048, "11-bit per-warp counters next to a 5-bit lane tag");
+  static_assert(kTile < 65536, "16-bit tile-local positions");
+};
+
+// 32-bit keys travel between the passes as packed 64-bit records
+// (key << 32 | payload): one load, one shared-memory slot and one scattered
+// store per element instead of two.  64-bit keys keep separate arrays.
+template <typename KeyT, int BITS, int THREADS, int IPT>
+struct SortSmem {
+  using C = SortCfg<KeyT, BITS, THREADS, IPT>;
+  static constexpr bool kPacked = sizeof(KeyT) == 4;
+  uint64_t keys[C::kTile];                   // packed records, or the 64-bit keys
+  uint32_t vals[kPacked ? 1 : C::kTile];     // payload of 64-bit keys
+  uint32_t bin_base[C::kBins];
+  uint16_t warp_hist[C::kWarps][C::kBins];  // (count << 5 | lane tag), later exclusive offsets
+  uint16_t local_start[C::kBins];
+  uint32_t scan_warp[32];
+  uint32_t peer_tbl[C::kWarps][32];
+};
+
+enum : int { kInSplit = 0, kInIota = 1, kInRec = 2 };
+enum : int { kOutSplit = 0, kOutRec = 1 };
+
+// Rank of this lane's key among the keys of the warp seen so far with the same
+// digit; bumps the warp's private counter.  wh[d] = (count << 5) | lane tag.
+// The tag read back names one lane per group of equal digits; the lanes of a
+// group OR their bit into that lane's slot of a 32-word table, which is then the
+// group's peer mask: three shared-memory operations instead of one ballot per
+// digit bit.  A warp holding one digit only (coherent input) skips the atomics.
+__device__ __forceinline__ uint32_t warp_rank(volatile uint16_t* wh, volatile uint32_t* peer_tbl,
+                                              uint32_t d, uint32_t lane, uint32_t lt_mask) {
+  const uint32_t c = (uint32_t)wh[d] >> 5;
+  peer_tbl[lane] = 0u;
+  __syncwarp();
+  wh[d] = (uint16_t)(((c + 1u) << 5) | lane);
+  __syncwarp();
+  const uint32_t winner = (uint32_t)wh[d] & 31u;  // one lane id per group of equal digits
+  uint32_t peers;
+  if (__all_sync(kFull, winner == __shfl_sync(kFull, winner, 0))) {
+    peers = kFull;
+  } else {
+    atomicOr(const_cast<uint32_t*>(peer_tbl) + winner, 1u << lane);
+    __syncwarp();
+    peers = peer_tbl[winner];
+  }
+  if ((peers & lt_mask) == 0u) wh[d] = (uint16_t)((c + __popc(peers)) << 5);
+  __syncwarp();
+  return c + __popc(peers & lt_mask);
+}
+
+// IN: kInSplit (keys_in + vals_in), kInIota (keys_in, payload = position),
+//     kInRec (recs_in, 32-bit keys only).   OUT: kOutSplit or kOutRec.
+template <typename KeyT, int BITS, int THREADS, int IPT, int MIN_BLOCKS, int IN, int OUT>
 __global__ void __launch_bounds__(THREADS, MIN_BLOCKS)
-onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
-                const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ vals_out,
-                const uint32_t* __restrict__ digit_base, uint32_t* __restrict__ lookback,
-                uint32_t* __restrict__ tile_counter, uint32_t n, int shift) {
-  using Smem = SortSmem<KeyT, THREADS, IPT>;
-  constexpr int kTile = Smem::kTile;
+scatter_kernel(const KeyT* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
+               const uint2* __restrict__ recs_in, KeyT* __restrict__ keys_out,
+               uint32_t* __restrict__ vals_out, uint2* __restrict__ recs_out,
+               const uint32_t* __restrict__ chunk_offsets, ChunkGeom g, int shift) {
+  using C = SortCfg<KeyT, BITS, THREADS, IPT>;
+  using Smem = SortSmem<KeyT, BITS, THREADS, IPT>;
+  constexpr bool kPacked = Smem::kPacked;
+  static_assert(kPacked || (IN != kInRec && OUT != kOutRec), "records carry 32-bit keys");
+  constexpr int kTile = C::kTile, kBins = C::kBins, kBPT = C::kBPT, kPPT = C::kPPT;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   Smem& sm = *reinterpret_cast<Smem*>(smem_raw);
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  if (tid == 0) sm.tile = atomicAdd(tile_counter, 1u);
-  // each warp clears its private counters
-#pragma unroll
-  for (int b = lane; b < kRadix; b += 32) sm.warp_hist[warp][b] = 0;
-  __syncthreads();
-  const uint32_t tile = sm.tile;
-  const uint32_t tile_base = tile * (uint32_t)kTile;
-  const uint32_t tile_n = min((uint32_t)kTile, n - tile_base);
-  const bool full = (tile_n == (uint32_t)kTile);
-  const uint32_t warp_base = tile_base + (uint32_t)warp * 32u * IPT + lane;
-
-  // ---- 2. keys: warp-striped, coalesced -----------------------------------
-  KeyT key[IPT];
-  if (full) {
-#pragma unroll
-    for (int k = 0; k < IPT; ++k) key[k] = keys_in[warp_base + k * 32];
-  } else {
-#pragma unroll
-    for (int k = 0; k < IPT; ++k) {
-      uint32_t idx = warp_base + k * 32;
-      key[k] = (idx < n) ? keys_in[idx] : ~KeyT(0);
-    }
-  }
-
-  // ---- 3. ranking inside the warp -------------------------------------------
-  uint32_t rank[IPT];
   const uint32_t lt_mask = (1u << lane) - 1u;
-  uint32_t* wh = sm.warp_hist[warp];
-#pragma unroll
-  for (int k = 0; k < IPT; ++k) {
-    const uint32_t d = (uint32_t)(key[k] >> shift) & (kRadix - 1);
-    const uint32_t peers = peers_of<USE_MATCH>(d);
-    const int leader = __ffs(peers) - 1;
-    uint32_t old = 0;
-    if (lane == leader) {
-      old = wh[d];
-      wh[d] = old + __popc(peers);
-    }
-    old = __shfl_sync(0xFFFFFFFFu, old, leader);
-    rank[k] = old + __popc(peers & lt_mask);
-    __syncwarp();
-  }
+  const uint32_t chunk = blockIdx.x;
+  const uint32_t chunk_begin = g.begin(chunk), chunk_end = g.end(chunk);
+  const uint32_t m = chunk_end - chunk_begin;
+  // equal tiles: T = ceil(m / kTile) tiles of `steps` key-steps each
+  const uint32_t n_tiles = (m + kTile - 1) / kTile;
+  const uint32_t per_tile = (m + n_tiles - 1) / n_tiles;
+  const int steps = (int)((per_tile + THREADS - 1) / THREADS);  // <= IPT
+  const uint32_t tile_size = (uint32_t)steps * THREADS;
+  const uint32_t seg = (uint32_t)steps * 32u;  // keys per warp per tile
 
-  // payload: issued now so the loads fly during the look-back
+  // running output position of the owned bins (registers, carried across tiles)
+  const bool owner = tid < C::kOwners;
+  const int bin0 = tid * kBPT;
+  uint32_t run_base[kBPT];
+#pragma unroll
+  for (int i = 0; i < kBPT; ++i)
+    run_base[i] = owner ? chunk_offsets[(size_t)chunk * kBins + bin0 + i] : 0u;
+
+  KeyT key[IPT];
   uint32_t val[IPT];
-  if (IOTA) {
-#pragma unroll
-    for (int k = 0; k < IPT; ++k) val[k] = warp_base + k * 32;
-  } else if (full) {
-#pragma unroll
-    for (int k = 0; k < IPT; ++k) val[k] = vals_in[warp_base + k * 32];
-  } else {
+  // keys (and, for records, payloads) of one tile; out-of-range slots hold all-ones
+  auto load_keys = [&](uint32_t tile_begin) {
+    const uint32_t wb = tile_begin + (uint32_t)warp * seg + lane;
+    const bool whole = (steps == IPT) && (tile_begin + tile_size <= chunk_end);
 #pragma unroll
     for (int k = 0; k < IPT; ++k) {
-      uint32_t idx = warp_base + k * 32;
-      val[k] = (idx < n) ? vals_in[idx] : 0u;
-    }
-  }
-  __syncthreads();
-
-  // ---- 4. per-bin fold, publish, look back -----------------------------------
-  uint32_t total = 0, excl = 0;
-  if (tid < kRadix) {
-#pragma unroll
-    for (int w = 0; w < Smem::kWarps; ++w) {
-      uint32_t c = sm.warp_hist[w][tid];
-      sm.warp_hist[w][tid] = total;
-      total += c;
-    }
-    uint32_t* mine = lookback + (size_t)tile * kRadix + tid;
-    if (tile == 0) {
-      st_relaxed(mine, total | kFlagIncl);
-    } else {
-      st_relaxed(mine, total | kFlagLocal);
-    }
-    // exclusive scan of the tile's bin totals -> position of the bin in the tile
-    uint32_t incl = total;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
-      if (lane >= o) incl += t;
-    }
-    if (lane == 31) sm.scan_warp[warp] = incl;
-    asm volatile("bar.sync 1, 256;" ::: "memory");  // the 256 bin threads only
-    uint32_t off = 0;
-#pragma unroll
-    for (int w = 0; w < 8; ++w) off += (w < warp) ? sm.scan_warp[w] : 0u;
-    const uint32_t lstart = off + incl - total;
-    sm.local_start[tid] = lstart;
-
-    if (tile != 0) {
-      int t = (int)tile - 1;
-      while (true) {
-        uint32_t v = ld_relaxed(lookback + (size_t)t * kRadix + tid);
-        uint32_t flag = v & ~kValueMask;
-        if (flag == 0) continue;  // predecessor has not published yet
-        excl += v & kValueMask;
-        if (flag == kFlagIncl) break;
-        --t;
+      const uint32_t idx = wb + k * 32;
+      const bool ok = whole || (k < steps && idx < chunk_end);
+      if (IN == kInRec) {
+        const uint2 r = ok ? recs_in[idx] : make_uint2(0u, 0xFFFFFFFFu);
+        key[k] = (KeyT)r.y;
+        val[k] = r.x;
+      } else {
+        key[k] = ok ? keys_in[idx] : ~KeyT(0);
       }
-      st_relaxed(mine, (excl + total) | kFlagIncl);
     }
-    sm.bin_base[tid] = digit_base[tid] + excl - lstart;
-  }
-  __syncthreads();
-
-  // ---- 5. tile-local placement, then coalesced write-out ---------------------
-#pragma unroll
-  for (int k = 0; k < IPT; ++k) {
-    const uint32_t d = (uint32_t)(key[k] >> shift) & (kRadix - 1);
-    const uint32_t pos = sm.local_start[d] + wh[d] + rank[k];
-    sm.keys[pos] = key[k];
-    sm.vals[pos] = val[k];
-  }
-  __syncthreads();
-  if (full) {
+  };
+  auto load_vals = [&](uint32_t tile_begin) {
+    const uint32_t wb = tile_begin + (uint32_t)warp * seg + lane;
+    const bool whole = (steps == IPT) && (tile_begin + tile_size <= chunk_end);
 #pragma unroll
     for (int k = 0; k < IPT; ++k) {
-      const uint32_t p = tid + k * THREADS;
-      const KeyT kk = sm.keys[p];
-      const uint32_t d = (uint32_t)(kk >> shift) & (kRadix - 1);
-      const uint32_t dst = sm.bin_base[d] + p;
-      keys_out[dst] = kk;
-      vals_out[dst] = sm.vals[p];
+      const uint32_t idx = wb + k * 32;
+      if (IN == kInIota) val[k] = idx;
+      else if (IN == kInSplit) val[k] = (whole || (k < steps && idx < chunk_end)) ? vals_in[idx] : 0u;
     }
-  } else {
-    for (uint32_t p = tid; p < tile_n; p += THREADS) {
-      const KeyT kk = sm.keys[p];
-      const uint32_t d = (uint32_t)(kk >> shift) & (kRadix - 1);
-      const uint32_t dst = sm.bin_base[d] + p;
-      keys_out[dst] = kk;
-      vals_out[dst] = sm.vals[p];
+  };
+  if (n_tiles) load_keys(chunk_begin);
+
+  for (uint32_t t = 0; t < n_tiles; ++t) {
+    const uint32_t tile_begin = chunk_begin + t * tile_size;
+    const uint32_t tile_n = min(tile_size, chunk_end - tile_begin);
+
+    {  // each warp clears its private counters (32-bit words = two counters)
+      uint32_t* w32 = reinterpret_cast<uint32_t*>(sm.warp_hist[warp]);
+#pragma unroll
+      for (int b = lane; b < kBins / 2; b += 32) w32[b] = 0u;
+      __syncwarp();
     }
+
+    // ---- ranking inside the warp ---------------------------------------------
+    uint32_t rank[IPT];
+    {
+      volatile uint16_t* wh = sm.warp_hist[warp];
+      volatile uint32_t* ptbl = sm.peer_tbl[warp];
+#pragma unroll
+      for (int k = 0; k < IPT; ++k) {
+        if (k < steps) {  // warp-uniform
+          const uint32_t d = (uint32_t)(key[k] >> shift) & (kBins - 1);
+          rank[k] = warp_rank(wh, ptbl, d, (uint32_t)lane, lt_mask);
+        } else {
+          rank[k] = 0u;
+        }
+      }
+    }
+    // payload: issued now so the loads fly during the fold
+    if (IN != kInRec) load_vals(tile_begin);
+    __syncthreads();
+
+    // ---- fold the warp counters, scan the bin totals ---------------------------
+    uint32_t total[kBPT];
+    uint32_t thread_sum = 0;
+    if (owner) {
+      uint32_t run[kPPT];
+#pragma unroll
+      for (int q = 0; q < kPPT; ++q) run[q] = 0u;
+#pragma unroll
+      for (int w = 0; w < C::kWarps; ++w) {
+        uint32_t* w32 = reinterpret_cast<uint32_t*>(sm.warp_hist[w]) + tid * kPPT;
+#pragma unroll
+        for (int q = 0; q < kPPT; ++q) {
+          const uint32_t x = w32[q];
+          w32[q] = run[q];
+          run[q] += (x >> 5) & 0x07FF07FFu;
+        }
+      }
+#pragma unroll
+      for (int q = 0; q < kPPT; ++q) {
+        total[2 * q] = run[q] & 0xFFFFu;
+        total[2 * q + 1] = run[q] >> 16;
+        thread_sum += total[2 * q] + total[2 * q + 1];
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < kBPT; ++i) total[i] = 0u;
+    }
+    {  // block-wide exclusive scan of thread_sum -> tile-local start of every bin
+      uint32_t incl = thread_sum;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        uint32_t v = __shfl_up_sync(kFull, incl, o);
+        if (lane >= o) incl += v;
+      }
+      if (lane == 31) sm.scan_warp[warp] = incl;
+      __syncthreads();
+      uint32_t run = incl - thread_sum;
+#pragma unroll
+      for (int w = 0; w < C::kWarps; ++w) run += (w < warp) ? sm.scan_warp[w] : 0u;
+      if (owner) {
+#pragma unroll
+        for (int i = 0; i < kBPT; ++i) {
+          sm.local_start[bin0 + i] = (uint16_t)run;
+          sm.bin_base[bin0 + i] = run_base[i] - run;
+          run_base[i] += total[i];
+          run += total[i];
+        }
+      }
+    }
+    __syncthreads();
+
+    // ---- tile-local placement ------------------------------------------------------
+    {
+      const uint16_t* wh = sm.warp_hist[warp];
+#pragma unroll
+      for (int k = 0; k < IPT; ++k) {
+        if (k < steps) {
+          const uint32_t d = (uint32_t)(key[k] >> shift) & (kBins - 1);
+          const uint32_t pos = (uint32_t)sm.local_start[d] + (uint32_t)wh[d] + rank[k];
+          if (kPacked) {
+            sm.keys[pos] = ((uint64_t)key[k] << 32) | val[k];
+          } else {
+            sm.keys[pos] = key[k];
+            sm.vals[pos] = val[k];
+          }
+        }
+      }
+    }
+    __syncthreads();
+
+    // next tile's keys travel while this tile is written out
+    if (t + 1 < n_tiles) load_keys(tile_begin + tile_size);
+
+    // ---- coalesced write-out -------------------------------------------------------
+    auto emit = [&](uint32_t p) {
+      const uint64_t kk = sm.keys[p];
+      const uint32_t d = (uint32_t)(kk >> (shift + (kPacked ? 32 : 0))) & (kBins - 1);
+      const uint32_t dst = sm.bin_base[d] + p;
+      if (kPacked) {
+        if (OUT == kOutRec) {
+          recs_out[dst] = make_uint2((uint32_t)kk, (uint32_t)(kk >> 32));
+        } else {
+          keys_out[dst] = (KeyT)(kk >> 32);
+          vals_out[dst] = (uint32_t)kk;
+        }
+      } else {
+        keys_out[dst] = (KeyT)kk;
+        vals_out[dst] = sm.vals[p];
+      }
+    };
+    if (steps == IPT && tile_n == (uint32_t)kTile) {
+#pragma unroll
+      for (int k = 0; k < IPT; ++k) emit(tid + k * THREADS);
+    } else {
+      for (uint32_t p = tid; p < tile_n; p += THREADS) emit(p);
+    }
+    // no barrier here: the next tile's placement sits behind three more barriers
   }
 }
 
-// ---- variants ----------------------------------------------------------------
-struct Variant {
-  int threads, ipt;
+// ---- launchers -----------------------------------------------------------------
+struct Shape {
+  int threads, ipt32, ipt64, ctas_per_sm;
 };
-// index = params().sort_variant; [key width][variant]
-constexpr int kNumVariants = 4;
-constexpr Variant kVariants32[kNumVariants] = {{512, 15}, {384, 18}, {256, 23}, {512, 15}};
-constexpr Variant kVariants64[kNumVariants] = {{512, 10}, {384, 13}, {256, 16}, {512, 10}};
-constexpr int kMinTile32 = 256 * 23, kMinTile64 = 256 * 16;
+// variant 0: 512 threads, 2 CTAs/SM; variant 1: 256 threads, 4 CTAs/SM
+constexpr int kNumVariants = 2;
+constexpr Shape kShapes[kNumVariants] = {{512, 15, 10, 2}, {256, 16, 11, 4}};
 
-template <typename KeyT, int THREADS, int IPT, int MIN_BLOCKS, bool USE_MATCH>
-int launch_pass(const KeyT* kin, KeyT* kout, const uint32_t* vin, uint32_t* vout,
-                const uint32_t* base, uint32_t* lookback, uint32_t* counter, uint32_t n, int shift,
-                bool iota, cudaStream_t s) {
-  using Smem = SortSmem<KeyT, THREADS, IPT>;
-  const uint32_t tiles = (n + Smem::kTile - 1) / Smem::kTile;
-  const size_t smem = sizeof(Smem);
-  if (iota) {
-    auto kern = onesweep_kernel<KeyT, THREADS, IPT, MIN_BLOCKS, true, USE_MATCH>;
-    RT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<tiles, THREADS, smem, s>>>(kin, kout, vin, vout, base, lookback, counter, n, shift);
+int clamp_variant() {
+  int v = params().sort_variant;
+  return (v < 0 || v >= kNumVariants) ? 0 : v;
+}
+
+ChunkGeom make_geom(uint64_t n, uint32_t key_bits) {
+  const Shape& sh = kShapes[clamp_variant()];
+  const uint64_t tile = (uint64_t)sh.threads * (key_bits == 30 ? sh.ipt32 : sh.ipt64);
+  const uint64_t max_ctas = (uint64_t)num_sms() * sh.ctas_per_sm;
+  ChunkGeom g;
+  g.n = (uint32_t)n;
+  const uint64_t tiles = (n + tile - 1) / tile;
+  if (tiles <= max_ctas) {
+    g.chunk_size = (uint32_t)tile;
+    g.chunks = (uint32_t)(tiles ? tiles : 1);
   } else {
-    auto kern = onesweep_kernel<KeyT, THREADS, IPT, MIN_BLOCKS, false, USE_MATCH>;
-    RT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<tiles, THREADS, smem, s>>>(kin, kout, vin, vout, base, lookback, counter, n, shift);
+    uint64_t cs = (n + max_ctas - 1) / max_ctas;
+    cs = (cs + 31) / 32 * 32;
+    g.chunk_size = (uint32_t)cs;
+    g.chunks = (uint32_t)((n + cs - 1) / cs);
   }
+  return g;
+}
+
+struct PassIO {
+  const void* keys_in = nullptr;   // KeyT keys (kInSplit / kInIota)
+  const uint32_t* vals_in = nullptr;
+  const uint2* recs_in = nullptr;  // packed records (kInRec)
+  void* keys_out = nullptr;
+  uint32_t* vals_out = nullptr;
+  uint2* recs_out = nullptr;
+  int in = kInSplit, out = kOutSplit;
+};
+
+template <typename KeyT, int BITS, int THREADS, int IPT, int MIN_BLOCKS, int IN, int OUT>
+int launch_scatter_io(const PassIO& io, const uint32_t* offsets, const ChunkGeom& g, int shift,
+                      cudaStream_t s) {
+  using Smem = SortSmem<KeyT, BITS, THREADS, IPT>;
+  const size_t smem = sizeof(Smem);
+  auto kern = scatter_kernel<KeyT, BITS, THREADS, IPT, MIN_BLOCKS, IN, OUT>;
+  RT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  kern<<<g.chunks, THREADS, smem, s>>>((const KeyT*)io.keys_in, io.vals_in, io.recs_in,
+                                      (KeyT*)io.keys_out, io.vals_out, io.recs_out, offsets, g,
+                                      shift);
   RT_LAUNCHED();
   return 0;
 }
 
-template <typename KeyT>
-int dispatch_pass(int variant, const KeyT* kin, KeyT* kout, const uint32_t* vin, uint32_t* vout,
-                  const uint32_t* base, uint32_t* lookback, uint32_t* counter, uint32_t n,
-                  int shift, bool iota, cudaStream_t s) {
-  constexpr bool k64 = sizeof(KeyT) == 8;
-  switch (variant) {
-    default:
-    case 0:
-      return launch_pass<KeyT, 512, k64 ? 10 : 15, 2, false>(kin, kout, vin, vout, base, lookback,
-                                                            counter, n, shift, iota, s);
-    case 1:
-      return launch_pass<KeyT, 384, k64 ? 13 : 18, 2, false>(kin, kout, vin, vout, base, lookback,
-                                                            counter, n, shift, iota, s);
-    case 2:
-      return launch_pass<KeyT, 256, k64 ? 16 : 23, 3, false>(kin, kout, vin, vout, base, lookback,
-                                                            counter, n, shift, iota, s);
-    case 3:
-      return launch_pass<KeyT, 512, k64 ? 10 : 15, 2, true>(kin, kout, vin, vout, base, lookback,
-                                                             counter, n, shift, iota, s);
+template <typename KeyT, int BITS, int THREADS, int IPT, int MIN_BLOCKS>
+int launch_scatter(const PassIO& io, const uint32_t* offsets, const ChunkGeom& g, int shift,
+                   cudaStream_t s) {
+  if (sizeof(KeyT) == 8) {
+    if (io.in == kInIota)
+      return launch_scatter_io<KeyT, BITS, THREADS, IPT, MIN_BLOCKS, kInIota, kOutSplit>(io, offsets, g, shift, s);
+    return launch_scatter_io<KeyT, BITS, THREADS, IPT, MIN_BLOCKS, kInSplit, kOutSplit>(io, offsets, g, shift, s);
+  } else {
+    // 32-bit keys: first pass builds records, last pass splits them again
+    constexpr bool k32 = sizeof(KeyT) == 4;
+    using K = typename std::conditional<k32, KeyT, uint32_t>::type;
+    if (io.in == kInIota)
+      return launch_scatter_io<K, BITS, THREADS, IPT, MIN_BLOCKS, kInIota, kOutRec>(io, offsets, g, shift, s);
+    if (io.in == kInSplit)
+      return launch_scatter_io<K, BITS, THREADS, IPT, MIN_BLOCKS, kInSplit, kOutRec>(io, offsets, g, shift, s);
+    if (io.out == kOutRec)
+      return launch_scatter_io<K, BITS, THREADS, IPT, MIN_BLOCKS, kInRec, kOutRec>(io, offsets, g, shift, s);
+    return launch_scatter_io<K, BITS, THREADS, IPT, MIN_BLOCKS, kInRec, kOutSplit>(io, offsets, g, shift, s);
   }
+}
+
+template <typename KeyT, int BITS>
+int run_pass(int variant, const PassIO& io, uint32_t* chunk_hist, uint32_t* totals,
+             const ChunkGeom& g, int shift, cudaStream_t s) {
+  constexpr bool k64 = sizeof(KeyT) == 8;
+  constexpr int kBins = 1 << BITS;
+  if (io.in == kInRec)  // the key is the high word of the record
+    chunk_hist_kernel<uint64_t, BITS><<<g.chunks, kHistThreads, 0, s>>>(
+        (const uint64_t*)io.recs_in, g, shift + 32, chunk_hist, totals);
+  else
+    chunk_hist_kernel<KeyT, BITS><<<g.chunks, kHistThreads, 0, s>>>((const KeyT*)io.keys_in, g,
+                                                                   shift, chunk_hist, totals);
+  RT_LAUNCHED();
+  chunk_offsets_kernel<BITS><<<kBins / kOffWarps, kOffWarps * 32, 0, s>>>(chunk_hist, totals, g.chunks);
+  RT_LAUNCHED();
+  if (variant == 1)
+    return launch_scatter<KeyT, BITS, 256, k64 ? 11 : 16, 4>(io, chunk_hist, g, shift, s);
+  return launch_scatter<KeyT, BITS, 512, k64 ? 10 : 15, 2>(io, chunk_hist, g, shift, s);
+}
+
+template <typename KeyT>
+int dispatch_pass(int bits, int variant, const PassIO& io, uint32_t* chunk_hist, uint32_t* totals,
+                  const ChunkGeom& g, int shift, cudaStream_t s) {
+  switch (bits) {
+    case 8: return run_pass<KeyT, 8>(variant, io, chunk_hist, totals, g, shift, s);
+    case 9: return run_pass<KeyT, 9>(variant, io, chunk_hist, totals, g, shift, s);
+    case 10: return run_pass<KeyT, 10>(variant, io, chunk_hist, totals, g, shift, s);
+    case 11: return run_pass<KeyT, 11>(variant, io, chunk_hist, totals, g, shift, s);
+  }
+  return fail(-2, "sort: unsupported digit width %d", bits);
 }
 
 }  // namespace
 
-int sort_num_passes(uint32_t key_bits) { return key_bits == 30 ? 4 : 8; }
+SortPlan sort_plan(uint32_t key_bits) {
+  int bits = params().sort_bits;
+  if (bits < 8 || bits > 11) bits = (key_bits == 30) ? 10 : 9;
+  SortPlan p;
+  p.bits = bits;
+  p.passes = ((int)key_bits + bits - 1) / bits;
+  return p;
+}
 
-// [passes][256] tile counters (one word used per pass, padded) then
-// [passes][tiles_max][256] look-back words
-uint64_t sort_lookback_words(uint64_t n, uint32_t key_bits) {
-  const uint64_t min_tile = key_bits == 30 ? kMinTile32 : kMinTile64;
-  const uint64_t tiles = (n + min_tile - 1) / min_tile;
-  const uint64_t passes = sort_num_passes(key_bits);
-  return passes * kRadix + passes * tiles * kRadix;
+// global bin totals of every pass: [passes][bins]
+uint64_t sort_hist_words(uint32_t key_bits) {
+  const SortPlan p = sort_plan(key_bits);
+  return (uint64_t)p.passes << p.bits;
+}
+
+// per-chunk histograms / offsets of one pass (reused by every pass): [chunks][bins]
+uint64_t sort_chunk_words(uint64_t n, uint32_t key_bits) {
+  const SortPlan p = sort_plan(key_bits);
+  return (uint64_t)make_geom(n, key_bits).chunks << p.bits;
 }
 
 int launch_sort(void* keys, uint64_t n, uint32_t key_bits, const SortWorkspace& ws,
@@ -307,37 +538,53 @@ int launch_sort(void* keys, uint64_t n, uint32_t key_bits, const SortWorkspace& 
   *keys_out = keys;
   *vals_out = ws.vals;
   if (n > ((1ull << 30) - 1)) return fail(-5, "sort: n = %llu beyond 2^30-1", (unsigned long long)n);
-  const int passes = sort_num_passes(key_bits);
   if (n == 0) return 0;
-  int variant = params().sort_variant;
-  if (variant < 0 || variant >= kNumVariants) variant = 0;
-  const uint64_t min_tile = key_bits == 30 ? kMinTile32 : kMinTile64;
-  const uint64_t tiles_max = (n + min_tile - 1) / min_tile;
-  RT_CUDA(cudaMemsetAsync(ws.lookback, 0, ws.lookback_words * sizeof(uint32_t), s));
-  uint32_t* base = ws.hist + (size_t)passes * kRadix;
-  scan_hist_kernel<<<passes, kRadix, 0, s>>>(ws.hist, base);
-  RT_LAUNCHED();
-  uint32_t* counters = ws.lookback;
-  uint32_t* lb = ws.lookback + (size_t)passes * kRadix;
-  for (int p = 0; p < passes; ++p) {
+  const SortPlan plan = sort_plan(key_bits);
+  const int variant = clamp_variant();
+  const uint64_t bins = 1ull << plan.bits;
+  const ChunkGeom g = make_geom(n, key_bits);
+  if (ws.chunk_words < (uint64_t)g.chunks * bins)
+    return fail(-2, "sort: chunk workspace too small");
+  RT_CUDA(cudaMemsetAsync(ws.hist, 0, sort_hist_words(key_bits) * sizeof(uint32_t), s));
+  for (int p = 0; p < plan.passes; ++p) {
     const bool fwd = (p & 1) == 0;
-    const void* kin = fwd ? keys : ws.keys_alt;
-    void* kout = fwd ? ws.keys_alt : keys;
-    const uint32_t* vin = fwd ? ws.vals : ws.vals_alt;
-    uint32_t* vout = fwd ? ws.vals_alt : ws.vals;
-    const bool iota = iota_payload && p == 0;
-    uint32_t* lbp = lb + (size_t)p * tiles_max * kRadix;
+    uint32_t* totals = ws.hist + (size_t)p * bins;
+    PassIO io;
     if (key_bits == 30) {
-      RT_TRY(dispatch_pass<uint32_t>(variant, (const uint32_t*)kin, (uint32_t*)kout, vin, vout,
-                                     base + p * kRadix, lbp, counters + p * kRadix, (uint32_t)n,
-                                     8 * p, iota, s));
+      // keys -> rec_a -> rec_b -> ... -> (keys, vals): records between the passes
+      const bool first = p == 0, last = p == plan.passes - 1;
+      if (first) {
+        io.in = iota_payload ? kInIota : kInSplit;
+        io.keys_in = keys;
+        io.vals_in = ws.vals;
+      } else {
+        io.in = kInRec;
+        io.recs_in = (const uint2*)(fwd ? ws.rec_b : ws.rec_a);
+      }
+      if (last) {
+        io.out = kOutSplit;
+        io.keys_out = keys;
+        io.vals_out = ws.vals;
+      } else {
+        io.out = kOutRec;
+        io.recs_out = (uint2*)(fwd ? ws.rec_a : ws.rec_b);
+      }
+      RT_TRY(dispatch_pass<uint32_t>(plan.bits, variant, io, ws.chunk_hist, totals, g,
+                                     plan.bits * p, s));
     } else {
-      RT_TRY(dispatch_pass<uint64_t>(variant, (const uint64_t*)kin, (uint64_t*)kout, vin, vout,
-                                     base + p * kRadix, lbp, counters + p * kRadix, (uint32_t)n,
-                                     8 * p, iota, s));
+      io.in = (iota_payload && p == 0) ? kInIota : kInSplit;
+      io.keys_in = fwd ? keys : ws.keys_alt;
+      io.keys_out = fwd ? ws.keys_alt : keys;
+      io.vals_in = fwd ? ws.vals : ws.vals_alt;
+      io.vals_out = fwd ? ws.vals_alt : ws.vals;
+      RT_TRY(dispatch_pass<uint64_t>(plan.bits, variant, io, ws.chunk_hist, totals, g,
+                                     plan.bits * p, s));
     }
   }
-  // passes is even (4 or 8): the result is back in the caller's buffers
+  if (key_bits != 30 && (plan.passes & 1)) {  // odd pass count: result in the partner buffers
+    *keys_out = ws.keys_alt;
+    *vals_out = ws.vals_alt;
+  }
   return 0;
 }
 

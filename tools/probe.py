@@ -60,7 +60,8 @@ def main():
         if name == "sort":
             for key_bits in (30, 63):
                 for n in (1000000, 10000000):
-                    for variant in range(4):
+                    for bits, variant in [(8, 0), (10, 0), (10, 1), (11, 0), (11, 1), (9, 0), (9, 1), (8, 1)]:
+                        g.set_param("sort.bits", bits)
                         g.set_param("sort.variant", variant)
                         ts = []
                         for rep in range(4):
@@ -72,10 +73,25 @@ def main():
                             v = torch.arange(n, device="cuda", dtype=torch.int32)
                             ts.append(g.sort_pairs(k, v, key_bits))
                         ms = min(ts)
-                        alg = n * (64 if key_bits == 30 else 192)  # passes x (r+w) x (key+idx), no histogram
-                        emit(probe="sort", key_bits=key_bits, n=n, variant=variant, ms=ms,
+                        alg = n * (68 if key_bits == 30 else 200)  # SURVEY 8d figure for A3
+                        emit(probe="sort", key_bits=key_bits, n=n, bits=bits, variant=variant, ms=ms,
                              gpairs_s=n / ms / 1e6, alg_gbs=alg / ms / 1e6)
             g.set_param("sort.variant", 0)
+            g.set_param("sort.bits", 0)
+            continue
+        if name.startswith("sortscene:"):
+            sc = name.split(":")[1]
+            tris = scene(sc)
+            for key_bits in (30, 63):
+                for bits, variant in [(8, 0), (8, 1), (9, 0), (9, 1), (10, 0), (10, 1), (11, 0), (11, 1)]:
+                    g.set_param("sort.bits", bits)
+                    g.set_param("sort.variant", variant)
+                    t = time_build(tris, key_bits, reps=4)
+                    emit(probe="sortscene", scene=sc, key_bits=key_bits, bits=bits, variant=variant,
+                         sort_ms=t["sort"], morton_ms=t["morton"], total_ms=t["total"])
+            g.set_param("sort.variant", 0)
+            g.set_param("sort.bits", 0)
+            del tris
             continue
         t0 = time.time()
         tris = scene(name)
