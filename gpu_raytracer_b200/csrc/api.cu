@@ -161,9 +161,12 @@ struct rt_bvh {
   Node* nodes = nullptr;
   SortedTri* stris = nullptr;
   BvhHeader* header = nullptr;
-  uint32_t* parent = nullptr;
+  // parent words: derived from the nodes on first use (refit_bvh, bvh_read_topology/boxes)
+  mutable uint32_t* parent = nullptr;
+  mutable std::mutex parent_mu;
   void* keys = nullptr;  // only with RT_BUILD_KEEP_KEYS
   float bounds[6] = {0, 0, 0, 0, 0, 0};
+  int root = 0;  // node id where traversal starts (header.root_node)
   float times[RT_STAGE_COUNT] = {0, 0, 0, 0, 0, 0};
   bool has_times = false;
   uint64_t bytes = 0;
@@ -187,16 +190,29 @@ void release(rt_bvh* h) {
   delete h;
 }
 
+// parent words of a finished tree, derived once per handle (current device = h->device)
+int ensure_parents(const rt_bvh* h, cudaStream_t s) {
+  std::lock_guard<std::mutex> lock(h->parent_mu);
+  if (h->parent || h->n == 0) return 0;
+  uint32_t* p = nullptr;
+  RT_CUDA(cudaMallocAsync((void**)&p, (2 * h->n - 1) * sizeof(uint32_t), s));
+  int rc = launch_derive_parents(h->nodes, h->n, h->root, p, s);
+  if (rc != 0) {
+    cudaFreeAsync(p, s);
+    return rc;
+  }
+  h->parent = p;
+  return 0;
+}
+
 int alloc_handle_buffers(rt_bvh* h, bool keep_keys, cudaStream_t s) {
   const uint64_t n = h->n;
   const size_t node_bytes = (n > 1 ? (n - 1) : 1) * sizeof(Node);
   const size_t tri_bytes = (n ? n : 1) * sizeof(SortedTri);
-  const size_t parent_bytes = (n ? (2 * n - 1) : 1) * sizeof(uint32_t);
   RT_CUDA(cudaMallocAsync((void**)&h->nodes, node_bytes, s));
   RT_CUDA(cudaMallocAsync((void**)&h->stris, tri_bytes, s));
   RT_CUDA(cudaMallocAsync((void**)&h->header, sizeof(BvhHeader), s));
-  RT_CUDA(cudaMallocAsync((void**)&h->parent, parent_bytes, s));
-  h->bytes = node_bytes + tri_bytes + sizeof(BvhHeader) + parent_bytes;
+  h->bytes = node_bytes + tri_bytes + sizeof(BvhHeader);
   if (keep_keys) {
     RT_CUDA(cudaMallocAsync(&h->keys, (n ? n : 1) * key_size(h->key_bits), s));
     h->bytes += (n ? n : 1) * key_size(h->key_bits);
@@ -280,10 +296,9 @@ int build_impl(rt_bvh* h, const float* tris_in, uint32_t flags, cudaStream_t s) 
   uint32_t* svals = nullptr;
   RT_TRY(launch_sort(keys, n, h->key_bits, ws, /*iota_payload=*/true, &skeys, &svals, s));
   RT_TRY(mark(3));
-  RT_TRY(launch_karras(skeys, n, h->key_bits, h->parent, s));
-  RT_TRY(mark(4));
-  RT_TRY(launch_refit(tris, svals, n, h->parent, (uint32_t*)flags_buf, h->nodes, h->stris,
-                      h->header, queue_buf, s));
+  RT_TRY(mark(4));  // A4 is fused into the bottom-up pass: the topology stage is empty
+  RT_TRY(launch_build_tree(tris, svals, skeys, h->key_bits, n, (uint32_t*)flags_buf, h->nodes,
+                           h->stris, h->header, queue_buf, s));
   RT_TRY(mark(5));
   if (h->keys) RT_CUDA(cudaMemcpyAsync(h->keys, skeys, n * ksz, cudaMemcpyDeviceToDevice, s));
   RT_CUDA(cudaMemcpyAsync(&hdr, h->header, sizeof(hdr), cudaMemcpyDeviceToHost, s));
@@ -292,6 +307,7 @@ int build_impl(rt_bvh* h, const float* tris_in, uint32_t flags, cudaStream_t s) 
     h->bounds[k] = hdr.root_min[k];
     h->bounds[3 + k] = hdr.root_max[k];
   }
+  h->root = (int)hdr.root_node;
   if (timed) {
     for (int i = 0; i < 5; ++i) RT_CUDA(cudaEventElapsedTime(&h->times[i], ev[i], ev[i + 1]));
     RT_CUDA(cudaEventElapsedTime(&h->times[RT_STAGE_TOTAL], ev[0], ev[5]));
@@ -361,6 +377,7 @@ extern "C" int refit_bvh(rt_bvh* h, const float* tris_in) {
   RT_TRY(tmp.alloc(&flags_buf, (h->n > 1 ? h->n - 1 : 1) * 4));
   void* queue_buf = nullptr;
   RT_TRY(tmp.alloc(&queue_buf, refit_queue_bytes(h->n)));
+  RT_TRY(ensure_parents(h, s));
   RT_TRY(launch_refit_update(tris, h->n, h->parent, (uint32_t*)flags_buf, h->nodes, h->stris,
                              h->header, queue_buf, s));
   BvhHeader hdr;
@@ -370,6 +387,7 @@ extern "C" int refit_bvh(rt_bvh* h, const float* tris_in) {
     h->bounds[k] = hdr.root_min[k];
     h->bounds[3 + k] = hdr.root_max[k];
   }
+  h->root = (int)hdr.root_node;
   return RT_OK;
 }
 
@@ -413,7 +431,7 @@ int trace_device(const rt_bvh* h, const float4* rays, uint64_t n_rays, uint32_t 
                  float4* hits, cudaStream_t s) {
   unsigned long long* counter = nullptr;
   RT_CUDA(cudaMallocAsync((void**)&counter, sizeof(unsigned long long), s));
-  int rc = launch_trace(h->nodes, h->stris, h->n, rays, n_rays, flags, hits, counter, s);
+  int rc = launch_trace(h->nodes, h->stris, h->n, h->root, rays, n_rays, flags, hits, counter, s);
   cudaFreeAsync(counter, s);
   return rc;
 }
@@ -449,7 +467,7 @@ int trace_staged(const rt_bvh* h, const float* rays, bool rays_dev, uint64_t n_r
       if (c >= 2) RT_CUDA(cudaStreamWaitEvent(p.s_run, p.ev_out[b], 0));  // slot drained
       hdst = p.hits[b];
     }
-    RT_TRY(launch_trace(h->nodes, h->stris, h->n, rsrc, cnt, flags, hdst, p.counters + b, p.s_run));
+    RT_TRY(launch_trace(h->nodes, h->stris, h->n, h->root, rsrc, cnt, flags, hdst, p.counters + b, p.s_run));
     RT_CUDA(cudaEventRecord(p.ev_run[b], p.s_run));
     if (!hits_dev) {
       RT_CUDA(cudaStreamWaitEvent(p.s_out, p.ev_run[b], 0));
@@ -525,7 +543,7 @@ extern "C" int trace_rays_stats(const rt_bvh* h, const float* rays, uint64_t n_r
   RT_TRY(tmp.alloc(&d, 3 * sizeof(unsigned long long)));
   RT_CUDA(cudaMemsetAsync(d, 0, 3 * sizeof(unsigned long long), s));
   unsigned long long* dc = (unsigned long long*)d;
-  RT_TRY(launch_trace(h->nodes, h->stris, h->n, reinterpret_cast<const float4*>(rays), n_rays,
+  RT_TRY(launch_trace(h->nodes, h->stris, h->n, h->root, reinterpret_cast<const float4*>(rays), n_rays,
                       flags, reinterpret_cast<float4*>(hits), dc + 2, s, dc));
   unsigned long long host[2] = {0, 0};
   RT_CUDA(cudaMemcpyAsync(host, dc, sizeof(host), cudaMemcpyDeviceToHost, s));
@@ -591,6 +609,7 @@ int read_canonical(const rt_bvh* h, uint32_t* left, uint32_t* right, uint32_t* p
   if (right) RT_TRY(tmp.alloc(&dr, (n - 1) * 4));
   if (parent) RT_TRY(tmp.alloc(&dp, nodes * 4));
   if (boxes) RT_TRY(tmp.alloc(&db, nodes * 24));
+  RT_TRY(ensure_parents(h, s));
   RT_TRY(launch_export_topology(h->nodes, h->parent, n, (uint32_t*)dl, (uint32_t*)dr,
                                 (uint32_t*)dp, (float*)db, h->header, s));
   if (left && n > 1) RT_CUDA(cudaMemcpyAsync(left, dl, (n - 1) * 4, cudaMemcpyDeviceToHost, s));
@@ -674,6 +693,7 @@ extern "C" int bvh_commit(rt_bvh* h) {
     h->bounds[k] = hdr.root_min[k];
     h->bounds[3 + k] = hdr.root_max[k];
   }
+  h->root = (int)hdr.root_node;
   return RT_OK;
 }
 

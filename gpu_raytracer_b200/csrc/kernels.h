@@ -8,9 +8,12 @@ namespace rt {
 
 // One BVH2 node, 64 bytes: the boxes of both children plus their ids, so that
 // one node fetch (two 32-byte sectors) feeds two slab tests.
-//   lo0 = child0.min.xyz, child0 id bits     hi0 = child0.max.xyz, 0
-//   lo1 = child1.min.xyz, child1 id bits     hi1 = child1.max.xyz, 0
-// child id: >= 0 internal node index, < 0 leaf (~sorted position).
+//   lo0 = child0.min.xyz, child0 id bits     hi0 = child0.max.xyz, first leaf of child0
+//   lo1 = child1.min.xyz, child1 id bits     hi1 = child1.max.xyz, last leaf of child1
+// child id: >= 0 internal node index, < 0 leaf (~sorted position).  A node's index
+// is its split position g: child0 ends at sorted leaf g, child1 starts at g+1
+// (refit.cu); the root's index is in the header.  hi0.w / hi1.w are the node's leaf
+// range [L, R], ignored by traversal.
 struct __align__(64) Node {
   float4 lo0, hi0, lo1, hi1;
 };
@@ -27,13 +30,14 @@ struct BvhHeader {
   float root_max[3];
   uint32_t n_tris_hi;
   uint32_t key_bits;
-  uint32_t pad[7];
+  uint32_t root_node;  // id of the root: a split position, or ~0 when the root is the one leaf
+  uint32_t pad[6];
 };
 
-// parent word: (parent internal index << 2) | (local << 1) | slot; kNoParent for
-// the root.  slot 0 = left child.  local = 1 when the parent's whole leaf range
-// lies inside one aligned group of kRefitLeaves leaves, i.e. inside the CTA that
-// refits those leaves, which may then use shared memory and CTA-scope fences.
+// parent word: (parent node id << 2) | (local << 1) | slot; kNoParent for the root.
+// slot 0 = left child.  local = 1 when the two children met in the shared memory
+// of one refit CTA while the tree was built (both leaf ranges inside one aligned
+// group of kRefitLeaves leaves); refit_bvh then meets there again.
 constexpr uint32_t kNoParent = 0xFFFFFFFFu;
 constexpr int kRefitLeavesLog2 = 10;
 constexpr int kRefitLeaves = 1 << kRefitLeavesLog2;
@@ -81,13 +85,17 @@ uint64_t sort_chunk_words(uint64_t n, uint32_t key_bits);
 int launch_sort(void* keys, uint64_t n, uint32_t key_bits, const SortWorkspace& ws,
                 bool iota_payload, void** keys_out, uint32_t** vals_out, cudaStream_t s);
 
-int launch_karras(const void* keys, uint64_t n, uint32_t key_bits, uint32_t* parent,
-                  cudaStream_t s);
-// flags: n-1 u32, zeroed by the launcher.  Writes nodes, sorted tris, header box.
-int launch_refit(const float4* tris, const uint32_t* sorted_idx, uint64_t n,
-                 const uint32_t* parent, uint32_t* flags, Node* nodes, SortedTri* stris,
-                 BvhHeader* header, void* queue_buf, cudaStream_t s);
-// bytes of the continuation queue launch_refit needs (queue_buf)
+// A4 + A5 fused: topology, triangle reorder, boxes (refit.cu).  keys: the sorted Morton
+// codes; flags: n-1 u32, zeroed by the launcher.  Writes nodes (indexed by split
+// position), sorted tris, header box and root id.
+int launch_build_tree(const float4* tris, const uint32_t* sorted_idx, const void* keys,
+                      uint32_t key_bits, uint64_t n, uint32_t* flags, Node* nodes,
+                      SortedTri* stris, BvhHeader* header, void* queue_buf, cudaStream_t s);
+// parent words (2n-1 u32) from the finished nodes; needed by launch_refit_update and
+// launch_export_topology only, so the handle derives them on first use
+int launch_derive_parents(const Node* nodes, uint64_t n, int root, uint32_t* parent,
+                          cudaStream_t s);
+// bytes of the continuation queue launch_build_tree / launch_refit_update need (queue_buf)
 size_t refit_queue_bytes(uint64_t n);
 // refit with moved vertices: the primitive index comes from stris[j].v0p.w
 int launch_refit_update(const float4* tris, uint64_t n, const uint32_t* parent, uint32_t* flags,
@@ -102,7 +110,8 @@ int launch_unpack_sorted(const SortedTri* stris, uint64_t n, uint32_t* idx, cuda
 int launch_widen_keys(const uint32_t* in, uint64_t n, uint64_t* out, cudaStream_t s);
 
 // ---- traversal (traverse.cu) -------------------------------------------------
-int launch_trace(const Node* nodes, const SortedTri* stris, uint64_t n_tris, const float4* rays,
+int launch_trace(const Node* nodes, const SortedTri* stris, uint64_t n_tris, int root,
+                 const float4* rays,
                  uint64_t n_rays, uint32_t flags, float4* hits, unsigned long long* ray_counter,
                  cudaStream_t s, unsigned long long* stats = nullptr);
 

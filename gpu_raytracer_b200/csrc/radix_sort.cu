@@ -122,11 +122,29 @@ chunk_offsets_kernel(uint32_t* __restrict__ chunk_hist, const uint32_t* __restri
     const uint32_t c = (uint32_t)lane + 32u * j;
     v[j] = (j < rounds && c < chunks) ? chunk_hist[(size_t)c * kBins + bin] : 0u;
   }
-  // start of the bin: totals of all lower bins
-  uint32_t run = 0;
-  for (int b = lane; b < bin; b += 32) run += totals[b];
+  // start of the bin: totals of all lower bins, summed by the whole CTA at once
+  __shared__ uint32_t s_part[kOffWarps];
+  __shared__ uint32_t s_tot[kOffWarps];
+  {
+    constexpr int kPer = (kBins + kOffWarps * 32 - 1) / (kOffWarps * 32);
+    const int first_bin = blockIdx.x * kOffWarps;
+    uint32_t part = 0;
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) run += __shfl_xor_sync(kFull, run, o);
+    for (int i = 0; i < kPer; ++i) {
+      const int b = (int)threadIdx.x + i * kOffWarps * 32;
+      if (b < first_bin) part += totals[b];
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(kFull, part, o);
+    if (lane == 0) {
+      s_part[warp] = part;
+      s_tot[warp] = totals[bin];
+    }
+  }
+  __syncthreads();
+  uint32_t run = 0;
+#pragma unroll
+  for (int w = 0; w < kOffWarps; ++w) run += s_part[w] + ((w < warp) ? s_tot[w] : 0u);
 #pragma unroll
   for (int j = 0; j < kOffMaxRounds; ++j) {
     if (j < rounds) {  // warp-uniform

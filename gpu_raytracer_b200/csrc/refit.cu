@@ -1,25 +1,40 @@
-// refit.cu — A5: leaf boxes, triangle reorder and the atomic-flag bottom-up
-// AABB refit, plus the kernels that turn the traversal
-// layout back into the canonical arrays the parity tests compare.
+// refit.cu — A4 + A5 in one bottom-up pass: radix-tree topology, leaf boxes,
+// triangle reorder and the AABB refit, plus the
+// table-driven refit of refit_bvh and the kernels that turn the traversal layout
+// back into the canonical arrays the parity tests compare.
 //
-// One thread per leaf.  It gathers its triangle through the sorted index,
-// stores it in traversal form {v0 | prim, e1, e2} at its sorted position, then
-// walks up: it writes the box it carries (and its own child id) into its slot
-// of the parent's 64-byte node — one full 32-byte sector — and bumps the
-// parent's counter.  The first arriver stops; the second unions with the
-// sibling's box and continues.  A CTA owns kRefitLeaves = 1024 consecutive
-// leaves; ~97 % of all internal nodes have their whole leaf range inside one
-// CTA (karras.cu marks them), and for those the counter and the deposited boxes
-// live in shared memory with CTA-scope fences.  Only nodes that straddle CTAs
-// use the device-scope protocol: global counter, __threadfence, sibling slot
-// re-read from L2 (ld.cg).  ncu on the first version showed 55 % of the stall
-// samples on MEMBAR.GPU; this removes them from all but the top of the tree.
-// A walker that reaches such a node does not climb on inside its 1024-thread
-// CTA (which would stay resident for one thread): it parks {box, id, parent
-// word} in a queue and refit_top_kernel, one dense thread per parked walker,
-// finishes the top ~3 % of the tree.  10M triangles: 1.02 ms -> 0.60 ms.  Every node slot is written exactly once and read at most
-// once: ~96 B per internal node against the 112 B of the textbook layout.
-// The walker that leaves the root stores the scene box in the header.
+// Topology without searches (Apetrei 2014).  A finished node covers the sorted
+// leaves [L, R].  With delta(i) = common-prefix length of the (index-augmented)
+// keys i and i+1, its parent merges it with the neighbour it shares the longer
+// prefix with: delta(R) > delta(L-1) makes it the LEFT child of the node that
+// splits after R, otherwise the RIGHT child of the node that splits after L-1.
+// Two children meet at their split position g, so the rendezvous counter, and
+// the 64-byte node itself, are indexed by g ("split numbering").  This is the
+// same tree as Karras 2012: the Karras index of the child in slot s of node g is
+// g + s, the root is Karras node 0, which is how export_kernel produces the
+// canonical arrays.  A top-down Karras kernel (two binary searches per node, 11
+// of 32 lanes active on average) used to take 0.28 ms for 10M leaves before the
+// refit even started; here the topology costs two byte loads per climb step.
+//
+// One thread per leaf, one CTA per kRefitLeaves = 1024 consecutive leaves.  The
+// thread gathers its triangle through the sorted index, stores it in traversal
+// form {v0 | prim, e1, e2}, then climbs: it writes the box it carries (child
+// id, far end of its range) into its slot of node g — one full 32-byte sector —
+// and meets its sibling.
+//   phase 1  meetings whose split lies inside the CTA's leaf group happen in
+//            shared memory with CTA-scope fences: deposit, atomicOr, first
+//            arriver stops, second unions and climbs on.  No global atomics, no
+//            MEMBAR.GPU (55 % of the stall samples of the first version).
+//   phase 2  after a CTA barrier, a slot that saw only one child means the
+//            sibling lives in another CTA: that child, and every walker whose
+//            next split falls on a group boundary, is parked in a queue.
+//   top      refit_top_kernel, one dense thread per parked walker, finishes
+//            the upper ~3 % of the tree with the device-scope protocol (global
+//            counter, __threadfence, sibling slot re-read from L2 with ld.cg).
+// Second arrivers also record the parent word of both children (8 B per node),
+// which is all refit_bvh needs to re-run the boxes later without keys.
+// The walker that completes [0, n-1] stores the scene box and the root id in
+// the header.
 //
 // min/max use the total order on bit patterns, so boxes are exact and
 // independent of which thread arrives first.
@@ -42,13 +57,48 @@ struct Box {
   float lx, ly, lz, hx, hy, hz;
 };
 
-// Shared state of one CTA = kRefitLeaves consecutive leaves: arrival counters and
-// deposited child boxes of the internal nodes whose leaf range lies inside the
-// CTA (index = node id - first leaf of the CTA; a Karras node id is one end of
-// its own range, so it falls in the same window).
+// CTA-scope release/acquire folded into the arrival atomic itself: the deposit
+// written before it is visible to whoever sees the bit, and what the sibling
+// deposited is visible after it.  (A separate __threadfence_block() compiles to
+// MEMBAR.SC.CTA, which also waits for the walker's outstanding global stores.)
+__device__ __forceinline__ uint32_t arrive_or_cta(uint32_t* flag, uint32_t bit) {
+  uint32_t old;
+  asm volatile("atom.acq_rel.cta.shared.or.b32 %0, [%1], %2;"
+               : "=r"(old)
+               : "r"((uint32_t)__cvta_generic_to_shared(flag)), "r"(bit)
+               : "memory");
+  return old;
+}
+__device__ __forceinline__ uint32_t arrive_add_cta(uint32_t* flag) {
+  uint32_t old;
+  asm volatile("atom.acq_rel.cta.shared.add.u32 %0, [%1], 1;"
+               : "=r"(old)
+               : "r"((uint32_t)__cvta_generic_to_shared(flag))
+               : "memory");
+  return old;
+}
+__device__ __forceinline__ float4 lds_volatile_v4(const void* p) {
+  float4 r;
+  asm volatile("ld.volatile.shared.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+               : "r"((uint32_t)__cvta_generic_to_shared(p))
+               : "memory");
+  return r;
+}
+
+// Shared state of one CTA = kRefitLeaves consecutive leaves: arrival bits and
+// deposited children of the nodes whose split position lies inside the group
+// (index = split position - first leaf of the CTA).
+struct __align__(16) Deposit {
+  float lx, ly, lz;
+  int child_enc;
+  float hx, hy, hz;
+  uint32_t far_end;  // the end of the child's leaf range away from the split
+};
 struct RefitSmem {
+  Deposit dep[kRefitLeaves][2];
   uint32_t flag[kRefitLeaves];
-  float box[kRefitLeaves][2][6];
+  uint8_t delta[kRefitLeaves + 8];  // delta(base - 1 + t), t in [0, kRefitLeaves]
 };
 
 // A walker that leaves its CTA's group parks here instead of keeping a 1024-thread
@@ -57,10 +107,193 @@ struct __align__(16) Continuation {
   float lx, ly, lz;
   int child_enc;
   float hx, hy, hz;
-  uint32_t pword;
+  uint32_t pword;  // table-driven refit: parent word.  build: unused
+  uint32_t L, R, pad0, pad1;
 };
-constexpr int kContPerCta = 64;  // queue capacity per leaf CTA; overflow climbs inline
+constexpr int kContPerCta = 96;  // queue capacity per leaf CTA; overflow climbs inline
 
+__device__ __forceinline__ uint32_t node_slot_of(int child_enc, uint32_t n) {
+  return child_enc < 0 ? (n - 1u) + (uint32_t)(~child_enc) : (uint32_t)child_enc;
+}
+
+// common-prefix length of the augmented keys i and i+1 (i + 1 < n)
+template <typename KeyT>
+__device__ __forceinline__ uint32_t delta_adj(KeyT a, KeyT b, uint32_t i) {
+  if (sizeof(KeyT) == 4) {
+    const uint32_t x = (uint32_t)a ^ (uint32_t)b;
+    return x ? (uint32_t)__clz((int)x) : 32u + (uint32_t)__clz((int)(i ^ (i + 1u)));
+  } else {
+    const uint64_t x = (uint64_t)a ^ (uint64_t)b;
+    return x ? (uint32_t)__clzll((long long)x) : 64u + (uint32_t)__clz((int)(i ^ (i + 1u)));
+  }
+}
+
+__device__ __forceinline__ void store_root(const Box& bx, int enc, BvhHeader* header) {
+  header->root_min[0] = bx.lx; header->root_min[1] = bx.ly; header->root_min[2] = bx.lz;
+  header->root_max[0] = bx.hx; header->root_max[1] = bx.hy; header->root_max[2] = bx.hz;
+  header->root_node = (uint32_t)enc;
+}
+
+// ---- build: device-scope climb with on-the-fly topology -------------------------
+template <typename KeyT>
+__device__ __forceinline__ void climb_build_global(Box bx, int enc, uint32_t L, uint32_t R,
+                                                   const KeyT* __restrict__ keys, uint32_t n,
+                                                   uint32_t* __restrict__ flags,
+                                                   Node* __restrict__ nodes,
+                                                   BvhHeader* __restrict__ header) {
+  while (true) {
+    if (L == 0u && R == n - 1u) {
+      store_root(bx, enc, header);
+      return;
+    }
+    bool left = (L == 0u);
+    if (!left && R != n - 1u) {
+      const uint32_t dr = delta_adj<KeyT>(__ldg(keys + R), __ldg(keys + R + 1), R);
+      const uint32_t dl = delta_adj<KeyT>(__ldg(keys + L - 1), __ldg(keys + L), L - 1);
+      left = dr > dl;
+    }
+    const uint32_t g = left ? R : L - 1u, slot = left ? 0u : 1u;
+    float4* np = reinterpret_cast<float4*>(nodes + g);
+    np[2 * slot] = make_float4(bx.lx, bx.ly, bx.lz, __int_as_float(enc));
+    np[2 * slot + 1] = make_float4(bx.hx, bx.hy, bx.hz, __uint_as_float(left ? L : R));
+    __threadfence();
+    if (atomicAdd(flags + g, 1u) == 0u) return;
+    // acquire side: the loads below are issued only after the atomic's result is
+    // known (control dependency) and go to L2 (ld.cg), where the sibling's
+    // fenced stores already are
+    const float4 slo = ld_cg(np + 2 * (slot ^ 1u));
+    const float4 shi = ld_cg(np + 2 * (slot ^ 1u) + 1);
+    bx.lx = omin(bx.lx, slo.x); bx.ly = omin(bx.ly, slo.y); bx.lz = omin(bx.lz, slo.z);
+    bx.hx = omax(bx.hx, shi.x); bx.hy = omax(bx.hy, shi.y); bx.hz = omax(bx.hz, shi.z);
+    if (left) R = __float_as_uint(shi.w); else L = __float_as_uint(shi.w);
+    enc = (int)g;
+  }
+}
+
+template <typename KeyT>
+__global__ void __launch_bounds__(256)
+build_top_kernel(const Continuation* __restrict__ queue, const uint32_t* __restrict__ queue_count,
+                 uint32_t capacity, const KeyT* __restrict__ keys, uint32_t n,
+                 uint32_t* __restrict__ flags, Node* __restrict__ nodes,
+                 BvhHeader* __restrict__ header) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t count = min(*queue_count, capacity);
+  if (i >= count) return;
+  const float4 a = reinterpret_cast<const float4*>(queue + i)[0];
+  const float4 b = reinterpret_cast<const float4*>(queue + i)[1];
+  const uint4 c = reinterpret_cast<const uint4*>(queue + i)[2];
+  Box bx{a.x, a.y, a.z, b.x, b.y, b.z};
+  climb_build_global<KeyT>(bx, __float_as_int(a.w), c.x, c.y, keys, n, flags, nodes, header);
+}
+
+template <typename KeyT>
+__device__ __forceinline__ void park_or_climb(const Box& bx, int enc, uint32_t L, uint32_t R,
+                                              Continuation* __restrict__ queue,
+                                              uint32_t* __restrict__ queue_count, uint32_t capacity,
+                                              const KeyT* __restrict__ keys, uint32_t n,
+                                              uint32_t* __restrict__ flags, Node* __restrict__ nodes,
+                                              BvhHeader* __restrict__ header) {
+  const uint32_t q = atomicAdd(queue_count, 1u);
+  if (q < capacity) {
+    float4* dst = reinterpret_cast<float4*>(queue + q);
+    dst[0] = make_float4(bx.lx, bx.ly, bx.lz, __int_as_float(enc));
+    dst[1] = make_float4(bx.hx, bx.hy, bx.hz, 0.0f);
+    reinterpret_cast<uint4*>(dst)[2] = make_uint4(L, R, 0u, 0u);
+  } else {
+    climb_build_global<KeyT>(bx, enc, L, R, keys, n, flags, nodes, header);  // queue full
+  }
+}
+
+template <typename KeyT>
+__global__ void __launch_bounds__(kRefitLeaves)
+build_walk_kernel(const float4* __restrict__ tris, const uint32_t* __restrict__ sorted_idx,
+                  const KeyT* __restrict__ keys, uint32_t n, uint32_t* __restrict__ flags,
+                  Node* __restrict__ nodes,
+                  SortedTri* __restrict__ stris, BvhHeader* __restrict__ header,
+                  Continuation* __restrict__ queue, uint32_t* __restrict__ queue_count,
+                  uint32_t capacity) {
+  extern __shared__ __align__(16) unsigned char refit_smem_raw[];
+  RefitSmem& sm = *reinterpret_cast<RefitSmem*>(refit_smem_raw);
+  const uint32_t tid = threadIdx.x;
+  const uint32_t base = blockIdx.x * kRefitLeaves;
+  const uint32_t j = base + tid;
+  sm.flag[tid] = 0;
+  // delta(i) for i = base - 1 + t: thread t owns slot t, thread 0 also the last one
+  {
+    const uint32_t i = j - 1u;  // wraps for j == 0: guarded
+    if (j >= 1u && j < n) sm.delta[tid] = (uint8_t)delta_adj<KeyT>(keys[i], keys[j], i);
+    if (tid == 0) {
+      const uint32_t e = base + kRefitLeaves;  // delta(e - 1)
+      if (e < n) sm.delta[kRefitLeaves] = (uint8_t)delta_adj<KeyT>(keys[e - 1], keys[e], e - 1);
+    }
+  }
+  Box bx;
+  int enc = ~(int)j;
+  uint32_t L = j, R = j;
+  bool alive = j < n;
+  if (alive) {
+    const uint32_t prim = sorted_idx[j];
+    const float4 a = __ldg(tris + 3 * (uint64_t)prim), b = __ldg(tris + 3 * (uint64_t)prim + 1),
+                 c = __ldg(tris + 3 * (uint64_t)prim + 2);
+    float4* st = reinterpret_cast<float4*>(stris + j);
+    st[0] = make_float4(a.x, a.y, a.z, __uint_as_float(prim));
+    st[1] = make_float4(b.x - a.x, b.y - a.y, b.z - a.z, 0.0f);
+    st[2] = make_float4(c.x - a.x, c.y - a.y, c.z - a.z, 0.0f);
+    bx.lx = omin(omin(a.x, b.x), c.x); bx.ly = omin(omin(a.y, b.y), c.y); bx.lz = omin(omin(a.z, b.z), c.z);
+    bx.hx = omax(omax(a.x, b.x), c.x); bx.hy = omax(omax(a.y, b.y), c.y); bx.hz = omax(omax(a.z, b.z), c.z);
+  }
+  __syncthreads();
+
+  // ---- phase 1: meetings inside the group, in shared memory -----------------------
+  while (alive) {
+    if (L == 0u && R == n - 1u) {
+      store_root(bx, enc, header);
+      break;
+    }
+    // L >= base and R < base + kRefitLeaves hold for every walker in this loop
+    bool left = (L == 0u);
+    if (!left && R != n - 1u) left = sm.delta[R - base + 1u] > sm.delta[L - base];
+    const uint32_t g = left ? R : L - 1u, slot = left ? 0u : 1u;
+    const float4 my_lo = make_float4(bx.lx, bx.ly, bx.lz, __int_as_float(enc));
+    const float4 my_hi = make_float4(bx.hx, bx.hy, bx.hz, __uint_as_float(left ? L : R));
+    float4* np = reinterpret_cast<float4*>(nodes + g) + 2 * slot;
+    if (g < base || g + 1u >= base + kRefitLeaves) {
+      // the sibling starts or ends in another group: device-scope meeting
+      park_or_climb<KeyT>(bx, enc, L, R, queue, queue_count, capacity, keys, n, flags, nodes,
+                          header);
+      break;
+    }
+    const uint32_t k = g - base;
+    float4* mine = reinterpret_cast<float4*>(&sm.dep[k][slot]);
+    mine[0] = my_lo;
+    mine[1] = my_hi;
+    const uint32_t seen = arrive_or_cta(&sm.flag[k], 1u << slot);
+    // the node half goes out after the meeting, so no fence ever waits for it
+    np[0] = my_lo;
+    np[1] = my_hi;
+    if (seen == 0u) break;  // first arriver stops
+    const float4 slo = lds_volatile_v4(&sm.dep[k][slot ^ 1u]);
+    const float4 shi = lds_volatile_v4(reinterpret_cast<const float4*>(&sm.dep[k][slot ^ 1u]) + 1);
+    bx.lx = omin(bx.lx, slo.x); bx.ly = omin(bx.ly, slo.y); bx.lz = omin(bx.lz, slo.z);
+    bx.hx = omax(bx.hx, shi.x); bx.hy = omax(bx.hy, shi.y); bx.hz = omax(bx.hz, shi.z);
+    if (left) R = __float_as_uint(shi.w); else L = __float_as_uint(shi.w);
+    enc = (int)g;
+  }
+  __syncthreads();
+
+  // ---- phase 2: a slot with one child only waits for a sibling from elsewhere --------
+  const uint32_t f = sm.flag[tid];
+  if (f == 1u || f == 2u) {
+    const uint32_t slot = f - 1u, g = base + tid;
+    const Deposit d = sm.dep[tid][slot];
+    Box b2{d.lx, d.ly, d.lz, d.hx, d.hy, d.hz};
+    const uint32_t l2 = slot ? g + 1u : d.far_end, r2 = slot ? d.far_end : g;
+    park_or_climb<KeyT>(b2, d.child_enc, l2, r2, queue, queue_count, capacity, keys, n, flags,
+                        nodes, header);
+  }
+}
+
+// ---- refit_bvh: table-driven (parent words recorded by the build) -------------------
 // the device-scope protocol, used for nodes whose children belong to different CTAs
 __device__ __forceinline__ void climb_global(Box bx, int child_enc, uint32_t pword,
                                              const uint32_t* __restrict__ parent,
@@ -70,13 +303,11 @@ __device__ __forceinline__ void climb_global(Box bx, int child_enc, uint32_t pwo
     const uint32_t p = pword >> 2, slot = pword & 1u;
     const uint32_t next_pword = parent[p];
     float4* np = reinterpret_cast<float4*>(nodes + p);
+    const float keep = ld_cg(np + 2 * slot + 1).w;  // far end of the range: topology, kept
     np[2 * slot] = make_float4(bx.lx, bx.ly, bx.lz, __int_as_float(child_enc));
-    np[2 * slot + 1] = make_float4(bx.hx, bx.hy, bx.hz, 0.0f);
+    np[2 * slot + 1] = make_float4(bx.hx, bx.hy, bx.hz, keep);
     __threadfence();
     if (atomicAdd(flags + p, 1u) == 0u) return;
-    // acquire side: the loads below are issued only after the atomic's result is
-    // known (control dependency) and go to L2 (ld.cg), where the sibling's
-    // fenced stores already are
     const float4 slo = ld_cg(np + 2 * (slot ^ 1u));
     const float4 shi = ld_cg(np + 2 * (slot ^ 1u) + 1);
     bx.lx = omin(bx.lx, slo.x); bx.ly = omin(bx.ly, slo.y); bx.lz = omin(bx.lz, slo.z);
@@ -102,12 +333,10 @@ refit_top_kernel(const Continuation* __restrict__ queue, const uint32_t* __restr
   climb_global(bx, __float_as_int(a.w), __float_as_uint(b.w), parent, flags, nodes, header);
 }
 
-// FROM_INDEX: prim comes from sorted_idx (build); else from stris[j].v0p.w (refit_bvh)
-template <bool FROM_INDEX>
+// moved vertices, unchanged topology: prim comes from stris[j].v0p.w
 __global__ void __launch_bounds__(kRefitLeaves)
-refit_kernel(const float4* __restrict__ tris, const uint32_t* __restrict__ sorted_idx, uint32_t n,
-             const uint32_t* __restrict__ parent, uint32_t* __restrict__ flags,
-             Node* __restrict__ nodes, SortedTri* __restrict__ stris,
+refit_kernel(const float4* __restrict__ tris, uint32_t n, const uint32_t* __restrict__ parent,
+             uint32_t* __restrict__ flags, Node* __restrict__ nodes, SortedTri* __restrict__ stris,
              BvhHeader* __restrict__ header, Continuation* __restrict__ queue,
              uint32_t* __restrict__ queue_count, uint32_t capacity) {
   extern __shared__ __align__(16) unsigned char refit_smem_raw[];
@@ -117,9 +346,7 @@ refit_kernel(const float4* __restrict__ tris, const uint32_t* __restrict__ sorte
   sm.flag[threadIdx.x] = 0;
   __syncthreads();
   if (j >= n) return;
-  uint32_t prim;
-  if (FROM_INDEX) prim = sorted_idx[j];
-  else prim = __float_as_uint(stris[j].v0p.w);
+  const uint32_t prim = __float_as_uint(stris[j].v0p.w);
   const float4 a = __ldg(tris + 3 * (uint64_t)prim), b = __ldg(tris + 3 * (uint64_t)prim + 1),
                c = __ldg(tris + 3 * (uint64_t)prim + 2);
   float4* st = reinterpret_cast<float4*>(stris + j);
@@ -133,22 +360,23 @@ refit_kernel(const float4* __restrict__ tris, const uint32_t* __restrict__ sorte
   int child_enc = ~(int)j;
   uint32_t pword = parent[(n - 1) + j];
   while (pword != kNoParent && (pword & 2u)) {
-    // both children are refitted by this CTA: meet in shared memory
+    // both children were refitted by this CTA when the tree was built: meet in shared memory
     const uint32_t p = pword >> 2, slot = pword & 1u;
     const uint32_t next_pword = parent[p];  // independent of who wins below: overlap its latency
     float4* np = reinterpret_cast<float4*>(nodes + p);
-    np[2 * slot] = make_float4(bx.lx, bx.ly, bx.lz, __int_as_float(child_enc));
-    np[2 * slot + 1] = make_float4(bx.hx, bx.hy, bx.hz, 0.0f);
+    const float keep = np[2 * slot + 1].w;  // far end of the range: topology, kept
     const uint32_t k = p - base;
-    float* mine = sm.box[k][slot];
-    mine[0] = bx.lx; mine[1] = bx.ly; mine[2] = bx.lz;
-    mine[3] = bx.hx; mine[4] = bx.hy; mine[5] = bx.hz;
-    __threadfence_block();
-    if (atomicAdd(&sm.flag[k], 1u) == 0u) return;  // first arriver stops
-    __threadfence_block();
-    const volatile float* sib = sm.box[k][slot ^ 1u];
-    bx.lx = omin(bx.lx, sib[0]); bx.ly = omin(bx.ly, sib[1]); bx.lz = omin(bx.lz, sib[2]);
-    bx.hx = omax(bx.hx, sib[3]); bx.hy = omax(bx.hy, sib[4]); bx.hz = omax(bx.hz, sib[5]);
+    float4* mine = reinterpret_cast<float4*>(&sm.dep[k][slot]);
+    mine[0] = make_float4(bx.lx, bx.ly, bx.lz, 0.0f);
+    mine[1] = make_float4(bx.hx, bx.hy, bx.hz, 0.0f);
+    const uint32_t seen = arrive_add_cta(&sm.flag[k]);
+    np[2 * slot] = make_float4(bx.lx, bx.ly, bx.lz, __int_as_float(child_enc));
+    np[2 * slot + 1] = make_float4(bx.hx, bx.hy, bx.hz, keep);
+    if (seen == 0u) return;  // first arriver stops
+    const float4 slo = lds_volatile_v4(&sm.dep[k][slot ^ 1u]);
+    const float4 shi = lds_volatile_v4(reinterpret_cast<const float4*>(&sm.dep[k][slot ^ 1u]) + 1);
+    bx.lx = omin(bx.lx, slo.x); bx.ly = omin(bx.ly, slo.y); bx.lz = omin(bx.lz, slo.z);
+    bx.hx = omax(bx.hx, shi.x); bx.hy = omax(bx.hy, shi.y); bx.hz = omax(bx.hz, shi.z);
     child_enc = (int)p;
     pword = next_pword;
   }
@@ -164,23 +392,50 @@ refit_kernel(const float4* __restrict__ tris, const uint32_t* __restrict__ sorte
   }
 }
 
-// canonical arrays from the traversal layout (parity accessors T3/T4)
+// parent words from the finished nodes (refit_bvh and the parity accessors need
+// them; the build does not).  The far ends stored next to the child boxes give
+// the node's leaf range [L, R]; the two children met in shared memory exactly
+// when that range lies inside one group of kRefitLeaves leaves.
+__global__ void __launch_bounds__(256)
+derive_parents_kernel(const Node* __restrict__ nodes, uint32_t n, int root,
+                      uint32_t* __restrict__ parent) {
+  const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g == 0) parent[node_slot_of(root, n)] = kNoParent;
+  if (g + 1u >= n) return;
+  const float4* np = reinterpret_cast<const float4*>(nodes + g);
+  const float4 lo0 = np[0], hi0 = np[1], lo1 = np[2], hi1 = np[3];
+  const uint32_t L = __float_as_uint(hi0.w), R = __float_as_uint(hi1.w);
+  const uint32_t local = ((L >> kRefitLeavesLog2) == (R >> kRefitLeavesLog2)) ? 2u : 0u;
+  parent[node_slot_of(__float_as_int(lo0.w), n)] = (g << 2) | local;
+  parent[node_slot_of(__float_as_int(lo1.w), n)] = (g << 2) | local | 1u;
+}
+
+// canonical arrays from the traversal layout (parity accessors T3/T4).  Nodes are
+// stored by split position g; the Karras index of the child in slot s of node g
+// is g + s, the root is Karras node 0, leaves keep n-1+j.
+__device__ __forceinline__ uint32_t karras_id(uint32_t x, uint32_t pw, uint32_t leaf0) {
+  if (x >= leaf0) return x;
+  return (pw == kNoParent) ? 0u : (pw >> 2) + (pw & 1u);
+}
+
 __global__ void __launch_bounds__(256)
 export_kernel(const Node* __restrict__ nodes, const uint32_t* __restrict__ parent, uint32_t n,
               uint32_t* __restrict__ left, uint32_t* __restrict__ right,
               uint32_t* __restrict__ parent_out, float* __restrict__ boxes,
               const BvhHeader* __restrict__ header) {
-  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t x = blockIdx.x * blockDim.x + threadIdx.x;  // storage slot: split or n-1+leaf
   const uint32_t n_nodes = 2 * n - 1, leaf0 = n - 1;
-  if (i >= n_nodes) return;
-  const uint32_t pw = parent[i];
-  if (parent_out) parent_out[i] = (pw == kNoParent) ? kNoParent : (pw >> 2);
+  if (x >= n_nodes) return;
+  const uint32_t pw = parent[x];
+  const uint32_t k = karras_id(x, pw, leaf0);
+  if (parent_out)
+    parent_out[k] = (pw == kNoParent) ? kNoParent : karras_id(pw >> 2, parent[pw >> 2], leaf0);
   if (boxes) {
-    float* o = boxes + 6 * (uint64_t)i;
+    float* o = boxes + 6 * (uint64_t)k;
     if (pw == kNoParent) {
-      for (int k = 0; k < 3; ++k) {
-        o[k] = header->root_min[k];
-        o[3 + k] = header->root_max[k];
+      for (int c = 0; c < 3; ++c) {
+        o[c] = header->root_min[c];
+        o[3 + c] = header->root_max[c];
       }
     } else {
       const float4* np = reinterpret_cast<const float4*>(nodes + (pw >> 2)) + 2 * (pw & 1u);
@@ -188,10 +443,10 @@ export_kernel(const Node* __restrict__ nodes, const uint32_t* __restrict__ paren
       o[0] = lo.x; o[1] = lo.y; o[2] = lo.z; o[3] = hi.x; o[4] = hi.y; o[5] = hi.z;
     }
   }
-  if (i < leaf0) {
-    const int c0 = __float_as_int(nodes[i].lo0.w), c1 = __float_as_int(nodes[i].lo1.w);
-    if (left) left[i] = (c0 < 0) ? (leaf0 + (uint32_t)(~c0)) : (uint32_t)c0;
-    if (right) right[i] = (c1 < 0) ? (leaf0 + (uint32_t)(~c1)) : (uint32_t)c1;
+  if (x < leaf0) {
+    const int c0 = __float_as_int(nodes[x].lo0.w), c1 = __float_as_int(nodes[x].lo1.w);
+    if (left) left[k] = (c0 < 0) ? (leaf0 + (uint32_t)(~c0)) : x;
+    if (right) right[k] = (c1 < 0) ? (leaf0 + (uint32_t)(~c1)) : x + 1u;
   }
 }
 
@@ -221,30 +476,9 @@ int launch_widen_keys(const uint32_t* in, uint64_t n, uint64_t* out, cudaStream_
   return 0;
 }
 
-static int refit_common(bool from_index, const float4* tris, const uint32_t* sorted_idx, uint64_t n,
-                        const uint32_t* parent, uint32_t* flags, Node* nodes, SortedTri* stris,
-                        BvhHeader* header, void* queue_buf, cudaStream_t s) {
-  if (n == 0) return 0;
-  const unsigned blocks = (unsigned)((n + kRefitLeaves - 1) / kRefitLeaves);
-  const uint32_t capacity = blocks * kContPerCta;
-  uint32_t* queue_count = reinterpret_cast<uint32_t*>(queue_buf);
-  Continuation* queue = reinterpret_cast<Continuation*>(reinterpret_cast<char*>(queue_buf) + 32);
-  if (n > 1) RT_CUDA(cudaMemsetAsync(flags, 0, (size_t)(n - 1) * sizeof(uint32_t), s));
-  RT_CUDA(cudaMemsetAsync(queue_count, 0, 32, s));
-  const size_t smem = sizeof(RefitSmem);
-  RT_CUDA(cudaFuncSetAttribute(refit_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  RT_CUDA(cudaFuncSetAttribute(refit_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  if (from_index)
-    refit_kernel<true><<<blocks, kRefitLeaves, smem, s>>>(tris, sorted_idx, (uint32_t)n, parent, flags,
-                                                         nodes, stris, header, queue, queue_count, capacity);
-  else
-    refit_kernel<false><<<blocks, kRefitLeaves, smem, s>>>(tris, sorted_idx, (uint32_t)n, parent, flags,
-                                                          nodes, stris, header, queue, queue_count, capacity);
-  RT_LAUNCHED();
-  refit_top_kernel<<<(capacity + 255) / 256, 256, 0, s>>>(queue, queue_count, capacity, parent, flags,
-                                                          nodes, header);
-  RT_LAUNCHED();
-  return 0;
+static void queue_layout(void* queue_buf, uint32_t** count, Continuation** queue) {
+  *count = reinterpret_cast<uint32_t*>(queue_buf);
+  *queue = reinterpret_cast<Continuation*>(reinterpret_cast<char*>(queue_buf) + 32);
 }
 
 size_t refit_queue_bytes(uint64_t n) {
@@ -252,16 +486,68 @@ size_t refit_queue_bytes(uint64_t n) {
   return 32 + (blocks ? blocks : 1) * kContPerCta * sizeof(Continuation);
 }
 
-int launch_refit(const float4* tris, const uint32_t* sorted_idx, uint64_t n,
-                 const uint32_t* parent, uint32_t* flags, Node* nodes, SortedTri* stris,
-                 BvhHeader* header, void* queue_buf, cudaStream_t s) {
-  return refit_common(true, tris, sorted_idx, n, parent, flags, nodes, stris, header, queue_buf, s);
+template <typename KeyT>
+static int build_tree_impl(const float4* tris, const uint32_t* sorted_idx, const KeyT* keys,
+                           uint64_t n, uint32_t* flags, Node* nodes, SortedTri* stris,
+                           BvhHeader* header, void* queue_buf, cudaStream_t s) {
+  const unsigned blocks = (unsigned)((n + kRefitLeaves - 1) / kRefitLeaves);
+  const uint32_t capacity = blocks * kContPerCta;
+  uint32_t* queue_count;
+  Continuation* queue;
+  queue_layout(queue_buf, &queue_count, &queue);
+  if (n > 1) RT_CUDA(cudaMemsetAsync(flags, 0, (size_t)(n - 1) * sizeof(uint32_t), s));
+  RT_CUDA(cudaMemsetAsync(queue_count, 0, 32, s));
+  const size_t smem = sizeof(RefitSmem);
+  RT_CUDA(cudaFuncSetAttribute(build_walk_kernel<KeyT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               (int)smem));
+  build_walk_kernel<KeyT><<<blocks, kRefitLeaves, smem, s>>>(
+      tris, sorted_idx, keys, (uint32_t)n, flags, nodes, stris, header, queue, queue_count, capacity);
+  RT_LAUNCHED();
+  build_top_kernel<KeyT><<<(capacity + 255) / 256, 256, 0, s>>>(
+      queue, queue_count, capacity, keys, (uint32_t)n, flags, nodes, header);
+  RT_LAUNCHED();
+  return 0;
+}
+
+int launch_build_tree(const float4* tris, const uint32_t* sorted_idx, const void* keys,
+                      uint32_t key_bits, uint64_t n, uint32_t* flags, Node* nodes,
+                      SortedTri* stris, BvhHeader* header, void* queue_buf, cudaStream_t s) {
+  if (n == 0) return 0;
+  if (key_bits == 30)
+    return build_tree_impl<uint32_t>(tris, sorted_idx, (const uint32_t*)keys, n, flags, nodes,
+                                     stris, header, queue_buf, s);
+  return build_tree_impl<uint64_t>(tris, sorted_idx, (const uint64_t*)keys, n, flags, nodes, stris,
+                                   header, queue_buf, s);
+}
+
+int launch_derive_parents(const Node* nodes, uint64_t n, int root, uint32_t* parent,
+                          cudaStream_t s) {
+  if (n == 0) return 0;
+  derive_parents_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(nodes, (uint32_t)n, root, parent);
+  RT_LAUNCHED();
+  return 0;
 }
 
 int launch_refit_update(const float4* tris, uint64_t n, const uint32_t* parent, uint32_t* flags,
                         Node* nodes, SortedTri* stris, BvhHeader* header, void* queue_buf,
                         cudaStream_t s) {
-  return refit_common(false, tris, nullptr, n, parent, flags, nodes, stris, header, queue_buf, s);
+  if (n == 0) return 0;
+  const unsigned blocks = (unsigned)((n + kRefitLeaves - 1) / kRefitLeaves);
+  const uint32_t capacity = blocks * kContPerCta;
+  uint32_t* queue_count;
+  Continuation* queue;
+  queue_layout(queue_buf, &queue_count, &queue);
+  if (n > 1) RT_CUDA(cudaMemsetAsync(flags, 0, (size_t)(n - 1) * sizeof(uint32_t), s));
+  RT_CUDA(cudaMemsetAsync(queue_count, 0, 32, s));
+  const size_t smem = sizeof(RefitSmem);
+  RT_CUDA(cudaFuncSetAttribute(refit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  refit_kernel<<<blocks, kRefitLeaves, smem, s>>>(tris, (uint32_t)n, parent, flags, nodes, stris,
+                                                 header, queue, queue_count, capacity);
+  RT_LAUNCHED();
+  refit_top_kernel<<<(capacity + 255) / 256, 256, 0, s>>>(queue, queue_count, capacity, parent, flags,
+                                                          nodes, header);
+  RT_LAUNCHED();
+  return 0;
 }
 
 int launch_export_topology(const Node* nodes, const uint32_t* parent, uint64_t n, uint32_t* left,

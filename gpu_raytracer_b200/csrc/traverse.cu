@@ -122,12 +122,11 @@ __device__ __forceinline__ void trace_one(const Node* __restrict__ nodes,
 template <bool ANY, bool STATS>
 __global__ void __launch_bounds__(kTraceThreads)
 trace_kernel(const Node* __restrict__ nodes, const SortedTri* __restrict__ stris, uint32_t n_tris,
-             const float4* __restrict__ rays, unsigned long long n_rays,
+             int root, const float4* __restrict__ rays, unsigned long long n_rays,
              float4* __restrict__ hits, unsigned long long* __restrict__ ray_counter,
              unsigned long long* __restrict__ stats) {
   uint32_t n_nodes = 0, n_tests = 0;
   const int lane = threadIdx.x & 31;
-  const int root = (n_tris == 1) ? ~0 : 0;
   const float inf = __int_as_float(0x7f800000);
   while (true) {
     unsigned long long base = 0;
@@ -185,12 +184,12 @@ trace_kernel(const Node* __restrict__ nodes, const SortedTri* __restrict__ stris
 template <bool ANY, bool STATS>
 __global__ void __launch_bounds__(kTraceThreads)
 trace_kernel_dyn(const Node* __restrict__ nodes, const SortedTri* __restrict__ stris,
-                 uint32_t n_tris, const float4* __restrict__ rays, unsigned long long n_rays,
-                 float4* __restrict__ hits, unsigned long long* __restrict__ ray_counter,
+                 uint32_t n_tris, int root, const float4* __restrict__ rays,
+                 unsigned long long n_rays, float4* __restrict__ hits,
+                 unsigned long long* __restrict__ ray_counter,
                  unsigned long long* __restrict__ stats, int chunk, int refill_min, int leaf_min) {
   const int lane = threadIdx.x & 31;
   const uint32_t lt_mask = (1u << lane) - 1u;
-  const int root = (n_tris == 1) ? ~0 : 0;
   const float inf = __int_as_float(0x7f800000);
   uint32_t n_nodes = 0, n_tests = 0;
 
@@ -306,7 +305,8 @@ trace_kernel_dyn(const Node* __restrict__ nodes, const SortedTri* __restrict__ s
 
 }  // namespace
 
-int launch_trace(const Node* nodes, const SortedTri* stris, uint64_t n_tris, const float4* rays,
+int launch_trace(const Node* nodes, const SortedTri* stris, uint64_t n_tris, int root,
+                 const float4* rays,
                  uint64_t n_rays, uint32_t flags, float4* hits, unsigned long long* ray_counter,
                  cudaStream_t s, unsigned long long* stats) {
   if (n_rays == 0) return 0;
@@ -326,7 +326,7 @@ int launch_trace(const Node* nodes, const SortedTri* stris, uint64_t n_tris, con
     const int leaf_min = p.trace_leaf_min > 0 ? p.trace_leaf_min : 8;
 #define RT_TRACE_DYN(A, S)                                                 \
   trace_kernel_dyn<A, S><<<(unsigned)blocks, kTraceThreads, 0, s>>>(       \
-      nodes, stris, (uint32_t)n_tris, rays, n_rays, hits, ray_counter, stats, chunk, refill_min, leaf_min)
+      nodes, stris, (uint32_t)n_tris, root, rays, n_rays, hits, ray_counter, stats, chunk, refill_min, leaf_min)
     if (stats) {
       if (any) RT_TRACE_DYN(true, true);
       else RT_TRACE_DYN(false, true);
@@ -340,7 +340,7 @@ int launch_trace(const Node* nodes, const SortedTri* stris, uint64_t n_tris, con
   }
 #define RT_TRACE_LAUNCH(A, S)                                          \
   trace_kernel<A, S><<<(unsigned)blocks, kTraceThreads, 0, s>>>(       \
-      nodes, stris, (uint32_t)n_tris, rays, n_rays, hits, ray_counter, stats)
+      nodes, stris, (uint32_t)n_tris, root, rays, n_rays, hits, ray_counter, stats)
   if (stats) {
     if (any) RT_TRACE_LAUNCH(true, true);
     else RT_TRACE_LAUNCH(false, true);
