@@ -38,9 +38,11 @@ UNIT = "Mrays/s"
 
 # algorithmic bytes per triangle of each build stage
 STAGE_BYTES = {
-    30: {"bounds": 48, "morton": 56, "sort": 68, "topology": 20, "refit": 196, "total": 388},
-    63: {"bounds": 48, "morton": 60, "sort": 200, "topology": 24, "refit": 196, "total": 528},
+    30: {"bounds": 48, "morton": 56, "sort": 68, "tree": 20 + 196, "total": 388},
+    63: {"bounds": 48, "morton": 60, "sort": 200, "tree": 24 + 196, "total": 528},
 }
+# "tree" = A4 topology + A5 leaves + refit: one fused bottom-up pass (csrc/refit.cu), so the
+# library's "topology" timer is empty and its time is reported with "refit".
 
 
 def measured_peak():
@@ -355,10 +357,12 @@ def run_ours(args):
     except Exception:
         pass
     sb = STAGE_BYTES[wl.key_bits]
+    stage_ms = dict(stage_ms)
+    stage_ms["tree"] = stage_ms.get("topology", 0.0) + stage_ms.get("refit", 0.0)
     stages = {k: {"ms": stage_ms[k], "alg_bytes_per_tri": sb[k],
                   "achieved_gbs": sb[k] * n_tris / stage_ms[k] / 1e6,
                   "frac": sb[k] * n_tris / stage_ms[k] / 1e6 / peak}
-              for k in ("bounds", "morton", "sort", "topology", "refit", "total") if stage_ms[k] > 0}
+              for k in ("bounds", "morton", "sort", "tree", "total") if stage_ms[k] > 0}
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
         "ms_per_step": (build_ms + total_trace_ms) / K, "higher_is_better": True, "scaling": "weak",

@@ -9,7 +9,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-SO_PATH = os.path.join(_HERE, "libgpu_raytracer_b200.so")
+# RT_LIB: development override used to A/B experimental builds of the same library
+SO_PATH = os.environ.get("RT_LIB") or os.path.join(_HERE, "libgpu_raytracer_b200.so")
 
 RT_OK, RT_ERR_INVALID, RT_ERR_CUDA, RT_ERR_OOM, RT_ERR_NO_DEVICE, RT_ERR_LIMIT = 0, -1, -2, -3, -4, -5
 RT_TRACE_CLOSEST, RT_TRACE_ANY = 0, 1

@@ -39,7 +39,10 @@ struct BvhHeader {
 // of one refit CTA while the tree was built (both leaf ranges inside one aligned
 // group of kRefitLeaves leaves); refit_bvh then meets there again.
 constexpr uint32_t kNoParent = 0xFFFFFFFFu;
-constexpr int kRefitLeavesLog2 = 10;
+#ifndef RT_REFIT_LOG2
+#define RT_REFIT_LOG2 8
+#endif
+constexpr int kRefitLeavesLog2 = RT_REFIT_LOG2;
 constexpr int kRefitLeaves = 1 << kRefitLeavesLog2;
 
 // ---- generators (scene_gen.cu, ray_gen.cu) ---------------------------------

@@ -16,7 +16,8 @@
 // of 32 lanes active on average) used to take 0.28 ms for 10M leaves before the
 // refit even started; here the topology costs two byte loads per climb step.
 //
-// One thread per leaf, one CTA per kRefitLeaves = 1024 consecutive leaves.  The
+// One thread per leaf, one CTA per kRefitLeaves = 256 consecutive leaves (measured:
+// 1024 -> 0.65 ms, 512 -> 0.62, 256 -> 0.59, 128 -> 0.59, 64 -> 0.92 ms for 10M).  The
 // thread gathers its triangle through the sorted index, stores it in traversal
 // form {v0 | prim, e1, e2}, then climbs: it writes the box it carries (child
 // id, far end of its range) into its slot of node g — one full 32-byte sector —
@@ -89,19 +90,17 @@ __device__ __forceinline__ float4 lds_volatile_v4(const void* p) {
 // Shared state of one CTA = kRefitLeaves consecutive leaves: arrival bits and
 // deposited children of the nodes whose split position lies inside the group
 // (index = split position - first leaf of the CTA).
-struct __align__(16) Deposit {
-  float lx, ly, lz;
-  int child_enc;
-  float hx, hy, hz;
-  uint32_t far_end;  // the end of the child's leaf range away from the split
-};
+// Deposits are stored as planes of float4 indexed [slot][k]: neighbouring walkers
+// deposit at neighbouring k, so a 16-byte stride keeps a warp's STS.128 / LDS.128
+// free of bank conflicts (the array-of-structs layout was 4-way conflicted).
 struct RefitSmem {
-  Deposit dep[kRefitLeaves][2];
+  float4 dep_lo[2][kRefitLeaves];  // min.xyz, child id
+  float4 dep_hi[2][kRefitLeaves];  // max.xyz, far end of the child's leaf range
   uint32_t flag[kRefitLeaves];
   uint8_t delta[kRefitLeaves + 8];  // delta(base - 1 + t), t in [0, kRefitLeaves]
 };
 
-// A walker that leaves its CTA's group parks here instead of keeping a 1024-thread
+// A walker that leaves its CTA's group parks here instead of keeping a whole
 // CTA resident while it climbs the (slow, device-scope) top of the tree.
 struct __align__(16) Continuation {
   float lx, ly, lz;
@@ -110,7 +109,9 @@ struct __align__(16) Continuation {
   uint32_t pword;  // table-driven refit: parent word.  build: unused
   uint32_t L, R, pad0, pad1;
 };
-constexpr int kContPerCta = 96;  // queue capacity per leaf CTA; overflow climbs inline
+// queue capacity: one global bound, about twice what the scenes in BASELINE.json park
+// with 256-leaf groups; a walker that finds the queue full climbs inline
+static uint32_t queue_capacity(uint64_t n) { return (uint32_t)(n / 8 + 4096); }
 
 __device__ __forceinline__ uint32_t node_slot_of(int child_enc, uint32_t n) {
   return child_enc < 0 ? (n - 1u) + (uint32_t)(~child_enc) : (uint32_t)child_enc;
@@ -264,16 +265,15 @@ build_walk_kernel(const float4* __restrict__ tris, const uint32_t* __restrict__ 
       break;
     }
     const uint32_t k = g - base;
-    float4* mine = reinterpret_cast<float4*>(&sm.dep[k][slot]);
-    mine[0] = my_lo;
-    mine[1] = my_hi;
+    sm.dep_lo[slot][k] = my_lo;
+    sm.dep_hi[slot][k] = my_hi;
     const uint32_t seen = arrive_or_cta(&sm.flag[k], 1u << slot);
     // the node half goes out after the meeting, so no fence ever waits for it
     np[0] = my_lo;
     np[1] = my_hi;
     if (seen == 0u) break;  // first arriver stops
-    const float4 slo = lds_volatile_v4(&sm.dep[k][slot ^ 1u]);
-    const float4 shi = lds_volatile_v4(reinterpret_cast<const float4*>(&sm.dep[k][slot ^ 1u]) + 1);
+    const float4 slo = lds_volatile_v4(&sm.dep_lo[slot ^ 1u][k]);
+    const float4 shi = lds_volatile_v4(&sm.dep_hi[slot ^ 1u][k]);
     bx.lx = omin(bx.lx, slo.x); bx.ly = omin(bx.ly, slo.y); bx.lz = omin(bx.lz, slo.z);
     bx.hx = omax(bx.hx, shi.x); bx.hy = omax(bx.hy, shi.y); bx.hz = omax(bx.hz, shi.z);
     if (left) R = __float_as_uint(shi.w); else L = __float_as_uint(shi.w);
@@ -285,10 +285,11 @@ build_walk_kernel(const float4* __restrict__ tris, const uint32_t* __restrict__ 
   const uint32_t f = sm.flag[tid];
   if (f == 1u || f == 2u) {
     const uint32_t slot = f - 1u, g = base + tid;
-    const Deposit d = sm.dep[tid][slot];
-    Box b2{d.lx, d.ly, d.lz, d.hx, d.hy, d.hz};
-    const uint32_t l2 = slot ? g + 1u : d.far_end, r2 = slot ? d.far_end : g;
-    park_or_climb<KeyT>(b2, d.child_enc, l2, r2, queue, queue_count, capacity, keys, n, flags,
+    const float4 dlo = sm.dep_lo[slot][tid], dhi = sm.dep_hi[slot][tid];
+    Box b2{dlo.x, dlo.y, dlo.z, dhi.x, dhi.y, dhi.z};
+    const uint32_t far_end = __float_as_uint(dhi.w);
+    const uint32_t l2 = slot ? g + 1u : far_end, r2 = slot ? far_end : g;
+    park_or_climb<KeyT>(b2, __float_as_int(dlo.w), l2, r2, queue, queue_count, capacity, keys, n, flags,
                         nodes, header);
   }
 }
@@ -366,15 +367,14 @@ refit_kernel(const float4* __restrict__ tris, uint32_t n, const uint32_t* __rest
     float4* np = reinterpret_cast<float4*>(nodes + p);
     const float keep = np[2 * slot + 1].w;  // far end of the range: topology, kept
     const uint32_t k = p - base;
-    float4* mine = reinterpret_cast<float4*>(&sm.dep[k][slot]);
-    mine[0] = make_float4(bx.lx, bx.ly, bx.lz, 0.0f);
-    mine[1] = make_float4(bx.hx, bx.hy, bx.hz, 0.0f);
+    sm.dep_lo[slot][k] = make_float4(bx.lx, bx.ly, bx.lz, 0.0f);
+    sm.dep_hi[slot][k] = make_float4(bx.hx, bx.hy, bx.hz, 0.0f);
     const uint32_t seen = arrive_add_cta(&sm.flag[k]);
     np[2 * slot] = make_float4(bx.lx, bx.ly, bx.lz, __int_as_float(child_enc));
     np[2 * slot + 1] = make_float4(bx.hx, bx.hy, bx.hz, keep);
     if (seen == 0u) return;  // first arriver stops
-    const float4 slo = lds_volatile_v4(&sm.dep[k][slot ^ 1u]);
-    const float4 shi = lds_volatile_v4(reinterpret_cast<const float4*>(&sm.dep[k][slot ^ 1u]) + 1);
+    const float4 slo = lds_volatile_v4(&sm.dep_lo[slot ^ 1u][k]);
+    const float4 shi = lds_volatile_v4(&sm.dep_hi[slot ^ 1u][k]);
     bx.lx = omin(bx.lx, slo.x); bx.ly = omin(bx.ly, slo.y); bx.lz = omin(bx.lz, slo.z);
     bx.hx = omax(bx.hx, shi.x); bx.hy = omax(bx.hy, shi.y); bx.hz = omax(bx.hz, shi.z);
     child_enc = (int)p;
@@ -482,8 +482,7 @@ static void queue_layout(void* queue_buf, uint32_t** count, Continuation** queue
 }
 
 size_t refit_queue_bytes(uint64_t n) {
-  const uint64_t blocks = (n + kRefitLeaves - 1) / kRefitLeaves;
-  return 32 + (blocks ? blocks : 1) * kContPerCta * sizeof(Continuation);
+  return 32 + (size_t)queue_capacity(n) * sizeof(Continuation);
 }
 
 template <typename KeyT>
@@ -491,7 +490,7 @@ static int build_tree_impl(const float4* tris, const uint32_t* sorted_idx, const
                            uint64_t n, uint32_t* flags, Node* nodes, SortedTri* stris,
                            BvhHeader* header, void* queue_buf, cudaStream_t s) {
   const unsigned blocks = (unsigned)((n + kRefitLeaves - 1) / kRefitLeaves);
-  const uint32_t capacity = blocks * kContPerCta;
+  const uint32_t capacity = queue_capacity(n);
   uint32_t* queue_count;
   Continuation* queue;
   queue_layout(queue_buf, &queue_count, &queue);
@@ -533,7 +532,7 @@ int launch_refit_update(const float4* tris, uint64_t n, const uint32_t* parent, 
                         cudaStream_t s) {
   if (n == 0) return 0;
   const unsigned blocks = (unsigned)((n + kRefitLeaves - 1) / kRefitLeaves);
-  const uint32_t capacity = blocks * kContPerCta;
+  const uint32_t capacity = queue_capacity(n);
   uint32_t* queue_count;
   Continuation* queue;
   queue_layout(queue_buf, &queue_count, &queue);
