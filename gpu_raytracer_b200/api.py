@@ -115,6 +115,12 @@ def shade(tris, rays, hits, ao_hits=None, spp: int = 0):
     return out
 
 
+# one slot of bvh_read_wide (include/gpu_raytracer.h)
+WIDE_NODE_DTYPE = np.dtype([("lo", np.float32, (3, 4)), ("hi", np.float32, (3, 4)),
+                            ("ref", np.uint32, 4), ("n_children", np.uint32), ("pad", np.uint32, 3)])
+WIDE_LEAF_BIT, WIDE_EMPTY, WIDE_FIRST_MASK = 0x80000000, 0x7FFFFFFF, (1 << 29) - 1
+
+
 # ---------------------------------------------------------------------------
 # the BVH handle
 # ---------------------------------------------------------------------------
@@ -127,11 +133,12 @@ class Bvh:
     # -- build_bvh -----------------------------------------------------------
     @classmethod
     def build(cls, tris, key_bits: int = 30, keep_keys: bool = False, timings: bool = False,
-              device: int = -1, stream: int = 0) -> "Bvh":
+              device: int = -1, stream: int = 0, wide: bool = False) -> "Bvh":
         n = _rows(tris, 12)
         opts = L.BuildOpts(key_bits=key_bits,
                            flags=(L.RT_BUILD_KEEP_KEYS if keep_keys else 0) |
-                                 (L.RT_BUILD_TIMINGS if timings else 0),
+                                 (L.RT_BUILD_TIMINGS if timings else 0) |
+                                 (L.RT_BUILD_WIDE4 if wide else 0),
                            device=device, reserved=0, stream=stream or None)
         h = C.c_void_p()
         L.check(L.lib().build_bvh(_ptr(tris) if n else None, n, C.byref(opts), C.byref(h)))
@@ -167,6 +174,19 @@ class Bvh:
 
     def refit(self, tris) -> None:
         L.check(L.lib().refit_bvh(self._h, _ptr(tris)))
+
+    def widen(self) -> None:
+        """Collapse to the 4-wide layout (A5w); ``trace`` then walks it."""
+        L.check(L.lib().bvh_widen(self._h))
+
+    def read_wide(self):
+        """(nodes, root_ref): the BVH4 as a structured array with n-1 slots."""
+        n = self.n_tris
+        nodes = np.zeros(max(n - 1, 0), dtype=WIDE_NODE_DTYPE)
+        root = C.c_uint32()
+        L.check(L.lib().bvh_read_wide(self._h, nodes.ctypes.data if n > 1 else None,
+                                      C.byref(root)))
+        return nodes, int(root.value)
 
     # -- accessors ---------------------------------------------------------------
     def info(self) -> L.BvhInfo:
@@ -205,7 +225,7 @@ class Bvh:
         return boxes
 
     def build_times(self) -> dict:
-        ms = (C.c_float * 6)()
+        ms = (C.c_float * len(L.RT_STAGE_NAMES))()
         L.check(L.lib().bvh_build_times(self._h, ms))
         return dict(zip(L.RT_STAGE_NAMES, [float(x) for x in ms]))
 

@@ -165,9 +165,13 @@ struct rt_bvh {
   mutable uint32_t* parent = nullptr;
   mutable std::mutex parent_mu;
   void* keys = nullptr;  // only with RT_BUILD_KEEP_KEYS
+  Node4* wide = nullptr;      // only with RT_BUILD_WIDE4 / bvh_widen: n-1 slots
+  uint32_t wide_root = 0;     // reference the BVH4 traversal starts from
+  bool is_wide = false;
+  uint32_t wide_leaf_max = kWideLeafDefault;
   float bounds[6] = {0, 0, 0, 0, 0, 0};
   int root = 0;  // node id where traversal starts (header.root_node)
-  float times[RT_STAGE_COUNT] = {0, 0, 0, 0, 0, 0};
+  float times[RT_STAGE_COUNT] = {0, 0, 0, 0, 0, 0, 0};
   bool has_times = false;
   uint64_t bytes = 0;
 };
@@ -186,6 +190,7 @@ void release(rt_bvh* h) {
   if (h->header) cudaFreeAsync(h->header, 0);
   if (h->parent) cudaFreeAsync(h->parent, 0);
   if (h->keys) cudaFreeAsync(h->keys, 0);
+  if (h->wide) cudaFreeAsync(h->wide, 0);
   if (prev != h->device && prev >= 0) cudaSetDevice(prev);
   delete h;
 }
@@ -203,6 +208,34 @@ int ensure_parents(const rt_bvh* h, cudaStream_t s) {
   }
   h->parent = p;
   return 0;
+}
+
+// (re)builds the BVH4 of a finished BVH2 (A5w); h->root must be current
+int widen(rt_bvh* h, cudaStream_t s) {
+  if (h->n > kWideMaxTris)
+    return fail(RT_ERR_LIMIT, "wide BVH: %llu triangles exceed 2^29", (unsigned long long)h->n);
+  int lm = params().wide_leaf_max;
+  h->wide_leaf_max = (uint32_t)(lm < 1 ? 1 : (lm > kWideLeafMax ? kWideLeafMax : lm));
+  if (!h->wide && h->n > 1) {
+    const size_t bytes = (h->n - 1) * sizeof(Node4);
+    RT_CUDA(cudaMallocAsync((void**)&h->wide, bytes, s));
+    h->bytes += bytes;
+  }
+  RT_TRY(launch_collapse4(h->nodes, h->n, h->wide_leaf_max, h->wide, s));
+  h->wide_root = wide_root_ref(h->n, h->root, h->wide_leaf_max);  // build_impl sets it again once the root is known
+  h->is_wide = true;
+  return 0;
+}
+
+// traversal of whichever layout the handle holds
+int launch_trace_h(const rt_bvh* h, const float4* rays, uint64_t n_rays, uint32_t flags,
+                   float4* hits, unsigned long long* counter, cudaStream_t s,
+                   unsigned long long* stats = nullptr) {
+  if (h->is_wide && params().trace_wide != 0)
+    return launch_trace_wide(h->wide, h->stris, h->n, h->wide_root, rays, n_rays, flags, hits,
+                             counter, s, stats);
+  return launch_trace(h->nodes, h->stris, h->n, h->root, rays, n_rays, flags, hits, counter, s,
+                      stats);
 }
 
 int alloc_handle_buffers(rt_bvh* h, bool keep_keys, cudaStream_t s) {
@@ -239,6 +272,7 @@ int build_impl(rt_bvh* h, const float* tris_in, uint32_t flags, cudaStream_t s) 
   hdr.key_bits = h->key_bits;
   RT_CUDA(cudaMemcpyAsync(h->header, &hdr, sizeof(hdr), cudaMemcpyHostToDevice, s));
   if (n == 0) {
+    if (flags & RT_BUILD_WIDE4) RT_TRY(widen(h, s));
     RT_CUDA(cudaStreamSynchronize(s));
     return 0;
   }
@@ -300,6 +334,8 @@ int build_impl(rt_bvh* h, const float* tris_in, uint32_t flags, cudaStream_t s) 
   RT_TRY(launch_build_tree(tris, svals, skeys, h->key_bits, n, (uint32_t*)flags_buf, h->nodes,
                            h->stris, h->header, queue_buf, s));
   RT_TRY(mark(5));
+  if (flags & RT_BUILD_WIDE4) RT_TRY(widen(h, s));  // A5w, optional
+  RT_TRY(mark(6));
   if (h->keys) RT_CUDA(cudaMemcpyAsync(h->keys, skeys, n * ksz, cudaMemcpyDeviceToDevice, s));
   RT_CUDA(cudaMemcpyAsync(&hdr, h->header, sizeof(hdr), cudaMemcpyDeviceToHost, s));
   RT_CUDA(cudaStreamSynchronize(s));
@@ -308,9 +344,11 @@ int build_impl(rt_bvh* h, const float* tris_in, uint32_t flags, cudaStream_t s) 
     h->bounds[3 + k] = hdr.root_max[k];
   }
   h->root = (int)hdr.root_node;
+  h->wide_root = wide_root_ref(n, h->root, h->wide_leaf_max);
   if (timed) {
     for (int i = 0; i < 5; ++i) RT_CUDA(cudaEventElapsedTime(&h->times[i], ev[i], ev[i + 1]));
-    RT_CUDA(cudaEventElapsedTime(&h->times[RT_STAGE_TOTAL], ev[0], ev[5]));
+    RT_CUDA(cudaEventElapsedTime(&h->times[RT_STAGE_WIDE], ev[5], ev[6]));
+    RT_CUDA(cudaEventElapsedTime(&h->times[RT_STAGE_TOTAL], ev[0], ev[6]));
     for (int i = 0; i < RT_STAGE_COUNT; ++i) cudaEventDestroy(ev[i]);
     h->has_times = true;
   }
@@ -388,6 +426,32 @@ extern "C" int refit_bvh(rt_bvh* h, const float* tris_in) {
     h->bounds[3 + k] = hdr.root_max[k];
   }
   h->root = (int)hdr.root_node;
+  if (h->is_wide) {  // same topology, new boxes: collapse again
+    RT_TRY(widen(h, s));
+    RT_CUDA(cudaStreamSynchronize(s));
+  }
+  return RT_OK;
+}
+
+extern "C" int bvh_widen(rt_bvh* h) {
+  if (!h) return fail(RT_ERR_INVALID, "bvh_widen: handle is NULL");
+  DeviceScope scope;
+  RT_TRY(scope.enter(h->device));
+  cudaStream_t s = 0;
+  RT_TRY(widen(h, s));
+  RT_CUDA(cudaStreamSynchronize(s));
+  return RT_OK;
+}
+
+extern "C" int bvh_read_wide(const rt_bvh* h, void* nodes4, uint32_t* root_ref) {
+  if (!h) return fail(RT_ERR_INVALID, "bvh_read_wide: handle is NULL");
+  if (!h->is_wide) return fail(RT_ERR_INVALID, "bvh_read_wide: the handle holds no BVH4");
+  if (root_ref) *root_ref = h->wide_root;
+  if (nodes4 && h->wide) {
+    DeviceScope scope;
+    RT_TRY(scope.enter(h->device));
+    RT_CUDA(cudaMemcpy(nodes4, h->wide, (h->n - 1) * sizeof(Node4), cudaMemcpyDeviceToHost));
+  }
   return RT_OK;
 }
 
@@ -431,7 +495,7 @@ int trace_device(const rt_bvh* h, const float4* rays, uint64_t n_rays, uint32_t 
                  float4* hits, cudaStream_t s) {
   unsigned long long* counter = nullptr;
   RT_CUDA(cudaMallocAsync((void**)&counter, sizeof(unsigned long long), s));
-  int rc = launch_trace(h->nodes, h->stris, h->n, h->root, rays, n_rays, flags, hits, counter, s);
+  int rc = launch_trace_h(h, rays, n_rays, flags, hits, counter, s);
   cudaFreeAsync(counter, s);
   return rc;
 }
@@ -467,7 +531,7 @@ int trace_staged(const rt_bvh* h, const float* rays, bool rays_dev, uint64_t n_r
       if (c >= 2) RT_CUDA(cudaStreamWaitEvent(p.s_run, p.ev_out[b], 0));  // slot drained
       hdst = p.hits[b];
     }
-    RT_TRY(launch_trace(h->nodes, h->stris, h->n, h->root, rsrc, cnt, flags, hdst, p.counters + b, p.s_run));
+    RT_TRY(launch_trace_h(h, rsrc, cnt, flags, hdst, p.counters + b, p.s_run));
     RT_CUDA(cudaEventRecord(p.ev_run[b], p.s_run));
     if (!hits_dev) {
       RT_CUDA(cudaStreamWaitEvent(p.s_out, p.ev_run[b], 0));
@@ -543,8 +607,8 @@ extern "C" int trace_rays_stats(const rt_bvh* h, const float* rays, uint64_t n_r
   RT_TRY(tmp.alloc(&d, 3 * sizeof(unsigned long long)));
   RT_CUDA(cudaMemsetAsync(d, 0, 3 * sizeof(unsigned long long), s));
   unsigned long long* dc = (unsigned long long*)d;
-  RT_TRY(launch_trace(h->nodes, h->stris, h->n, h->root, reinterpret_cast<const float4*>(rays), n_rays,
-                      flags, reinterpret_cast<float4*>(hits), dc + 2, s, dc));
+  RT_TRY(launch_trace_h(h, reinterpret_cast<const float4*>(rays), n_rays, flags,
+                        reinterpret_cast<float4*>(hits), dc + 2, s, dc));
   unsigned long long host[2] = {0, 0};
   RT_CUDA(cudaMemcpyAsync(host, dc, sizeof(host), cudaMemcpyDeviceToHost, s));
   RT_CUDA(cudaStreamSynchronize(s));
@@ -842,6 +906,8 @@ extern "C" int rt_set_param(const char* name, int64_t value) {
   else if (!strcmp(name, "sort.bits")) p.sort_bits = (int)value;
   else if (!strcmp(name, "trace.blocks_per_sm")) p.trace_blocks_per_sm = (int)value;
   else if (!strcmp(name, "trace.variant")) p.trace_variant = (int)value;
+  else if (!strcmp(name, "trace.wide")) p.trace_wide = (int)value;
+  else if (!strcmp(name, "wide.leaf_max")) p.wide_leaf_max = (int)value;
   else if (!strcmp(name, "trace.zero_copy")) p.zero_copy = (int)value;
   else if (!strcmp(name, "trace.stage_chunk")) p.stage_chunk = (int)value;
   else if (!strcmp(name, "trace.chunk")) p.trace_chunk = (int)value;

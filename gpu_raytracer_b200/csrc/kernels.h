@@ -112,6 +112,43 @@ int launch_export_topology(const Node* nodes, const uint32_t* parent, uint64_t n
 int launch_unpack_sorted(const SortedTri* stris, uint64_t n, uint32_t* idx, cudaStream_t s);
 int launch_widen_keys(const uint32_t* in, uint64_t n, uint64_t* out, cudaStream_t s);
 
+// ---- A5w: wide BVH4 (wide.cu) ---------------------------------------------------
+// One BVH4 node, 128 bytes = one cache line: the boxes of up to four children in
+// struct-of-arrays form (component k of every float4 belongs to child k) and their
+// references.  A reference is
+//   internal  the split position g of the BVH2 node the child was collapsed from
+//             (Node4s live at the same index as their BVH2 node, so the collapse
+//             needs no allocation and no queue),
+//   leaf      kWideLeafBit | (count-1) << 29 | first : `count` (1..4) consecutive
+//             sorted triangles starting at `first`,
+//   empty     kWideEmpty.
+struct __align__(128) Node4 {
+  float4 lox, loy, loz, hix, hiy, hiz;
+  uint4 ref;
+  uint4 pad;
+};
+constexpr uint32_t kWideLeafBit = 0x80000000u;
+constexpr uint32_t kWideEmpty = 0x7FFFFFFFu;
+constexpr uint32_t kWideFirstMask = (1u << 29) - 1u;
+constexpr uint32_t kWideMaxTris = 1u << 29;  // `first` has 29 bits
+constexpr int kWideLeafMax = 4;      // upper bound of Params::wide_leaf_max (2 bits of a reference)
+constexpr int kWideLeafDefault = 2;  // measured best on B200 (profiles/r01e_wide.md)
+
+// Collapses the BVH2 (split numbering, refit.cu) into Node4s: wide[g] for every BVH2
+// node g holding more than kWideLeafMax triangles (n-1 slots).
+int launch_collapse4(const Node* nodes, uint64_t n, uint32_t leaf_max, Node4* wide, cudaStream_t s);
+// the reference traversal starts from: the root's Node4, or one leaf when the whole
+// scene fits a leaf (root = BvhHeader::root_node)
+inline uint32_t wide_root_ref(uint64_t n, int root, uint32_t leaf_max) {
+  if (n == 0) return kWideEmpty;
+  if (n <= (uint64_t)leaf_max) return kWideLeafBit | ((uint32_t)(n - 1) << 29);
+  return (uint32_t)root;
+}
+int launch_trace_wide(const Node4* wide, const SortedTri* stris, uint64_t n_tris, uint32_t root_ref,
+                      const float4* rays, uint64_t n_rays, uint32_t flags, float4* hits,
+                      unsigned long long* ray_counter, cudaStream_t s,
+                      unsigned long long* stats = nullptr);
+
 // ---- traversal (traverse.cu) -------------------------------------------------
 int launch_trace(const Node* nodes, const SortedTri* stris, uint64_t n_tris, int root,
                  const float4* rays,
@@ -125,6 +162,8 @@ struct Params {
   int trace_blocks_per_sm = 0;  // 0 = kernel default
   int trace_variant = 1;        // 0 = plain while-while, 1 = dynamic fetch + voted leaf loop
   int trace_chunk = 0, trace_refill_min = 0, trace_leaf_min = 0;  // 0 = defaults
+  int trace_wide = 1;           // 1 = use the BVH4 of handles built with RT_BUILD_WIDE4
+  int wide_leaf_max = kWideLeafDefault;  // triangles per BVH4 leaf (1..4), read when collapsing
   // bit 0: kernels read pinned host rays in place, bit 1: store hits to pinned host in
   // place.  Measured slower than the copy engines on B200/PCIe5 (profiles/r01b_e2e_modes.md),
   // so the default stages both.

@@ -6,8 +6,8 @@
 // ray fetch), so the grid never depends on the batch size and long rays do not
 // hold a whole CTA hostage.
 //
-// Per ray: the inner loop walks internal nodes — one 64-byte node fetch (4 x
-// LDG.128, two sectors) carries both children's boxes and ids; near child
+// Per ray: the inner loop walks internal nodes — one 64-byte node fetch (2 x
+// LDG.256, two sectors) carries both children's boxes and ids; near child
 // first, far child pushed on a per-thread stack in local memory — until it
 // reaches a leaf; the second loop intersects leaves (one triangle each, stored
 // as v0|prim, e1, e2 = 48 B) and pops.  Box tests cull with tnear <= tfar*pad
@@ -17,66 +17,10 @@
 //
 // Bound: L2/HBM latency and divergence, not streaming bandwidth; algorithmic
 // bytes/ray = 48 + 64 x nodes fetched + 48 x triangles tested.
-#include "common.cuh"
-#include "kernels.h"
+#include "trace_common.cuh"
 
 namespace rt {
 namespace {
-
-constexpr int kStack = 96;  // >= 63 key bits + 32 tie-break bits of tree depth
-constexpr int kEmpty = (int)0x80000000;
-constexpr float kSlabPad = 1.0000004f;
-constexpr int kTraceThreads = 256;
-
-struct RayState {
-  float ox, oy, oz, tmin;
-  float dx, dy, dz;
-  float ix, iy, iz;
-  float best_t, bu, bv;
-  int best_prim;
-};
-
-__device__ __forceinline__ bool slab(const float4 lo, const float4 hi, const RayState& r,
-                                     float& tn) {
-  const float t0x = (lo.x - r.ox) * r.ix, t1x = (hi.x - r.ox) * r.ix;
-  const float t0y = (lo.y - r.oy) * r.iy, t1y = (hi.y - r.oy) * r.iy;
-  const float t0z = (lo.z - r.oz) * r.iz, t1z = (hi.z - r.oz) * r.iz;
-  tn = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), r.tmin));
-  float tf = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fminf(fmaxf(t0z, t1z), r.best_t));
-  tf = tf * kSlabPad;
-  return tn <= tf;
-}
-
-// returns true when the hit was accepted
-__device__ __forceinline__ bool intersect(const SortedTri* __restrict__ stris, uint32_t j,
-                                          RayState& r) {
-  const float4* tp = reinterpret_cast<const float4*>(stris + j);
-  const float4 v0 = __ldg(tp), e1 = __ldg(tp + 1), e2 = __ldg(tp + 2);
-  const float px = fmaf(r.dy, e2.z, -(r.dz * e2.y));
-  const float py = fmaf(r.dz, e2.x, -(r.dx * e2.z));
-  const float pz = fmaf(r.dx, e2.y, -(r.dy * e2.x));
-  const float det = fmaf(e1.x, px, fmaf(e1.y, py, e1.z * pz));
-  if (det == 0.0f) return false;
-  const float inv = 1.0f / det;
-  const float sx = r.ox - v0.x, sy = r.oy - v0.y, sz = r.oz - v0.z;
-  const float u = fmaf(sx, px, fmaf(sy, py, sz * pz)) * inv;
-  const float qx = fmaf(sy, e1.z, -(sz * e1.y));
-  const float qy = fmaf(sz, e1.x, -(sx * e1.z));
-  const float qz = fmaf(sx, e1.y, -(sy * e1.x));
-  const float v = fmaf(r.dx, qx, fmaf(r.dy, qy, r.dz * qz)) * inv;
-  const float t = fmaf(e2.x, qx, fmaf(e2.y, qy, e2.z * qz)) * inv;
-  if (!((u >= 0.0f) && (v >= 0.0f) && ((u + v) <= 1.0f))) return false;
-  const int prim = __float_as_int(v0.w);
-  const bool ok = (t > r.tmin) &&
-                  ((t < r.best_t) || (t == r.best_t && r.best_prim >= 0 && prim < r.best_prim));
-  if (ok) {
-    r.best_t = t;
-    r.bu = u;
-    r.bv = v;
-    r.best_prim = prim;
-  }
-  return ok;
-}
 
 template <bool ANY, bool STATS>
 __device__ __forceinline__ void trace_one(const Node* __restrict__ nodes,
@@ -89,8 +33,8 @@ __device__ __forceinline__ void trace_one(const Node* __restrict__ nodes,
     // ---- internal nodes until a leaf (or nothing) is at hand ----------------
     while (node >= 0) {
       if (STATS) ++n_nodes;
-      const float4* np = reinterpret_cast<const float4*>(nodes + node);
-      const float4 lo0 = __ldg(np), hi0 = __ldg(np + 1), lo1 = __ldg(np + 2), hi1 = __ldg(np + 3);
+      const F8 c0h = ldg256(nodes + node), c1h = ldg256(&nodes[node].lo1);
+      const float4 lo0 = c0h.a, hi0 = c0h.b, lo1 = c1h.a, hi1 = c1h.b;
       float tn0, tn1;
       const bool h0 = slab(lo0, hi0, r, tn0);
       const bool h1 = slab(lo1, hi1, r, tn1);
@@ -251,8 +195,8 @@ trace_kernel_dyn(const Node* __restrict__ nodes, const SortedTri* __restrict__ s
       if (__popc(waiting) >= leaf_min) break;
       if (has_ray && node >= 0) {
         if (STATS) ++n_nodes;
-        const float4* np = reinterpret_cast<const float4*>(nodes + node);
-        const float4 lo0 = __ldg(np), hi0 = __ldg(np + 1), lo1 = __ldg(np + 2), hi1 = __ldg(np + 3);
+        const F8 c0h = ldg256(nodes + node), c1h = ldg256(&nodes[node].lo1);
+        const float4 lo0 = c0h.a, hi0 = c0h.b, lo1 = c1h.a, hi1 = c1h.b;
         float tn0, tn1;
         const bool h0 = slab(lo0, hi0, r, tn0);
         const bool h1 = slab(lo1, hi1, r, tn1);

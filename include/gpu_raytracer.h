@@ -61,6 +61,8 @@ extern "C" {
 /* build flags */
 #define RT_BUILD_KEEP_KEYS 1u /* keep the sorted Morton codes for bvh_read_sorted */
 #define RT_BUILD_TIMINGS 2u   /* record per-stage CUDA events (bvh_build_times) */
+#define RT_BUILD_WIDE4 4u     /* A5w: also collapse the tree to a 4-wide BVH; trace_rays then
+                                 walks that layout (same hits, bit for bit); n <= 2^29 */
 
 /* scene kinds for rt_gen_scene */
 #define RT_SCENE_CORNELL 0     /* config 1: 1,024 triangles, no parameters       */
@@ -97,8 +99,9 @@ enum {
   RT_STAGE_SORT = 2,   /* A3 */
   RT_STAGE_TOPOLOGY = 3, /* A4 */
   RT_STAGE_REFIT = 4,  /* A5 (leaf boxes, triangle reorder, bottom-up unions) */
-  RT_STAGE_TOTAL = 5,
-  RT_STAGE_COUNT = 6
+  RT_STAGE_TOTAL = 5,  /* all stages, RT_STAGE_WIDE included */
+  RT_STAGE_WIDE = 6,   /* A5w collapse to BVH4 (0 without RT_BUILD_WIDE4) */
+  RT_STAGE_COUNT = 7
 };
 
 /* ---- the three entry points (BASELINE.json:5) ------------- */
@@ -146,6 +149,20 @@ RT_API int bvh_build_times(const rt_bvh* h, float* ms);
 
 /* ---- refit: same topology, moved vertices -------------- */
 RT_API int refit_bvh(rt_bvh* h, const float* tris);
+
+/* ---- A5w: wide BVH4 -------------------------------- */
+
+/* Collapses the handle's binary tree to a 4-wide BVH (what RT_BUILD_WIDE4 does at
+ * build time); also for handles filled through bvh_device_buffers + bvh_commit. */
+RT_API int bvh_widen(rt_bvh* h);
+/* nodes4: host, (n-1) x 128 bytes, may be NULL.  Slot g holds the wide node made from
+ * the binary node that splits the sorted triangles after position g: 6 x float4
+ * lo.x[4] lo.y[4] lo.z[4] hi.x[4] hi.y[4] hi.z[4], then u32 ref[4], u32 n_children,
+ * 3 x u32 padding.  ref: 0x7FFFFFFF empty; bit 31 set = leaf, bits 29-30 = count-1,
+ * bits 0-28 = first sorted triangle; otherwise the slot of the child node.  Slots of
+ * subtrees with <= 4 triangles are unused (unspecified bytes).  root_ref: the
+ * reference traversal starts from. */
+RT_API int bvh_read_wide(const rt_bvh* h, void* nodes4, uint32_t* root_ref);
 
 /* ---- multi-GPU helpers ----------------------------------- */
 

@@ -71,6 +71,8 @@ def lib() -> C.CDLL:
         L.orc_build_times.argtypes = [vp, vp]
         L.orc_trace.argtypes = [vp, vp, u64, u32, vp, vp]
         L.orc_brute.argtypes = [vp, u64, vp, u64, u32, vp]
+        L.orc_collapse4.argtypes = [vp, u32, u64, vp, vp]
+        L.orc_collapse4.restype = u64
         _lib = L
     return _lib
 
@@ -170,6 +172,15 @@ class OracleBvh:
         if counters:
             return hits, (int(cnt[0]), int(cnt[1]))
         return hits
+
+    def collapse4(self, leaf_max: int = 4):
+        """A5w: the 4-wide tree in pre-order: (boxes [m,4,6] f32, desc [m,4,3] u32)."""
+        m = int(lib().orc_collapse4(self._h, leaf_max, 0, None, None))
+        boxes = np.zeros((m, 4, 6), dtype=np.float32)
+        desc = np.zeros((m, 4, 3), dtype=np.uint32)
+        if m:
+            lib().orc_collapse4(self._h, leaf_max, m, _p(boxes), _p(desc))
+        return boxes, desc
 
     def close(self):
         if self._h:

@@ -774,6 +774,120 @@ ORC_API void orc_trace(const void* h, const float* rays, uint64_t n, uint32_t fl
   if (counters) { counters[0] = nodes; counters[1] = tests; }
 }
 
+// ---------------------------------------------------------------------------
+// A5w: collapse of the binary tree to a 4-wide BVH (the
+// fixed rule is written out in DESIGN.md §4).  A wide node starts with the two
+// children of its binary node; up to two times the slot chosen by
+//   1. among slots with more than leaf_max triangles, the largest half area;
+//      if there is none,
+//   2. among slots with more than one triangle, the largest half area;
+//   ties -> leftmost slot; half area = (dx*dy + dy*dz) + dz*dx in float
+// is replaced in place by its two children.  Slots with <= leaf_max triangles
+// are leaf ranges [first, first+cnt) of the sorted order, the others are wide
+// nodes themselves.  Output: the wide nodes reachable from the root in
+// pre-order (children in slot order), so two implementations can be compared
+// array for array.
+//   boxes: cap x 4 x 6 floats (zeros for empty slots)
+//   desc:  cap x 4 x 3 u32: kind (0 empty, 1 leaf, 2 node), first, cnt for a
+//          leaf; kind, pre-order index of the child, 0 for a node
+// Returns the number of wide nodes (call with cap = 0 to size the arrays).
+// ---------------------------------------------------------------------------
+namespace {
+struct WSlot { uint32_t node, first, cnt; };
+
+float half_area(const float* bx) {
+  float dx = bx[3] - bx[0], dy = bx[4] - bx[1], dz = bx[5] - bx[2];
+  return (dx * dy + dy * dz) + dz * dx;
+}
+
+struct Collapser {
+  const Bvh& b;
+  uint32_t leaf_max;
+  uint64_t cap;
+  float* boxes;
+  uint32_t* desc;
+  std::vector<uint32_t> first, cnt;
+  uint64_t count = 0;
+
+  void ranges() {
+    const uint64_t n = b.n, nodes = 2 * n - 1;
+    const uint32_t leaf0 = (uint32_t)(n - 1);
+    first.assign(nodes, 0);
+    cnt.assign(nodes, 0);
+    for (uint64_t j = 0; j < n; ++j) { first[leaf0 + j] = (uint32_t)j; cnt[leaf0 + j] = 1; }
+    if (n < 2) return;
+    std::vector<uint32_t> stack{0};
+    std::vector<uint8_t> seen(n - 1, 0);
+    while (!stack.empty()) {
+      uint32_t i = stack.back();
+      if (!seen[i]) {
+        seen[i] = 1;
+        if (b.left[i] < leaf0) stack.push_back(b.left[i]);
+        if (b.right[i] < leaf0) stack.push_back(b.right[i]);
+      } else {
+        stack.pop_back();
+        first[i] = first[b.left[i]];
+        cnt[i] = cnt[b.left[i]] + cnt[b.right[i]];
+      }
+    }
+  }
+  WSlot slot_of(uint32_t node) const { return WSlot{node, first[node], cnt[node]}; }
+
+  uint64_t emit(uint32_t i) {
+    const uint64_t me = count++;
+    WSlot s[4];
+    int ns = 2;
+    s[0] = slot_of(b.left[i]);
+    s[1] = slot_of(b.right[i]);
+    for (int it = 0; it < 2; ++it) {
+      int best = -1;
+      float best_area = 0.0f;
+      for (int k = 0; k < ns; ++k)
+        if (s[k].cnt > leaf_max) {
+          float a = half_area(&b.boxes[(uint64_t)s[k].node * 6]);
+          if (best < 0 || a > best_area) { best = k; best_area = a; }
+        }
+      if (best < 0)
+        for (int k = 0; k < ns; ++k)
+          if (s[k].cnt > 1) {
+            float a = half_area(&b.boxes[(uint64_t)s[k].node * 6]);
+            if (best < 0 || a > best_area) { best = k; best_area = a; }
+          }
+      if (best < 0) break;
+      const uint32_t x = s[best].node;
+      for (int k = ns; k > best + 1; --k) s[k] = s[k - 1];
+      s[best] = slot_of(b.left[x]);
+      s[best + 1] = slot_of(b.right[x]);
+      ++ns;
+    }
+    for (int k = 0; k < 4; ++k) {
+      uint32_t d[3] = {0, 0, 0};
+      float bx[6] = {0, 0, 0, 0, 0, 0};
+      if (k < ns) {
+        std::memcpy(bx, &b.boxes[(uint64_t)s[k].node * 6], 24);
+        if (s[k].cnt <= leaf_max) { d[0] = 1; d[1] = s[k].first; d[2] = s[k].cnt; }
+        else { d[0] = 2; d[1] = (uint32_t)emit(s[k].node); }
+      }
+      if (me < cap) {
+        std::memcpy(boxes + (me * 4 + k) * 6, bx, 24);
+        std::memcpy(desc + (me * 4 + k) * 3, d, 12);
+      }
+    }
+    return me;
+  }
+};
+}  // namespace
+
+ORC_API uint64_t orc_collapse4(const void* h, uint32_t leaf_max, uint64_t cap, float* boxes,
+                               uint32_t* desc) {
+  const Bvh& b = *(const Bvh*)h;
+  if (b.n <= leaf_max) return 0;  // the whole scene is one leaf: no wide node
+  Collapser c{b, leaf_max, cap, boxes, desc, {}, {}, 0};
+  c.ranges();
+  c.emit(0);
+  return c.count;
+}
+
 // T0: all-pairs intersector, no BVH.  Same triangle test and acceptance rule.
 ORC_API void orc_brute(const float* tris, uint64_t n, const float* rays, uint64_t nr, uint32_t flags,
                        float* hits) {
