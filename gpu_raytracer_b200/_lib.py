@@ -51,6 +51,12 @@ SIGNATURES = {
     "bvh_device_buffers": (_i32, [_vp, C.POINTER(_vp), C.POINTER(_u64)]),
     "bvh_alloc_empty": (_i32, [_u64, _u32, C.POINTER(_vp)]),
     "bvh_commit": (_i32, [_vp]),
+    "rt_load_obj": (_i32, [C.c_char_p, C.POINTER(_vp), C.POINTER(_u64)]),
+    "rt_save_tris": (_i32, [C.c_char_p, _vp, _u64]),
+    "rt_load_tris": (_i32, [C.c_char_p, C.POINTER(_vp), C.POINTER(_u64)]),
+    "rt_free_host": (None, [_vp]),
+    "bvh_save": (_i32, [_vp, C.c_char_p]),
+    "bvh_load": (_i32, [C.c_char_p, C.POINTER(_vp)]),
     "rt_scene_size": (_u64, [_i32, _u64, _u64]),
     "rt_gen_scene": (_i32, [_i32, _u64, _u64, _u64, _u64, _u64, _vp]),
     "rt_gen_primary_rays": (_i32, [_vp, _u32, _u32, _u64, _u64, _vp]),

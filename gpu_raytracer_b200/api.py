@@ -122,6 +122,37 @@ WIDE_LEAF_BIT, WIDE_EMPTY, WIDE_FIRST_MASK = 0x80000000, 0x7FFFFFFF, (1 << 29) -
 
 
 # ---------------------------------------------------------------------------
+# scene files (host code of the library; no GPU needed)
+# ---------------------------------------------------------------------------
+def _take_host_tris(ptr: C.c_void_p, n: int) -> np.ndarray:
+    try:
+        if n == 0:
+            return np.zeros((0, 12), dtype=np.float32)
+        src = np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_float)), shape=(n, 12))
+        return src.copy()
+    finally:
+        L.lib().rt_free_host(ptr)
+
+
+def load_obj(path: str) -> np.ndarray:
+    """Triangles of a Wavefront OBJ file as float32 [n, 12] (rt_load_obj)."""
+    ptr, n = C.c_void_p(), C.c_uint64()
+    L.check(L.lib().rt_load_obj(str(path).encode(), C.byref(ptr), C.byref(n)))
+    return _take_host_tris(ptr, int(n.value))
+
+
+def save_tris(path: str, tris: np.ndarray) -> None:
+    tris = np.ascontiguousarray(tris, dtype=np.float32).reshape(-1, 12)
+    L.check(L.lib().rt_save_tris(str(path).encode(), tris.ctypes.data, tris.shape[0]))
+
+
+def load_tris(path: str) -> np.ndarray:
+    ptr, n = C.c_void_p(), C.c_uint64()
+    L.check(L.lib().rt_load_tris(str(path).encode(), C.byref(ptr), C.byref(n)))
+    return _take_host_tris(ptr, int(n.value))
+
+
+# ---------------------------------------------------------------------------
 # the BVH handle
 # ---------------------------------------------------------------------------
 class Bvh:
@@ -143,6 +174,16 @@ class Bvh:
         h = C.c_void_p()
         L.check(L.lib().build_bvh(_ptr(tris) if n else None, n, C.byref(opts), C.byref(h)))
         return cls(h.value)
+
+    @classmethod
+    def load(cls, path: str) -> "Bvh":
+        """A BVH written by ``save`` (bvh_load)."""
+        h = C.c_void_p()
+        L.check(L.lib().bvh_load(str(path).encode(), C.byref(h)))
+        return cls(h.value)
+
+    def save(self, path: str) -> None:
+        L.check(L.lib().bvh_save(self._h, str(path).encode()))
 
     @classmethod
     def alloc_empty(cls, n_tris: int, key_bits: int = 30) -> "Bvh":

@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 SO = os.path.join(HERE, "libgpu_raytracer_b200.so")
 SOURCES = ["api.cu", "scene_gen.cu", "ray_gen.cu", "morton.cu", "radix_sort.cu",
-           "refit.cu", "traverse.cu", "wide.cu"]
+           "refit.cu", "traverse.cu", "wide.cu", "scene_io.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-fmad=false",
               "-std=c++17", "-Xcompiler", "-fPIC,-fvisibility=hidden", "-shared",
               "-diag-suppress", "177"]

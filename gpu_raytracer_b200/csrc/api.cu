@@ -762,6 +762,82 @@ extern "C" int bvh_commit(rt_bvh* h) {
 }
 
 // ===========================================================================
+// BVH serialisation: header, node array, reordered triangles
+// ===========================================================================
+namespace {
+constexpr char kBvhMagic[8] = {'R', 'T', 'B', 'V', 'H', '1', 0, 0};
+constexpr size_t kIoChunk = 64u << 20;
+
+// device -> file or file -> device through one pinned bounce buffer
+int stream_file(FILE* f, void* dev, size_t bytes, bool to_file) {
+  if (bytes == 0) return 0;
+  void* host = nullptr;
+  const size_t chunk = bytes < kIoChunk ? bytes : kIoChunk;
+  RT_CUDA(cudaMallocHost(&host, chunk));
+  int rc = 0;
+  for (size_t off = 0; off < bytes && rc == 0; off += chunk) {
+    const size_t len = (bytes - off < chunk) ? bytes - off : chunk;
+    if (to_file) {
+      if (cudaMemcpy(host, (char*)dev + off, len, cudaMemcpyDeviceToHost) != cudaSuccess) rc = RT_ERR_CUDA;
+      else if (fwrite(host, 1, len, f) != len) rc = RT_ERR_INVALID;
+    } else {
+      if (fread(host, 1, len, f) != len) rc = RT_ERR_INVALID;
+      else if (cudaMemcpy((char*)dev + off, host, len, cudaMemcpyHostToDevice) != cudaSuccess) rc = RT_ERR_CUDA;
+    }
+  }
+  cudaFreeHost(host);
+  if (rc == RT_ERR_CUDA) return fail(RT_ERR_CUDA, "BVH file transfer: CUDA copy failed");
+  if (rc != 0) return fail(RT_ERR_INVALID, "BVH file transfer: short %s", to_file ? "write" : "read");
+  return 0;
+}
+}  // namespace
+
+extern "C" int bvh_save(const rt_bvh* h, const char* path) {
+  if (!h || !path) return fail(RT_ERR_INVALID, "bvh_save: NULL argument");
+  DeviceScope scope;
+  RT_TRY(scope.enter(h->device));
+  FILE* f = fopen(path, "wb");
+  if (!f) return fail(RT_ERR_INVALID, "bvh_save: cannot open %s", path);
+  const uint64_t n = h->n;
+  const uint32_t meta[2] = {h->key_bits, 0u};
+  int rc = (fwrite(kBvhMagic, 1, 8, f) == 8 && fwrite(&n, 8, 1, f) == 1 && fwrite(meta, 4, 2, f) == 2)
+               ? 0 : fail(RT_ERR_INVALID, "bvh_save: short write to %s", path);
+  if (rc == 0) rc = stream_file(f, h->header, sizeof(BvhHeader), true);
+  if (rc == 0) rc = stream_file(f, h->nodes, (n > 1 ? n - 1 : 0) * sizeof(Node), true);
+  if (rc == 0) rc = stream_file(f, h->stris, n * sizeof(SortedTri), true);
+  if (fclose(f) != 0 && rc == 0) rc = fail(RT_ERR_INVALID, "bvh_save: cannot close %s", path);
+  return rc;
+}
+
+extern "C" int bvh_load(const char* path, rt_bvh** out) {
+  if (!path || !out) return fail(RT_ERR_INVALID, "bvh_load: NULL argument");
+  *out = nullptr;
+  FILE* f = fopen(path, "rb");
+  if (!f) return fail(RT_ERR_INVALID, "bvh_load: cannot open %s", path);
+  char magic[8];
+  uint64_t n = 0;
+  uint32_t meta[2] = {0, 0};
+  if (fread(magic, 1, 8, f) != 8 || memcmp(magic, kBvhMagic, 8) != 0 || fread(&n, 8, 1, f) != 1 ||
+      fread(meta, 4, 2, f) != 2) {
+    fclose(f);
+    return fail(RT_ERR_INVALID, "bvh_load: %s is not a BVH file", path);
+  }
+  rt_bvh* h = nullptr;
+  int rc = bvh_alloc_empty(n, meta[0], &h);
+  if (rc == 0) rc = stream_file(f, h->header, sizeof(BvhHeader), false);
+  if (rc == 0) rc = stream_file(f, h->nodes, (n > 1 ? n - 1 : 0) * sizeof(Node), false);
+  if (rc == 0) rc = stream_file(f, h->stris, n * sizeof(SortedTri), false);
+  fclose(f);
+  if (rc == 0) rc = bvh_commit(h);
+  if (rc != 0) {
+    release(h);
+    return rc;
+  }
+  *out = h;
+  return RT_OK;
+}
+
+// ===========================================================================
 // generators and shading
 // ===========================================================================
 namespace {

@@ -176,6 +176,23 @@ RT_API int bvh_alloc_empty(uint64_t n_tris, uint32_t key_bits, rt_bvh** out);
 /* Re-reads the header buffer after it was filled by a broadcast. */
 RT_API int bvh_commit(rt_bvh* h);
 
+/* ---- scene input and BVH files --------------------- */
+
+/* Reads a Wavefront OBJ file: "v x y z" and "f a b c ..." records (a, a/t, a//n,
+ * a/t/n; negative = relative to the vertices read so far); polygons are fanned
+ * around their first vertex; every other record is ignored.  *tris_out: host
+ * memory, *n_out x 12 floats, to be released with rt_free_host.  Host code only. */
+RT_API int rt_load_obj(const char* path, float** tris_out, uint64_t* n_out);
+/* Flat binary triangle file: 8-byte magic "RTTRI1", u64 count, count x 12 floats. */
+RT_API int rt_save_tris(const char* path, const float* tris, uint64_t n);
+RT_API int rt_load_tris(const char* path, float** tris_out, uint64_t* n_out);
+RT_API void rt_free_host(void* p);
+/* A built BVH as a file (header, node array, reordered triangles) and back, on the
+ * current device; a loaded handle traces exactly like the one that was saved.  The
+ * optional BVH4 is not stored: call bvh_widen after bvh_load. */
+RT_API int bvh_save(const rt_bvh* h, const char* path);
+RT_API int bvh_load(const char* path, rt_bvh** out);
+
 /* ---- on-device generators (A8 and the §8d synthetic scenes) -------------- */
 
 RT_API uint64_t rt_scene_size(int kind, uint64_t p0, uint64_t p1);
