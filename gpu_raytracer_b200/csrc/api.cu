@@ -551,7 +551,7 @@ extern "C" int trace_rays_async(const rt_bvh* h, const float* rays, uint64_t n_r
   if (!h) return fail(RT_ERR_INVALID, "trace_rays: handle is NULL");
   if (n_rays == 0) return RT_OK;
   if (!rays || !hits) return fail(RT_ERR_INVALID, "trace_rays: rays or hits is NULL");
-  if (flags > 1u) return fail(RT_ERR_INVALID, "trace_rays: unknown flags 0x%x", flags);
+  if (flags > 3u) return fail(RT_ERR_INVALID, "trace_rays: unknown flags 0x%x", flags);
   DeviceScope scope;
   RT_TRY(scope.enter(h->device));
   return trace_device(h, reinterpret_cast<const float4*>(rays), n_rays, flags,
@@ -563,7 +563,7 @@ extern "C" int trace_rays(const rt_bvh* h, const float* rays, uint64_t n_rays, u
   if (!h) return fail(RT_ERR_INVALID, "trace_rays: handle is NULL");
   if (n_rays == 0) return RT_OK;
   if (!rays || !hits) return fail(RT_ERR_INVALID, "trace_rays: rays or hits is NULL");
-  if (flags > 1u) return fail(RT_ERR_INVALID, "trace_rays: unknown flags 0x%x", flags);
+  if (flags > 3u) return fail(RT_ERR_INVALID, "trace_rays: unknown flags 0x%x", flags);
   DeviceScope scope;
   RT_TRY(scope.enter(h->device));
   int d0 = -1, d1 = -1;
@@ -594,7 +594,7 @@ extern "C" int trace_rays_stats(const rt_bvh* h, const float* rays, uint64_t n_r
                                 float* hits, uint64_t* counters) {
   if (!h || !rays || !hits || !counters)
     return fail(RT_ERR_INVALID, "trace_rays_stats: NULL argument");
-  if (flags > 1u) return fail(RT_ERR_INVALID, "trace_rays_stats: unknown flags 0x%x", flags);
+  if (flags > 3u) return fail(RT_ERR_INVALID, "trace_rays_stats: unknown flags 0x%x", flags);
   counters[0] = counters[1] = 0;
   if (n_rays == 0) return RT_OK;
   DeviceScope scope;

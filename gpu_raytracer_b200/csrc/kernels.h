@@ -18,9 +18,10 @@ struct __align__(64) Node {
   float4 lo0, hi0, lo1, hi1;
 };
 
-// Reordered triangle, 48 bytes: v0.xyz + original primitive index, e1, e2.
+// Reordered triangle, 48 bytes: v0.xyz + original primitive index, v1, v2 (raw
+// vertices: both intersectors derive what they need with the oracle's operations).
 struct __align__(16) SortedTri {
-  float4 v0p, e1, e2;
+  float4 v0p, v1, v2;
 };
 
 // 16-float header living next to the node array (broadcast with it).

@@ -19,7 +19,7 @@
 // One thread per leaf, one CTA per kRefitLeaves = 256 consecutive leaves (measured:
 // 1024 -> 0.65 ms, 512 -> 0.62, 256 -> 0.59, 128 -> 0.59, 64 -> 0.92 ms for 10M).  The
 // thread gathers its triangle through the sorted index, stores it in traversal
-// form {v0 | prim, e1, e2}, then climbs: it writes the box it carries (child
+// form {v0 | prim, v1, v2}, then climbs: it writes the box it carries (child
 // id, far end of its range) into its slot of node g — one full 32-byte sector —
 // and meets its sibling.
 //   phase 1  meetings whose split lies inside the CTA's leaf group happen in
@@ -238,8 +238,8 @@ build_walk_kernel(const float4* __restrict__ tris, const uint32_t* __restrict__ 
                  c = __ldg(tris + 3 * (uint64_t)prim + 2);
     float4* st = reinterpret_cast<float4*>(stris + j);
     st[0] = make_float4(a.x, a.y, a.z, __uint_as_float(prim));
-    st[1] = make_float4(b.x - a.x, b.y - a.y, b.z - a.z, 0.0f);
-    st[2] = make_float4(c.x - a.x, c.y - a.y, c.z - a.z, 0.0f);
+    st[1] = make_float4(b.x, b.y, b.z, 0.0f);
+    st[2] = make_float4(c.x, c.y, c.z, 0.0f);
     bx.lx = omin(omin(a.x, b.x), c.x); bx.ly = omin(omin(a.y, b.y), c.y); bx.lz = omin(omin(a.z, b.z), c.z);
     bx.hx = omax(omax(a.x, b.x), c.x); bx.hy = omax(omax(a.y, b.y), c.y); bx.hz = omax(omax(a.z, b.z), c.z);
   }
@@ -352,8 +352,8 @@ refit_kernel(const float4* __restrict__ tris, uint32_t n, const uint32_t* __rest
                c = __ldg(tris + 3 * (uint64_t)prim + 2);
   float4* st = reinterpret_cast<float4*>(stris + j);
   st[0] = make_float4(a.x, a.y, a.z, __uint_as_float(prim));
-  st[1] = make_float4(b.x - a.x, b.y - a.y, b.z - a.z, 0.0f);
-  st[2] = make_float4(c.x - a.x, c.y - a.y, c.z - a.z, 0.0f);
+  st[1] = make_float4(b.x, b.y, b.z, 0.0f);
+  st[2] = make_float4(c.x, c.y, c.z, 0.0f);
   Box bx;
   bx.lx = omin(omin(a.x, b.x), c.x); bx.ly = omin(omin(a.y, b.y), c.y); bx.lz = omin(omin(a.z, b.z), c.z);
   bx.hx = omax(omax(a.x, b.x), c.x); bx.hy = omax(omax(a.y, b.y), c.y); bx.hz = omax(omax(a.z, b.z), c.z);

@@ -46,26 +46,8 @@ __device__ __forceinline__ bool slab(const float4 lo, const float4 hi, const Ray
   return tn <= tf;
 }
 
-// returns true when the hit was accepted
-__device__ __forceinline__ bool intersect(const SortedTri* __restrict__ stris, uint32_t j,
-                                          RayState& r) {
-  const float4* tp = reinterpret_cast<const float4*>(stris + j);
-  const float4 v0 = __ldg(tp), e1 = __ldg(tp + 1), e2 = __ldg(tp + 2);
-  const float px = fmaf(r.dy, e2.z, -(r.dz * e2.y));
-  const float py = fmaf(r.dz, e2.x, -(r.dx * e2.z));
-  const float pz = fmaf(r.dx, e2.y, -(r.dy * e2.x));
-  const float det = fmaf(e1.x, px, fmaf(e1.y, py, e1.z * pz));
-  if (det == 0.0f) return false;
-  const float inv = 1.0f / det;
-  const float sx = r.ox - v0.x, sy = r.oy - v0.y, sz = r.oz - v0.z;
-  const float u = fmaf(sx, px, fmaf(sy, py, sz * pz)) * inv;
-  const float qx = fmaf(sy, e1.z, -(sz * e1.y));
-  const float qy = fmaf(sz, e1.x, -(sx * e1.z));
-  const float qz = fmaf(sx, e1.y, -(sy * e1.x));
-  const float v = fmaf(r.dx, qx, fmaf(r.dy, qy, r.dz * qz)) * inv;
-  const float t = fmaf(e2.x, qx, fmaf(e2.y, qy, e2.z * qz)) * inv;
-  if (!((u >= 0.0f) && (v >= 0.0f) && ((u + v) <= 1.0f))) return false;
-  const int prim = __float_as_int(v0.w);
+// acceptance rule (A6): closest t in (tmin, best]; on equal t the smaller primitive wins
+__device__ __forceinline__ bool accept_hit(float t, float u, float v, int prim, RayState& r) {
   const bool ok = (t > r.tmin) &&
                   ((t < r.best_t) || (t == r.best_t && r.best_prim >= 0 && prim < r.best_prim));
   if (ok) {
@@ -77,6 +59,90 @@ __device__ __forceinline__ bool intersect(const SortedTri* __restrict__ stris, u
   return ok;
 }
 
+// Moeller-Trumbore, two-sided.  The triangle record holds the raw vertices
+// {v0 | prim, v1, v2}; the edges are one subtraction each, as in the oracle.
+// Returns true when the hit was accepted.
+__device__ __forceinline__ bool intersect(const SortedTri* __restrict__ stris, uint32_t j,
+                                          RayState& r) {
+  const float4* tp = reinterpret_cast<const float4*>(stris + j);
+  const float4 v0 = __ldg(tp), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
+  const float e1x = v1.x - v0.x, e1y = v1.y - v0.y, e1z = v1.z - v0.z;
+  const float e2x = v2.x - v0.x, e2y = v2.y - v0.y, e2z = v2.z - v0.z;
+  const float px = fmaf(r.dy, e2z, -(r.dz * e2y));
+  const float py = fmaf(r.dz, e2x, -(r.dx * e2z));
+  const float pz = fmaf(r.dx, e2y, -(r.dy * e2x));
+  const float det = fmaf(e1x, px, fmaf(e1y, py, e1z * pz));
+  if (det == 0.0f) return false;
+  const float inv = 1.0f / det;
+  const float sx = r.ox - v0.x, sy = r.oy - v0.y, sz = r.oz - v0.z;
+  const float u = fmaf(sx, px, fmaf(sy, py, sz * pz)) * inv;
+  const float qx = fmaf(sy, e1z, -(sz * e1y));
+  const float qy = fmaf(sz, e1x, -(sx * e1z));
+  const float qz = fmaf(sx, e1y, -(sy * e1x));
+  const float v = fmaf(r.dx, qx, fmaf(r.dy, qy, r.dz * qz)) * inv;
+  const float t = fmaf(e2x, qx, fmaf(e2y, qy, e2z * qz)) * inv;
+  if (!((u >= 0.0f) && (v >= 0.0f) && ((u + v) <= 1.0f))) return false;
+  return accept_hit(t, u, v, __float_as_int(v0.w), r);
+}
+
+// Watertight test (Woop, Benthin & Wald 2013), RT_TRACE_WATERTIGHT: the ray is
+// sheared so its dominant axis is +z (kx, ky, kz, S* are per-ray constants); the
+// scaled edge functions U, V, W decide the hit and are recomputed in double when one
+// of them is exactly zero, so a ray through a shared edge or vertex hits one of the
+// triangles around it.  Same operation order as the oracle's tri_test_wt.
+struct WtRay {
+  int kx, ky, kz;
+  float Sx, Sy, Sz;
+};
+__device__ __forceinline__ float sel3(float x, float y, float z, int k) {
+  return k == 0 ? x : (k == 1 ? y : z);
+}
+__device__ __forceinline__ WtRay wt_setup(const RayState& r) {
+  WtRay w;
+  w.kz = 0;
+  float m = fabsf(r.dx);
+  if (fabsf(r.dy) > m) { w.kz = 1; m = fabsf(r.dy); }
+  if (fabsf(r.dz) > m) w.kz = 2;
+  w.kx = (w.kz + 1) % 3;
+  w.ky = (w.kx + 1) % 3;
+  const float dz = sel3(r.dx, r.dy, r.dz, w.kz);
+  if (dz < 0.0f) {
+    const int t = w.kx;
+    w.kx = w.ky;
+    w.ky = t;
+  }
+  w.Sx = sel3(r.dx, r.dy, r.dz, w.kx) / dz;
+  w.Sy = sel3(r.dx, r.dy, r.dz, w.ky) / dz;
+  w.Sz = 1.0f / dz;
+  return w;
+}
+__device__ __forceinline__ bool intersect_wt(const SortedTri* __restrict__ stris, uint32_t j,
+                                             RayState& r, const WtRay& w) {
+  const float4* tp = reinterpret_cast<const float4*>(stris + j);
+  const float4 v0 = __ldg(tp), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
+  const float ax = v0.x - r.ox, ay = v0.y - r.oy, az = v0.z - r.oz;
+  const float bx = v1.x - r.ox, by = v1.y - r.oy, bz = v1.z - r.oz;
+  const float cx = v2.x - r.ox, cy = v2.y - r.oy, cz = v2.z - r.oz;
+  const float Akz = sel3(ax, ay, az, w.kz), Bkz = sel3(bx, by, bz, w.kz), Ckz = sel3(cx, cy, cz, w.kz);
+  const float Ax = sel3(ax, ay, az, w.kx) - w.Sx * Akz, Ay = sel3(ax, ay, az, w.ky) - w.Sy * Akz;
+  const float Bx = sel3(bx, by, bz, w.kx) - w.Sx * Bkz, By = sel3(bx, by, bz, w.ky) - w.Sy * Bkz;
+  const float Cx = sel3(cx, cy, cz, w.kx) - w.Sx * Ckz, Cy = sel3(cx, cy, cz, w.ky) - w.Sy * Ckz;
+  float U = Cx * By - Cy * Bx;
+  float V = Ax * Cy - Ay * Cx;
+  float W = Bx * Ay - By * Ax;
+  if (U == 0.0f || V == 0.0f || W == 0.0f) {
+    U = (float)((double)Cx * (double)By - (double)Cy * (double)Bx);
+    V = (float)((double)Ax * (double)Cy - (double)Ay * (double)Cx);
+    W = (float)((double)Bx * (double)Ay - (double)By * (double)Ax);
+  }
+  if ((U < 0.0f || V < 0.0f || W < 0.0f) && (U > 0.0f || V > 0.0f || W > 0.0f)) return false;
+  const float det = (U + V) + W;
+  if (det == 0.0f) return false;
+  const float Az = w.Sz * Akz, Bz = w.Sz * Bkz, Cz = w.Sz * Ckz;
+  const float T = (U * Az + V * Bz) + W * Cz;
+  const float inv = 1.0f / det;
+  return accept_hit(T * inv, V * inv, W * inv, __float_as_int(v0.w), r);
+}
 
 // fills the ray state from the two float4 of a ray record
 __device__ __forceinline__ void load_ray(RayState& r, const float4 ro, const float4 rd) {
@@ -96,5 +162,17 @@ __device__ __forceinline__ float4 hit_record(const RayState& r, bool any) {
   if (any) return make_float4(0.0f, 0.0f, 0.0f, __int_as_float(0x7FFFFFFF));
   return make_float4(r.best_t, r.bu, r.bv, __int_as_float(r.best_prim));
 }
+
+// expands M(any, stats, watertight) for the run-time values of the three flags
+#define RT_DISPATCH3(M, a, b, c)              \
+  do {                                        \
+    if (a) {                                  \
+      if (b) { if (c) M(true, true, true); else M(true, true, false); }       \
+      else   { if (c) M(true, false, true); else M(true, false, false); }     \
+    } else {                                  \
+      if (b) { if (c) M(false, true, true); else M(false, true, false); }     \
+      else   { if (c) M(false, false, true); else M(false, false, false); }   \
+    }                                         \
+  } while (0)
 
 }  // namespace rt

@@ -10,7 +10,7 @@
 // LDG.256, two sectors) carries both children's boxes and ids; near child
 // first, far child pushed on a per-thread stack in local memory — until it
 // reaches a leaf; the second loop intersects leaves (one triangle each, stored
-// as v0|prim, e1, e2 = 48 B) and pops.  Box tests cull with tnear <= tfar*pad
+// as v0|prim, v1, v2 = 48 B) and pops.  Box tests cull with tnear <= tfar*pad
 // (<=, so equal-t candidates in other subtrees are still visited) and the
 // acceptance rule breaks equal-t ties towards the smaller primitive index, so
 // the result does not depend on traversal order.
@@ -22,10 +22,12 @@
 namespace rt {
 namespace {
 
-template <bool ANY, bool STATS>
+template <bool ANY, bool STATS, bool WT>
 __device__ __forceinline__ void trace_one(const Node* __restrict__ nodes,
                                           const SortedTri* __restrict__ stris, int root,
                                           RayState& r, uint32_t& n_nodes, uint32_t& n_tests) {
+  WtRay wr;
+  if (WT) wr = wt_setup(r);
   int stack[kStack];
   int sp = 0;
   int node = root;
@@ -54,7 +56,8 @@ __device__ __forceinline__ void trace_one(const Node* __restrict__ nodes,
     // ---- leaves ----------------------------------------------------------------
     while (node < 0 && node != kEmpty) {
       if (STATS) ++n_tests;
-      const bool hit = intersect(stris, (uint32_t)(~node), r);
+      const bool hit = WT ? intersect_wt(stris, (uint32_t)(~node), r, wr)
+                          : intersect(stris, (uint32_t)(~node), r);
       if (ANY && hit) return;
       node = (sp > 0) ? stack[--sp] : kEmpty;
     }
@@ -63,7 +66,7 @@ __device__ __forceinline__ void trace_one(const Node* __restrict__ nodes,
 
 // STATS: also counts node fetches and triangle tests into stats[0..1] (the
 // algorithmic-bytes figure of the roofline; never used on the timed path)
-template <bool ANY, bool STATS>
+template <bool ANY, bool STATS, bool WT>
 __global__ void __launch_bounds__(kTraceThreads)
 trace_kernel(const Node* __restrict__ nodes, const SortedTri* __restrict__ stris, uint32_t n_tris,
              int root, const float4* __restrict__ rays, unsigned long long n_rays,
@@ -90,7 +93,7 @@ trace_kernel(const Node* __restrict__ nodes, const SortedTri* __restrict__ stris
       r.iy = fminf(fmaxf(1.0f / rd.y, -fmx), fmx);
       r.iz = fminf(fmaxf(1.0f / rd.z, -fmx), fmx);
       r.best_t = rd.w; r.bu = 0.0f; r.bv = 0.0f; r.best_prim = -1;
-      if (n_tris != 0) trace_one<ANY, STATS>(nodes, stris, root, r, n_nodes, n_tests);
+      if (n_tris != 0) trace_one<ANY, STATS, WT>(nodes, stris, root, r, n_nodes, n_tests);
       float4 h;
       if (r.best_prim < 0) h = make_float4(inf, 0.0f, 0.0f, __int_as_float(-1));
       else if (ANY) h = make_float4(0.0f, 0.0f, 0.0f, __int_as_float(0x7FFFFFFF));
@@ -125,7 +128,7 @@ trace_kernel(const Node* __restrict__ nodes, const SortedTri* __restrict__ stris
 // acceptance) is the shared code above, so results are bit-identical to
 // variant 0 and to the oracle whatever the scheduling.
 // ---------------------------------------------------------------------------
-template <bool ANY, bool STATS>
+template <bool ANY, bool STATS, bool WT>
 __global__ void __launch_bounds__(kTraceThreads)
 trace_kernel_dyn(const Node* __restrict__ nodes, const SortedTri* __restrict__ stris,
                  uint32_t n_tris, int root, const float4* __restrict__ rays,
@@ -144,6 +147,7 @@ trace_kernel_dyn(const Node* __restrict__ nodes, const SortedTri* __restrict__ s
   unsigned long long my_ray = 0;
   RayState r;
   r.best_prim = -1;
+  WtRay wr = {0, 1, 2, 0.0f, 0.0f, 0.0f};
   unsigned long long chunk_next = 0, chunk_end = 0;  // warp-uniform
   bool exhausted = false;                            // warp-uniform
 
@@ -175,6 +179,7 @@ trace_kernel_dyn(const Node* __restrict__ nodes, const SortedTri* __restrict__ s
         r.iy = fminf(fmaxf(1.0f / rd.y, -fmx), fmx);
         r.iz = fminf(fmaxf(1.0f / rd.z, -fmx), fmx);
         r.best_t = rd.w; r.bu = 0.0f; r.bv = 0.0f; r.best_prim = -1;
+        if (WT) wr = wt_setup(r);
         has_ray = true;
         sp = 0;
         node = (n_tris != 0) ? root : kEmpty;
@@ -218,7 +223,8 @@ trace_kernel_dyn(const Node* __restrict__ nodes, const SortedTri* __restrict__ s
     // ---- one leaf per waiting lane ---------------------------------------------
     if (has_ray && node < 0 && node != kEmpty) {
       if (STATS) ++n_tests;
-      const bool hit = intersect(stris, (uint32_t)(~node), r);
+      const bool hit = WT ? intersect_wt(stris, (uint32_t)(~node), r, wr)
+                          : intersect(stris, (uint32_t)(~node), r);
       if (ANY && hit) {
         node = kEmpty;
         sp = 0;
@@ -260,7 +266,8 @@ int launch_trace(const Node* nodes, const SortedTri* stris, uint64_t n_tris, int
   uint64_t blocks = (uint64_t)num_sms() * bps;
   const uint64_t need = (n_rays + kTraceThreads - 1) / kTraceThreads;
   if (blocks > need) blocks = need;
-  const bool any = (flags & 1u) != 0;
+  const bool any = (flags & 1u) != 0, wt = (flags & 2u) != 0;
+  const bool st = stats != nullptr;
   if (params().trace_variant != 0) {
     const Params& p = params();
     int chunk = p.trace_chunk > 0 ? p.trace_chunk : 64;
@@ -268,30 +275,18 @@ int launch_trace(const Node* nodes, const SortedTri* stris, uint64_t n_tris, int
     if (p.trace_chunk <= 0 && n_rays < blocks * (kTraceThreads / 32) * (uint64_t)chunk * 2) chunk = 32;
     const int refill_min = p.trace_refill_min > 0 ? p.trace_refill_min : 16;
     const int leaf_min = p.trace_leaf_min > 0 ? p.trace_leaf_min : 8;
-#define RT_TRACE_DYN(A, S)                                                 \
-  trace_kernel_dyn<A, S><<<(unsigned)blocks, kTraceThreads, 0, s>>>(       \
+#define RT_TRACE_DYN(A, S, W)                                                 \
+  trace_kernel_dyn<A, S, W><<<(unsigned)blocks, kTraceThreads, 0, s>>>(       \
       nodes, stris, (uint32_t)n_tris, root, rays, n_rays, hits, ray_counter, stats, chunk, refill_min, leaf_min)
-    if (stats) {
-      if (any) RT_TRACE_DYN(true, true);
-      else RT_TRACE_DYN(false, true);
-    } else {
-      if (any) RT_TRACE_DYN(true, false);
-      else RT_TRACE_DYN(false, false);
-    }
+    RT_DISPATCH3(RT_TRACE_DYN, any, st, wt);
 #undef RT_TRACE_DYN
     RT_LAUNCHED();
     return 0;
   }
-#define RT_TRACE_LAUNCH(A, S)                                          \
-  trace_kernel<A, S><<<(unsigned)blocks, kTraceThreads, 0, s>>>(       \
+#define RT_TRACE_LAUNCH(A, S, W)                                          \
+  trace_kernel<A, S, W><<<(unsigned)blocks, kTraceThreads, 0, s>>>(       \
       nodes, stris, (uint32_t)n_tris, root, rays, n_rays, hits, ray_counter, stats)
-  if (stats) {
-    if (any) RT_TRACE_LAUNCH(true, true);
-    else RT_TRACE_LAUNCH(false, true);
-  } else {
-    if (any) RT_TRACE_LAUNCH(true, false);
-    else RT_TRACE_LAUNCH(false, false);
-  }
+  RT_DISPATCH3(RT_TRACE_LAUNCH, any, st, wt);
 #undef RT_TRACE_LAUNCH
   RT_LAUNCHED();
   return 0;

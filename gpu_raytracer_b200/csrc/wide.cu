@@ -157,7 +157,7 @@ __device__ __forceinline__ uint32_t pick(const uint4 v, uint32_t k) {
   return (k & 2u) ? ((k & 1u) ? v.w : v.z) : ((k & 1u) ? v.y : v.x);
 }
 
-template <bool ANY, bool STATS>
+template <bool ANY, bool STATS, bool WT>
 __global__ void __launch_bounds__(kTraceThreads)
 trace_wide_kernel(const Node4* __restrict__ wide, const SortedTri* __restrict__ stris,
                   uint32_t root_ref, const float4* __restrict__ rays, unsigned long long n_rays,
@@ -174,6 +174,7 @@ trace_wide_kernel(const Node4* __restrict__ wide, const SortedTri* __restrict__ 
   unsigned long long my_ray = 0;
   RayState r;
   r.best_prim = -1;
+  WtRay wr = {0, 1, 2, 0.0f, 0.0f, 0.0f};
   unsigned long long chunk_next = 0, chunk_end = 0;  // warp-uniform
   bool exhausted = false;                            // warp-uniform
 
@@ -198,6 +199,7 @@ trace_wide_kernel(const Node4* __restrict__ wide, const SortedTri* __restrict__ 
       if (!has_ray && slot < avail) {
         my_ray = chunk_next + slot;
         load_ray(r, ld_stream(rays + 2 * my_ray), ld_stream(rays + 2 * my_ray + 1));
+        if (WT) wr = wt_setup(r);
         has_ray = true;
         sp = 0;
         cur = root_ref;
@@ -245,7 +247,8 @@ trace_wide_kernel(const Node4* __restrict__ wide, const SortedTri* __restrict__ 
     // ---- one triangle per waiting lane ---------------------------------------------
     if (has_ray && (cur & kWideLeafBit)) {
       if (STATS) ++n_tests;
-      const bool hit = intersect(stris, cur & kWideFirstMask, r);
+      const bool hit = WT ? intersect_wt(stris, cur & kWideFirstMask, r, wr)
+                          : intersect(stris, cur & kWideFirstMask, r);
       if (ANY && hit) {
         cur = kWideEmpty;
         sp = 0;
@@ -294,7 +297,7 @@ int launch_trace_wide(const Node4* wide, const SortedTri* stris, uint64_t n_tris
     static std::atomic<int> resident{0};
     int occ = resident.load(std::memory_order_relaxed);
     if (occ == 0) {
-      RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, trace_wide_kernel<false, false>,
+      RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, trace_wide_kernel<false, false, false>,
                                                             kTraceThreads, 0));
       if (occ < 1) occ = 1;
       resident.store(occ, std::memory_order_relaxed);
@@ -304,22 +307,16 @@ int launch_trace_wide(const Node4* wide, const SortedTri* stris, uint64_t n_tris
   uint64_t blocks = (uint64_t)num_sms() * bps;
   const uint64_t need = (n_rays + kTraceThreads - 1) / kTraceThreads;
   if (blocks > need) blocks = need;
-  const bool any = (flags & 1u) != 0;
+  const bool any = (flags & 1u) != 0, wt = (flags & 2u) != 0;
   int chunk = p.trace_chunk > 0 ? p.trace_chunk : 64;
   if (p.trace_chunk <= 0 && n_rays < blocks * (kTraceThreads / 32) * (uint64_t)chunk * 2) chunk = 32;
   const int refill_min = p.trace_refill_min > 0 ? p.trace_refill_min : 16;
   const int leaf_min = p.trace_leaf_min > 0 ? p.trace_leaf_min : 8;
   if (n_tris == 0) root_ref = kWideEmpty;
-#define RT_TRACE_WIDE(A, S)                                              \
-  trace_wide_kernel<A, S><<<(unsigned)blocks, kTraceThreads, 0, s>>>(    \
+#define RT_TRACE_WIDE(A, S, W)                                              \
+  trace_wide_kernel<A, S, W><<<(unsigned)blocks, kTraceThreads, 0, s>>>(    \
       wide, stris, root_ref, rays, n_rays, hits, ray_counter, stats, chunk, refill_min, leaf_min)
-  if (stats) {
-    if (any) RT_TRACE_WIDE(true, true);
-    else RT_TRACE_WIDE(false, true);
-  } else {
-    if (any) RT_TRACE_WIDE(true, false);
-    else RT_TRACE_WIDE(false, false);
-  }
+  RT_DISPATCH3(RT_TRACE_WIDE, any, stats != nullptr, wt);
 #undef RT_TRACE_WIDE
   RT_LAUNCHED();
   return 0;

@@ -56,6 +56,8 @@ extern "C" {
 /* trace_rays flags (A6) */
 #define RT_TRACE_CLOSEST 0u
 #define RT_TRACE_ANY 1u
+#define RT_TRACE_WATERTIGHT 2u /* A7 option: Woop-Benthin-Wald watertight triangle test instead of
+                                  Moeller-Trumbore; may be combined with RT_TRACE_ANY */
 #define RT_ANY_HIT_PRIM 0x7FFFFFFF
 
 /* build flags */

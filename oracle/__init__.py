@@ -21,7 +21,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _SO = os.path.join(_HERE, "liblbvh_oracle.so")
 
 SCENE_CORNELL, SCENE_SOUP, SCENE_SPHEREFLAKE, SCENE_TERRAIN = 0, 1, 2, 3
-TRACE_CLOSEST, TRACE_ANY = 0, 1
+TRACE_CLOSEST, TRACE_ANY, TRACE_WATERTIGHT = 0, 1, 2
 ANY_HIT_PRIM = 0x7FFFFFFF
 
 

@@ -524,6 +524,58 @@ inline bool tri_test(const float* p, const Ray& r, float& t, float& u, float& v)
   return (u >= 0.0f) && (v >= 0.0f) && ((u + v) <= 1.0f);
 }
 
+// ---------------------------------------------------------------------------
+// A7 option: watertight ray/triangle test (Woop, Benthin & Wald 2013).  The ray
+// is sheared so that its dominant axis becomes +z; the three scaled edge
+// functions U, V, W decide the hit, recomputed in double precision when one of
+// them is exactly zero (a ray through an edge or a vertex), so no ray slips
+// between two triangles sharing that edge.  Plain * + - / in one fixed order
+// (no contraction); barycentrics are returned in the Moeller-Trumbore
+// convention (u weights v1, v weights v2).
+// ---------------------------------------------------------------------------
+struct WtRay { int kx, ky, kz; float Sx, Sy, Sz; };
+
+inline WtRay wt_setup(const Ray& r) {
+  WtRay w;
+  w.kz = 0;
+  if (std::fabs(r.d[1]) > std::fabs(r.d[w.kz])) w.kz = 1;
+  if (std::fabs(r.d[2]) > std::fabs(r.d[w.kz])) w.kz = 2;
+  w.kx = (w.kz + 1) % 3;
+  w.ky = (w.kx + 1) % 3;
+  if (r.d[w.kz] < 0.0f) std::swap(w.kx, w.ky);
+  w.Sx = r.d[w.kx] / r.d[w.kz];
+  w.Sy = r.d[w.ky] / r.d[w.kz];
+  w.Sz = 1.0f / r.d[w.kz];
+  return w;
+}
+
+inline bool tri_test_wt(const float* p, const Ray& r, const WtRay& w, float& t, float& u, float& v) {
+  const float A[3] = {p[0] - r.o[0], p[1] - r.o[1], p[2] - r.o[2]};
+  const float B[3] = {p[4] - r.o[0], p[5] - r.o[1], p[6] - r.o[2]};
+  const float C[3] = {p[8] - r.o[0], p[9] - r.o[1], p[10] - r.o[2]};
+  const float Ax = A[w.kx] - w.Sx * A[w.kz], Ay = A[w.ky] - w.Sy * A[w.kz];
+  const float Bx = B[w.kx] - w.Sx * B[w.kz], By = B[w.ky] - w.Sy * B[w.kz];
+  const float Cx = C[w.kx] - w.Sx * C[w.kz], Cy = C[w.ky] - w.Sy * C[w.kz];
+  float U = Cx * By - Cy * Bx;
+  float V = Ax * Cy - Ay * Cx;
+  float W = Bx * Ay - By * Ax;
+  if (U == 0.0f || V == 0.0f || W == 0.0f) {
+    U = (float)((double)Cx * (double)By - (double)Cy * (double)Bx);
+    V = (float)((double)Ax * (double)Cy - (double)Ay * (double)Cx);
+    W = (float)((double)Bx * (double)Ay - (double)By * (double)Ax);
+  }
+  if ((U < 0.0f || V < 0.0f || W < 0.0f) && (U > 0.0f || V > 0.0f || W > 0.0f)) return false;
+  const float det = (U + V) + W;
+  if (det == 0.0f) return false;
+  const float Az = w.Sz * A[w.kz], Bz = w.Sz * B[w.kz], Cz = w.Sz * C[w.kz];
+  const float T = (U * Az + V * Bz) + W * Cz;
+  const float inv = 1.0f / det;
+  t = T * inv;
+  u = V * inv;
+  v = W * inv;
+  return true;
+}
+
 // A6 acceptance rule: closest t in (tmin, tmax); on equal t the smaller
 // primitive index wins.
 inline bool accept(float t, int32_t prim, float tmin, float best_t, int32_t best_prim) {
@@ -542,7 +594,7 @@ inline bool slab(const float* bx, const Ray& r, const float idir[3], float best_
   return tn <= tf;
 }
 
-enum { TRACE_CLOSEST = 0, TRACE_ANY = 1 };
+enum { TRACE_CLOSEST = 0, TRACE_ANY = 1, TRACE_WATERTIGHT = 2 };
 const int32_t kAnyHitPrim = 0x7FFFFFFF;
 
 inline Hit miss_hit() { Hit h; h.t = std::numeric_limits<float>::infinity(); h.u = 0; h.v = 0; h.prim = -1; return h; }
@@ -564,12 +616,16 @@ Hit trace_one(const Bvh& b, const Ray& r, uint32_t flags, uint64_t& nodes, uint6
   int sp = 0;
   uint32_t node = 0;  // root: internal 0, or leaf 0 when n == 1 (leaf0 == 0)
   bool any = (flags & TRACE_ANY) != 0;
+  const bool wt = (flags & TRACE_WATERTIGHT) != 0;
+  WtRay wr = {0, 1, 2, 0, 0, 0};
+  if (wt) wr = wt_setup(r);
   for (;;) {
     if (node >= leaf0) {
       uint32_t prim = b.idx[node - leaf0];
       float t, u, v;
       ++tests;
-      if (tri_test(&b.tris[(uint64_t)prim * 12], r, t, u, v) &&
+      const float* tp = &b.tris[(uint64_t)prim * 12];
+      if ((wt ? tri_test_wt(tp, r, wr, t, u, v) : tri_test(tp, r, t, u, v)) &&
           accept(t, (int32_t)prim, r.tmin, best_t, best_prim)) {
         best_t = t; best_prim = (int32_t)prim; bu = u; bv = v;
         if (any) break;
@@ -897,9 +953,12 @@ ORC_API void orc_brute(const float* tris, uint64_t n, const float* rays, uint64_
     std::memcpy(&r, rays + (uint64_t)i * 8, 32);
     float best_t = r.tmax, bu = 0, bv = 0;
     int32_t best_prim = -1;
+    const bool wt = (flags & TRACE_WATERTIGHT) != 0;
+    WtRay wr = {0, 1, 2, 0, 0, 0};
+    if (wt) wr = wt_setup(r);
     for (uint64_t p = 0; p < n; ++p) {
       float t, u, v;
-      if (tri_test(tris + p * 12, r, t, u, v) && accept(t, (int32_t)p, r.tmin, best_t, best_prim)) {
+      if ((wt ? tri_test_wt(tris + p * 12, r, wr, t, u, v) : tri_test(tris + p * 12, r, t, u, v)) && accept(t, (int32_t)p, r.tmin, best_t, best_prim)) {
         best_t = t; best_prim = (int32_t)p; bu = u; bv = v;
       }
     }
