@@ -308,6 +308,8 @@ int build_impl(rt_bvh* h, const float* tris_in, uint32_t flags, cudaStream_t s) 
   ws.chunk_words = sort_chunk_words(n, h->key_bits);
   RT_TRY(tmp.alloc((void**)&ws.chunk_hist, ws.chunk_words * 4));
   RT_TRY(tmp.alloc(&bkeys, 32));
+  float* centroids = nullptr;
+  RT_TRY(tmp.alloc((void**)&centroids, n * 12));
   RT_TRY(tmp.alloc(&flags_buf, (n > 1 ? n - 1 : 1) * 4));
   void* queue_buf = nullptr;
   RT_TRY(tmp.alloc(&queue_buf, refit_queue_bytes(n)));
@@ -322,13 +324,17 @@ int build_impl(rt_bvh* h, const float* tris_in, uint32_t flags, cudaStream_t s) 
   };
 
   RT_TRY(mark(0));
-  RT_TRY(launch_bounds(tris, n, (uint32_t*)bkeys, s));
+  RT_TRY(launch_bounds(tris, n, (uint32_t*)bkeys, centroids, s));
   RT_TRY(mark(1));
-  RT_TRY(launch_morton(tris, n, (const uint32_t*)bkeys, h->key_bits, keys, s));
+  int hist_ready = 0;
+  RT_CUDA(cudaMemsetAsync(ws.hist, 0, sort_hist_words(h->key_bits) * sizeof(uint32_t), s));
+  RT_TRY(launch_morton(centroids, n, (const uint32_t*)bkeys, h->key_bits, keys, ws.chunk_hist,
+                       ws.hist, &hist_ready, s));
   RT_TRY(mark(2));
   void* skeys = nullptr;
   uint32_t* svals = nullptr;
-  RT_TRY(launch_sort(keys, n, h->key_bits, ws, /*iota_payload=*/true, &skeys, &svals, s));
+  RT_TRY(launch_sort(keys, n, h->key_bits, ws, /*iota_payload=*/true, &skeys, &svals, s,
+                     hist_ready != 0));
   RT_TRY(mark(3));
   RT_TRY(mark(4));  // A4 is fused into the bottom-up pass: the topology stage is empty
   RT_TRY(launch_build_tree(tris, svals, skeys, h->key_bits, n, (uint32_t*)flags_buf, h->nodes,

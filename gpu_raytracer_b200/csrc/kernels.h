@@ -61,10 +61,28 @@ int launch_shade(const float4* tris, const float4* rays, const float4* hits,
 // ---- build (morton.cu, radix_sort.cu, karras.cu, refit.cu) -----------------
 // bounds_keys: 6 ordered-int keys, min.xyz then max.xyz; must be pre-set to
 // 0xFFFFFFFF x3, 0 x3 (launch_bounds does that itself).
-int launch_bounds(const float4* tris, uint64_t n, uint32_t* bounds_keys, cudaStream_t s);
-// keys: n u32 (30-bit) or n u64 (63-bit)
-int launch_morton(const float4* tris, uint64_t n, const uint32_t* bounds_keys, uint32_t key_bits,
-                  void* keys, cudaStream_t s);
+// Also writes the centroid of every triangle's own box (3 planes of n floats: x, y, z), so
+// the Morton pass reads 12 B per triangle instead of 48.
+int launch_bounds(const float4* tris, uint64_t n, uint32_t* bounds_keys, float* centroids,
+                  cudaStream_t s);
+
+// where chunk c of a sort pass starts and ends (host and device agree on this)
+struct ChunkGeom {
+  uint32_t n, chunk_size, chunks;
+  __host__ __device__ uint32_t begin(uint32_t c) const { return c * chunk_size; }
+  __host__ __device__ uint32_t end(uint32_t c) const {
+    const uint32_t e = (c + 1u) * chunk_size;
+    return (e < n && c + 1u < chunks) ? e : n;
+  }
+};
+ChunkGeom sort_geometry(uint64_t n, uint32_t key_bits);
+
+// keys: n u32 (30-bit) or n u64 (63-bit).  When chunk_hist is not null the kernel runs on
+// the sort's chunk geometry and also produces the first pass's per-chunk digit histograms
+// (chunk_hist [chunks][bins]) and bin totals (totals [bins], zeroed by the caller); returns
+// 1 in *fused when it did (default digit widths only), else 0 and the sort histograms itself.
+int launch_morton(const float* centroids, uint64_t n, const uint32_t* bounds_keys, uint32_t key_bits,
+                  void* keys, uint32_t* chunk_hist, uint32_t* totals, int* fused, cudaStream_t s);
 
 struct SortWorkspace {
   void* keys_alt = nullptr;     // 63-bit keys: n keys, ping-pong partner of the input
@@ -86,8 +104,11 @@ uint64_t sort_hist_words(uint32_t key_bits);
 uint64_t sort_chunk_words(uint64_t n, uint32_t key_bits);
 // Sorts (keys, iota) by key.  Result: *keys_out / *vals_out point at whichever
 // ping-pong buffer holds the sorted data.
+// first_hist_ready: ws.chunk_hist / ws.hist already hold the first pass's histograms
+// (launch_morton produced them); ws.hist must then have been zeroed before that.
 int launch_sort(void* keys, uint64_t n, uint32_t key_bits, const SortWorkspace& ws,
-                bool iota_payload, void** keys_out, uint32_t** vals_out, cudaStream_t s);
+                bool iota_payload, void** keys_out, uint32_t** vals_out, cudaStream_t s,
+                bool first_hist_ready = false);
 
 // A4 + A5 fused: topology, triangle reorder, boxes (refit.cu).  keys: the sorted Morton
 // codes; flags: n-1 u32, zeroed by the launcher.  Writes nodes (indexed by split

@@ -1,15 +1,18 @@
 // morton.cu — A1 scene bounds and A2 Morton encoding.
 //
-// A1  bounds_kernel: one streaming pass over the 3N vertices (48 B/triangle).
-//     Each thread keeps min/max as total-order integer keys (-0 < +0, exact and
+// A1  bounds_kernel: one streaming pass over the triangles (48 B read).  Each
+//     thread keeps min/max as total-order integer keys (-0 < +0, exact and
 //     order-free), warps reduce with redux.sync (__reduce_min/max_sync), blocks
-//     reduce through shared memory and finish with 6 atomics per block.
-// A2  morton_kernel: one thread per triangle: centroid of the triangle's own
-//     box, quantised against the scene box, bit-interleaved (x highest).
-//     Writes the key only; the payload of the first sort pass is the element
-//     position (iota), which needs no memory.
+//     reduce through shared memory and finish with 6 atomics per block.  The pass
+//     also stores the centroid of each triangle's own box (12 B written), because
+//     that is all the Morton pass needs: the triangles are read once, not twice.
+// A2  morton(_hist)_kernel: one thread per triangle: centroid, quantised against
+//     the scene box, bit-interleaved (x highest).  Writes the key only; the
+//     payload of the first sort pass is the element position (iota), which needs
+//     no memory.  On the default digit widths the kernel runs on the sort's chunk
+//     geometry and also counts the first digit (radix_sort.cu).
 //
-// Roofline: both kernels are HBM-bound: 48 B/tri read (+4 or 8 B/tri written).
+// Roofline: HBM-bound: 48 + 12 B/tri, then 12 + 4 (or 8) B/tri.
 #include "common.cuh"
 #include "kernels.h"
 
@@ -18,31 +21,36 @@ namespace {
 
 constexpr int kBoundsThreads = 256;
 
+// One thread per triangle and trip, two triangles (6 x LDG.128) in flight per thread.
+// The centroid of the triangle's own box goes to three planes of floats; the scene box is
+// the min/max over the triangle boxes, which is the min/max over all vertices.
 __global__ void __launch_bounds__(kBoundsThreads)
-bounds_kernel(const float4* __restrict__ verts, uint64_t n_verts, uint32_t* __restrict__ out) {
+bounds_kernel(const float4* __restrict__ tris, uint64_t n, uint32_t* __restrict__ out,
+              float* __restrict__ cx, float* __restrict__ cy, float* __restrict__ cz) {
   uint32_t mn[3] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu}, mx[3] = {0u, 0u, 0u};
   const uint64_t stride = (uint64_t)gridDim.x * kBoundsThreads;
-  uint64_t i = (uint64_t)blockIdx.x * kBoundsThreads + threadIdx.x;
-  // 4 independent 16-byte loads in flight per thread
-  for (; i + 3 * stride < n_verts; i += 4 * stride) {
-    float4 v[4];
-#pragma unroll
-    for (int k = 0; k < 4; ++k) v[k] = ld_stream(verts + i + k * stride);
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      uint32_t kx = ord_key(v[k].x), ky = ord_key(v[k].y), kz = ord_key(v[k].z);
-      mn[0] = min(mn[0], kx); mx[0] = max(mx[0], kx);
-      mn[1] = min(mn[1], ky); mx[1] = max(mx[1], ky);
-      mn[2] = min(mn[2], kz); mx[2] = max(mx[2], kz);
-    }
+  auto one = [&](uint64_t t, const float4 a, const float4 b, const float4 c) {
+    const float lx = omin(omin(a.x, b.x), c.x), hx = omax(omax(a.x, b.x), c.x);
+    const float ly = omin(omin(a.y, b.y), c.y), hy = omax(omax(a.y, b.y), c.y);
+    const float lz = omin(omin(a.z, b.z), c.z), hz = omax(omax(a.z, b.z), c.z);
+    cx[t] = 0.5f * (lx + hx);
+    cy[t] = 0.5f * (ly + hy);
+    cz[t] = 0.5f * (lz + hz);
+    mn[0] = min(mn[0], ord_key(lx)); mx[0] = max(mx[0], ord_key(hx));
+    mn[1] = min(mn[1], ord_key(ly)); mx[1] = max(mx[1], ord_key(hy));
+    mn[2] = min(mn[2], ord_key(lz)); mx[2] = max(mx[2], ord_key(hz));
+  };
+  uint64_t t = (uint64_t)blockIdx.x * kBoundsThreads + threadIdx.x;
+  for (; t + stride < n; t += 2 * stride) {
+    const uint64_t u = t + stride;
+    const float4 a0 = ld_stream(tris + 3 * t), b0 = ld_stream(tris + 3 * t + 1),
+                 c0 = ld_stream(tris + 3 * t + 2);
+    const float4 a1 = ld_stream(tris + 3 * u), b1 = ld_stream(tris + 3 * u + 1),
+                 c1 = ld_stream(tris + 3 * u + 2);
+    one(t, a0, b0, c0);
+    one(u, a1, b1, c1);
   }
-  for (; i < n_verts; i += stride) {
-    float4 v = ld_stream(verts + i);
-    uint32_t kx = ord_key(v.x), ky = ord_key(v.y), kz = ord_key(v.z);
-    mn[0] = min(mn[0], kx); mx[0] = max(mx[0], kx);
-    mn[1] = min(mn[1], ky); mx[1] = max(mx[1], ky);
-    mn[2] = min(mn[2], kz); mx[2] = max(mx[2], kz);
-  }
+  if (t < n) one(t, ld_stream(tris + 3 * t), ld_stream(tris + 3 * t + 1), ld_stream(tris + 3 * t + 2));
   __shared__ uint32_t s_mn[3], s_mx[3];
   if (threadIdx.x < 3) {
     s_mn[threadIdx.x] = 0xFFFFFFFFu;
@@ -97,38 +105,97 @@ __device__ __forceinline__ uint32_t quantize(float c, float smin, float scale, f
 
 constexpr int kMortonThreads = 256;
 
+struct Quant {
+  float smin[3], scale[3], qmax;
+};
 template <int KEY_BITS>
-__global__ void __launch_bounds__(kMortonThreads)
-morton_kernel(const float4* __restrict__ tris, uint64_t n, const uint32_t* __restrict__ bkeys,
-              void* __restrict__ keys_out) {
+__device__ __forceinline__ Quant load_quant(const uint32_t* __restrict__ bkeys) {
   constexpr float kCells = (KEY_BITS == 30) ? 1024.0f : 2097152.0f;
-
-  float smin[3], scale[3];
+  Quant q;
 #pragma unroll
   for (int k = 0; k < 3; ++k) {
-    smin[k] = ord_unkey(bkeys[k]);
-    float ext = ord_unkey(bkeys[3 + k]) - smin[k];
-    scale[k] = (ext > 0.0f) ? (kCells / ext) : 0.0f;
+    q.smin[k] = ord_unkey(bkeys[k]);
+    const float ext = ord_unkey(bkeys[3 + k]) - q.smin[k];
+    q.scale[k] = (ext > 0.0f) ? (kCells / ext) : 0.0f;
   }
-  const float qmax = kCells - 1.0f;
+  q.qmax = kCells - 1.0f;
+  return q;
+}
+template <int KEY_BITS>
+__device__ __forceinline__ uint64_t encode(const Quant& q, float cx, float cy, float cz) {
+  const uint32_t qx = quantize(cx, q.smin[0], q.scale[0], q.qmax);
+  const uint32_t qy = quantize(cy, q.smin[1], q.scale[1], q.qmax);
+  const uint32_t qz = quantize(cz, q.smin[2], q.scale[2], q.qmax);
+  if (KEY_BITS == 30) return (expand10(qx) << 2) | (expand10(qy) << 1) | expand10(qz);
+  return (expand21(qx) << 2) | (expand21(qy) << 1) | expand21(qz);
+}
 
+template <int KEY_BITS>
+__global__ void __launch_bounds__(kMortonThreads)
+morton_kernel(const float* __restrict__ cx, const float* __restrict__ cy,
+              const float* __restrict__ cz, uint64_t n, const uint32_t* __restrict__ bkeys,
+              void* __restrict__ keys_out) {
+  const Quant q = load_quant<KEY_BITS>(bkeys);
   for (uint64_t t = (uint64_t)blockIdx.x * kMortonThreads + threadIdx.x; t < n;
        t += (uint64_t)gridDim.x * kMortonThreads) {
-    float4 a = ld_stream(tris + 3 * t), b = ld_stream(tris + 3 * t + 1),
-           c = ld_stream(tris + 3 * t + 2);
-    float cx = 0.5f * (omin(omin(a.x, b.x), c.x) + omax(omax(a.x, b.x), c.x));
-    float cy = 0.5f * (omin(omin(a.y, b.y), c.y) + omax(omax(a.y, b.y), c.y));
-    float cz = 0.5f * (omin(omin(a.z, b.z), c.z) + omax(omax(a.z, b.z), c.z));
-    uint32_t qx = quantize(cx, smin[0], scale[0], qmax);
-    uint32_t qy = quantize(cy, smin[1], scale[1], qmax);
-    uint32_t qz = quantize(cz, smin[2], scale[2], qmax);
-    if (KEY_BITS == 30) {
-      uint32_t key = (expand10(qx) << 2) | (expand10(qy) << 1) | expand10(qz);
-      reinterpret_cast<uint32_t*>(keys_out)[t] = key;
-    } else {
-      uint64_t key = (expand21(qx) << 2) | (expand21(qy) << 1) | expand21(qz);
-      reinterpret_cast<uint64_t*>(keys_out)[t] = key;
+    const uint64_t key = encode<KEY_BITS>(q, cx[t], cy[t], cz[t]);
+    if (KEY_BITS == 30) reinterpret_cast<uint32_t*>(keys_out)[t] = (uint32_t)key;
+    else reinterpret_cast<uint64_t*>(keys_out)[t] = key;
+  }
+}
+
+// The same encode on the radix sort's chunk geometry (one CTA per chunk), which also counts
+// the lowest digit of the keys it produces: the sort's first chunk_hist_kernel, and its read
+// of every key, disappear.
+constexpr int kMortonHistThreads = 1024;
+template <int KEY_BITS, int BITS>
+__global__ void __launch_bounds__(kMortonHistThreads)
+morton_hist_kernel(const float* __restrict__ cx, const float* __restrict__ cy,
+                   const float* __restrict__ cz, ChunkGeom g, const uint32_t* __restrict__ bkeys,
+                   void* __restrict__ keys_out, uint32_t* __restrict__ chunk_hist,
+                   uint32_t* __restrict__ totals) {
+  constexpr int kBins = 1 << BITS;
+  __shared__ uint32_t sh[kBins];
+  for (int b = threadIdx.x; b < kBins; b += kMortonHistThreads) sh[b] = 0u;
+  __syncthreads();
+  const Quant q = load_quant<KEY_BITS>(bkeys);
+  const uint32_t c = blockIdx.x, end = g.end(c);
+  constexpr int kUnroll = 4;  // 12 independent loads in flight per thread
+  for (uint32_t base = g.begin(c); base < end; base += kUnroll * kMortonHistThreads) {  // CTA-uniform trips
+    float x[kUnroll], y[kUnroll], z[kUnroll];
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      const uint32_t t = base + u * kMortonHistThreads + threadIdx.x;
+      const bool valid = t < end;
+      x[u] = valid ? cx[t] : 0.0f;
+      y[u] = valid ? cy[t] : 0.0f;
+      z[u] = valid ? cz[t] : 0.0f;
     }
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      const uint32_t t = base + u * kMortonHistThreads + threadIdx.x;
+      const bool valid = t < end;
+      uint32_t d = 0;
+      if (valid) {
+        const uint64_t key = encode<KEY_BITS>(q, x[u], y[u], z[u]);
+        if (KEY_BITS == 30) reinterpret_cast<uint32_t*>(keys_out)[t] = (uint32_t)key;
+        else reinterpret_cast<uint64_t*>(keys_out)[t] = key;
+        d = (uint32_t)key & (kBins - 1);
+      }
+      // coherent meshes put one cell, hence one digit, in a whole warp: count it once
+      const uint32_t d0 = __shfl_sync(0xFFFFFFFFu, d, 0);
+      if (__all_sync(0xFFFFFFFFu, valid && d == d0)) {
+        if ((threadIdx.x & 31) == 0) atomicAdd(&sh[d], 32u);
+      } else if (valid) {
+        atomicAdd(&sh[d], 1u);
+      }
+    }
+  }
+  __syncthreads();
+  for (int b = threadIdx.x; b < kBins; b += kMortonHistThreads) {
+    const uint32_t v = sh[b];
+    chunk_hist[(size_t)c * kBins + b] = v;
+    if (v) atomicAdd(&totals[b], v);
   }
 }
 
@@ -142,26 +209,43 @@ inline unsigned persistent_grid(uint64_t items, int threads, int blocks_per_sm) 
 
 }  // namespace
 
-int launch_bounds(const float4* tris, uint64_t n, uint32_t* bounds_keys, cudaStream_t s) {
+int launch_bounds(const float4* tris, uint64_t n, uint32_t* bounds_keys, float* centroids,
+                  cudaStream_t s) {
   init_bounds_kernel<<<1, 32, 0, s>>>(bounds_keys);
   RT_LAUNCHED();
   if (n == 0) return 0;
-  uint64_t n_verts = 3 * n;
-  // 4 loads per thread per trip: size the grid for the unrolled loop
-  unsigned grid = persistent_grid((n_verts + 3) / 4, kBoundsThreads, 8);
-  bounds_kernel<<<grid, kBoundsThreads, 0, s>>>(tris, n_verts, bounds_keys);
+  // 2 triangles per thread per trip: size the grid for the unrolled loop
+  unsigned grid = persistent_grid((n + 1) / 2, kBoundsThreads, 8);
+  bounds_kernel<<<grid, kBoundsThreads, 0, s>>>(tris, n, bounds_keys, centroids, centroids + n,
+                                               centroids + 2 * n);
   RT_LAUNCHED();
   return 0;
 }
 
-int launch_morton(const float4* tris, uint64_t n, const uint32_t* bounds_keys, uint32_t key_bits,
-                  void* keys, cudaStream_t s) {
+int launch_morton(const float* centroids, uint64_t n, const uint32_t* bounds_keys, uint32_t key_bits,
+                  void* keys, uint32_t* chunk_hist, uint32_t* totals, int* fused, cudaStream_t s) {
+  if (fused) *fused = 0;
   if (n == 0) return 0;
+  const float *cx = centroids, *cy = centroids + n, *cz = centroids + 2 * n;
+  const SortPlan plan = sort_plan(key_bits);
+  const bool fuse = chunk_hist && totals && fused && plan.bits == (key_bits == 30 ? 10 : 9);
+  if (fuse) {
+    const ChunkGeom g = sort_geometry(n, key_bits);
+    if (key_bits == 30)
+      morton_hist_kernel<30, 10><<<g.chunks, kMortonHistThreads, 0, s>>>(cx, cy, cz, g, bounds_keys,
+                                                                        keys, chunk_hist, totals);
+    else
+      morton_hist_kernel<63, 9><<<g.chunks, kMortonHistThreads, 0, s>>>(cx, cy, cz, g, bounds_keys,
+                                                                       keys, chunk_hist, totals);
+    RT_LAUNCHED();
+    *fused = 1;
+    return 0;
+  }
   unsigned grid = persistent_grid(n, kMortonThreads, 8);
   if (key_bits == 30)
-    morton_kernel<30><<<grid, kMortonThreads, 0, s>>>(tris, n, bounds_keys, keys);
+    morton_kernel<30><<<grid, kMortonThreads, 0, s>>>(cx, cy, cz, n, bounds_keys, keys);
   else
-    morton_kernel<63><<<grid, kMortonThreads, 0, s>>>(tris, n, bounds_keys, keys);
+    morton_kernel<63><<<grid, kMortonThreads, 0, s>>>(cx, cy, cz, n, bounds_keys, keys);
   RT_LAUNCHED();
   return 0;
 }

@@ -45,16 +45,6 @@ namespace {
 
 constexpr uint32_t kFull = 0xFFFFFFFFu;
 
-// where chunk c of the pass starts and ends (host and device agree on this)
-struct ChunkGeom {
-  uint32_t n, chunk_size, chunks;
-  __host__ __device__ uint32_t begin(uint32_t c) const { return c * chunk_size; }
-  __host__ __device__ uint32_t end(uint32_t c) const {
-    const uint32_t e = (c + 1u) * chunk_size;
-    return (e < n && c + 1u < chunks) ? e : n;
-  }
-};
-
 // ---- per-chunk digit histogram ------------------------------------------------
 constexpr int kHistThreads = 1024;
 
@@ -433,7 +423,8 @@ int clamp_variant() {
   return (v < 0 || v >= kNumVariants) ? 0 : v;
 }
 
-ChunkGeom make_geom(uint64_t n, uint32_t key_bits) {
+}  // namespace
+ChunkGeom sort_geometry(uint64_t n, uint32_t key_bits) {
   const Shape& sh = kShapes[clamp_variant()];
   const uint64_t tile = (uint64_t)sh.threads * (key_bits == 30 ? sh.ipt32 : sh.ipt64);
   const uint64_t max_ctas = (uint64_t)num_sms() * sh.ctas_per_sm;
@@ -451,6 +442,8 @@ ChunkGeom make_geom(uint64_t n, uint32_t key_bits) {
   }
   return g;
 }
+namespace {
+ChunkGeom make_geom(uint64_t n, uint32_t key_bits) { return sort_geometry(n, key_bits); }
 
 struct PassIO {
   const void* keys_in = nullptr;   // KeyT keys (kInSplit / kInIota)
@@ -499,16 +492,18 @@ int launch_scatter(const PassIO& io, const uint32_t* offsets, const ChunkGeom& g
 
 template <typename KeyT, int BITS>
 int run_pass(int variant, const PassIO& io, uint32_t* chunk_hist, uint32_t* totals,
-             const ChunkGeom& g, int shift, cudaStream_t s) {
+             const ChunkGeom& g, int shift, cudaStream_t s, bool hist_ready) {
   constexpr bool k64 = sizeof(KeyT) == 8;
   constexpr int kBins = 1 << BITS;
-  if (io.in == kInRec)  // the key is the high word of the record
+  if (hist_ready) {
+    // the producer of the keys (morton_hist_kernel) already counted this digit
+  } else if (io.in == kInRec)  // the key is the high word of the record
     chunk_hist_kernel<uint64_t, BITS><<<g.chunks, kHistThreads, 0, s>>>(
         (const uint64_t*)io.recs_in, g, shift + 32, chunk_hist, totals);
   else
     chunk_hist_kernel<KeyT, BITS><<<g.chunks, kHistThreads, 0, s>>>((const KeyT*)io.keys_in, g,
                                                                    shift, chunk_hist, totals);
-  RT_LAUNCHED();
+  if (!hist_ready) RT_LAUNCHED();
   chunk_offsets_kernel<BITS><<<kBins / kOffWarps, kOffWarps * 32, 0, s>>>(chunk_hist, totals, g.chunks);
   RT_LAUNCHED();
   if (variant == 1)
@@ -518,12 +513,12 @@ int run_pass(int variant, const PassIO& io, uint32_t* chunk_hist, uint32_t* tota
 
 template <typename KeyT>
 int dispatch_pass(int bits, int variant, const PassIO& io, uint32_t* chunk_hist, uint32_t* totals,
-                  const ChunkGeom& g, int shift, cudaStream_t s) {
+                  const ChunkGeom& g, int shift, cudaStream_t s, bool hist_ready) {
   switch (bits) {
-    case 8: return run_pass<KeyT, 8>(variant, io, chunk_hist, totals, g, shift, s);
-    case 9: return run_pass<KeyT, 9>(variant, io, chunk_hist, totals, g, shift, s);
-    case 10: return run_pass<KeyT, 10>(variant, io, chunk_hist, totals, g, shift, s);
-    case 11: return run_pass<KeyT, 11>(variant, io, chunk_hist, totals, g, shift, s);
+    case 8: return run_pass<KeyT, 8>(variant, io, chunk_hist, totals, g, shift, s, hist_ready);
+    case 9: return run_pass<KeyT, 9>(variant, io, chunk_hist, totals, g, shift, s, hist_ready);
+    case 10: return run_pass<KeyT, 10>(variant, io, chunk_hist, totals, g, shift, s, hist_ready);
+    case 11: return run_pass<KeyT, 11>(variant, io, chunk_hist, totals, g, shift, s, hist_ready);
   }
   return fail(-2, "sort: unsupported digit width %d", bits);
 }
@@ -552,7 +547,8 @@ uint64_t sort_chunk_words(uint64_t n, uint32_t key_bits) {
 }
 
 int launch_sort(void* keys, uint64_t n, uint32_t key_bits, const SortWorkspace& ws,
-                bool iota_payload, void** keys_out, uint32_t** vals_out, cudaStream_t s) {
+                bool iota_payload, void** keys_out, uint32_t** vals_out, cudaStream_t s,
+                bool first_hist_ready) {
   *keys_out = keys;
   *vals_out = ws.vals;
   if (n > ((1ull << 30) - 1)) return fail(-5, "sort: n = %llu beyond 2^30-1", (unsigned long long)n);
@@ -563,8 +559,10 @@ int launch_sort(void* keys, uint64_t n, uint32_t key_bits, const SortWorkspace& 
   const ChunkGeom g = make_geom(n, key_bits);
   if (ws.chunk_words < (uint64_t)g.chunks * bins)
     return fail(-2, "sort: chunk workspace too small");
-  RT_CUDA(cudaMemsetAsync(ws.hist, 0, sort_hist_words(key_bits) * sizeof(uint32_t), s));
+  if (!first_hist_ready)
+    RT_CUDA(cudaMemsetAsync(ws.hist, 0, sort_hist_words(key_bits) * sizeof(uint32_t), s));
   for (int p = 0; p < plan.passes; ++p) {
+    const bool ready = first_hist_ready && p == 0;
     const bool fwd = (p & 1) == 0;
     uint32_t* totals = ws.hist + (size_t)p * bins;
     PassIO io;
@@ -588,7 +586,7 @@ int launch_sort(void* keys, uint64_t n, uint32_t key_bits, const SortWorkspace& 
         io.recs_out = (uint2*)(fwd ? ws.rec_a : ws.rec_b);
       }
       RT_TRY(dispatch_pass<uint32_t>(plan.bits, variant, io, ws.chunk_hist, totals, g,
-                                     plan.bits * p, s));
+                                     plan.bits * p, s, ready));
     } else {
       io.in = (iota_payload && p == 0) ? kInIota : kInSplit;
       io.keys_in = fwd ? keys : ws.keys_alt;
@@ -596,7 +594,7 @@ int launch_sort(void* keys, uint64_t n, uint32_t key_bits, const SortWorkspace& 
       io.vals_in = fwd ? ws.vals : ws.vals_alt;
       io.vals_out = fwd ? ws.vals_alt : ws.vals;
       RT_TRY(dispatch_pass<uint64_t>(plan.bits, variant, io, ws.chunk_hist, totals, g,
-                                     plan.bits * p, s));
+                                     plan.bits * p, s, ready));
     }
   }
   if (key_bits != 30 && (plan.passes & 1)) {  // odd pass count: result in the partner buffers
