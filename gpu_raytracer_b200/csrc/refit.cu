@@ -136,37 +136,49 @@ __device__ __forceinline__ void store_root(const Box& bx, int enc, BvhHeader* he
 }
 
 // ---- build: device-scope climb with on-the-fly topology -------------------------
+// One level costs two dependent L2 round trips: the arrival exchange, then (second
+// arriver only) the sibling's box together with the four keys that decide the next
+// parent.  The arrival word carries the first arriver's far end + 1, so the second one
+// knows the merged range, and can ask for those keys, before it has seen the box.
+__device__ __forceinline__ void fence_acq_rel_gpu() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
+
 template <typename KeyT>
 __device__ __forceinline__ void climb_build_global(Box bx, int enc, uint32_t L, uint32_t R,
                                                    const KeyT* __restrict__ keys, uint32_t n,
                                                    uint32_t* __restrict__ flags,
                                                    Node* __restrict__ nodes,
                                                    BvhHeader* __restrict__ header) {
+  // keys around both ends of [L, R]; out-of-range ends are never compared
+  KeyT kl0 = 0, kl1 = 0, kr0 = 0, kr1 = 0;
+  auto fetch = [&]() {
+    if (L != 0u) { kl0 = __ldg(keys + L - 1); kl1 = __ldg(keys + L); }
+    if (R != n - 1u) { kr0 = __ldg(keys + R); kr1 = __ldg(keys + R + 1); }
+  };
+  fetch();
   while (true) {
     if (L == 0u && R == n - 1u) {
       store_root(bx, enc, header);
       return;
     }
     bool left = (L == 0u);
-    if (!left && R != n - 1u) {
-      const uint32_t dr = delta_adj<KeyT>(__ldg(keys + R), __ldg(keys + R + 1), R);
-      const uint32_t dl = delta_adj<KeyT>(__ldg(keys + L - 1), __ldg(keys + L), L - 1);
-      left = dr > dl;
-    }
+    if (!left && R != n - 1u)
+      left = delta_adj<KeyT>(kr0, kr1, R) > delta_adj<KeyT>(kl0, kl1, L - 1);
     const uint32_t g = left ? R : L - 1u, slot = left ? 0u : 1u;
     float4* np = reinterpret_cast<float4*>(nodes + g);
     np[2 * slot] = make_float4(bx.lx, bx.ly, bx.lz, __int_as_float(enc));
     np[2 * slot + 1] = make_float4(bx.hx, bx.hy, bx.hz, __uint_as_float(left ? L : R));
-    __threadfence();
-    if (atomicAdd(flags + g, 1u) == 0u) return;
-    // acquire side: the loads below are issued only after the atomic's result is
-    // known (control dependency) and go to L2 (ld.cg), where the sibling's
-    // fenced stores already are
+    fence_acq_rel_gpu();
+    const uint32_t old = atomicExch(flags + g, (left ? L : R) + 1u);
+    if (old == 0u) return;  // first arriver stops
+    if (left) R = old - 1u; else L = old - 1u;
+    fetch();  // next level's keys travel with the sibling's box
+    // acquire side: the loads below are issued only after the exchange's result is
+    // known (control dependency) and go to L2 (ld.cg), where the sibling's fenced
+    // stores already are
     const float4 slo = ld_cg(np + 2 * (slot ^ 1u));
     const float4 shi = ld_cg(np + 2 * (slot ^ 1u) + 1);
     bx.lx = omin(bx.lx, slo.x); bx.ly = omin(bx.ly, slo.y); bx.lz = omin(bx.lz, slo.z);
     bx.hx = omax(bx.hx, shi.x); bx.hy = omax(bx.hy, shi.y); bx.hz = omax(bx.hz, shi.z);
-    if (left) R = __float_as_uint(shi.w); else L = __float_as_uint(shi.w);
     enc = (int)g;
   }
 }
