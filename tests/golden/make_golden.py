@@ -27,7 +27,10 @@ def build_fixture(name, tris, key_bits, rays, extra=None):
     b = O.OracleBvh(tris, key_bits)
     hits = b.trace(rays)
     occ = b.trace(rays, O.TRACE_ANY)
-    out = dict(key_bits=np.int32(key_bits), n=np.int64(b.n), bounds=b.bounds,
+    wt_hits = b.trace(rays, O.TRACE_WATERTIGHT)             # A7 option
+    wide_boxes, wide_desc = b.collapse4(2)                  # A5w, default leaf size
+    out = dict(wt_hits=wt_hits, wide_desc=wide_desc, wide_boxes_sha=digest(wide_boxes),
+               key_bits=np.int32(key_bits), n=np.int64(b.n), bounds=b.bounds,
                tris_sha=digest(tris), keys=b.keys, idx=b.idx, left=b.left, right=b.right,
                parent=b.parent, boxes_sha=digest(b.boxes), boxes_head=b.boxes[:64],
                rays_sha=digest(rays), hits=hits, any_prim=O.hit_prims(occ))

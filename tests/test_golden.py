@@ -49,6 +49,10 @@ def test_oracle_reproduces_golden(oracle, path):
     assert np.array_equal(digest(b.boxes), g["boxes_sha"])
     assert np.array_equal(bits(b.trace(rays)), bits(g["hits"]))
     assert np.array_equal(oracle.hit_prims(b.trace(rays, oracle.TRACE_ANY)), g["any_prim"])
+    assert np.array_equal(bits(b.trace(rays, oracle.TRACE_WATERTIGHT)), bits(g["wt_hits"]))
+    wide_boxes, wide_desc = b.collapse4(2)
+    assert np.array_equal(wide_desc, g["wide_desc"])
+    assert np.array_equal(digest(wide_boxes), g["wide_boxes_sha"])
 
 
 @pytest.mark.gpu
@@ -74,3 +78,14 @@ def test_gpu_reproduces_golden(rt, path):
         assert np.array_equal(bits(b.trace(rays).cpu().numpy()), bits(g["hits"]))
         occ = b.trace(rays, rt.RT_TRACE_ANY).cpu().numpy()
         assert np.array_equal(np.ascontiguousarray(occ[:, 3]).view(np.int32), g["any_prim"])
+        wt = b.trace(rays, rt.RT_TRACE_WATERTIGHT).cpu().numpy()
+        assert np.array_equal(bits(wt), bits(g["wt_hits"]))
+        # A5w: the collapsed tree, then the same hits through it
+        from test_wide import gpu_preorder
+        b.widen()
+        nodes, root = b.read_wide()
+        wide_boxes, wide_desc = gpu_preorder(nodes, root, b.n_tris)
+        assert np.array_equal(wide_desc, g["wide_desc"])
+        assert np.array_equal(digest(wide_boxes), g["wide_boxes_sha"])
+        assert np.array_equal(bits(b.trace(rays).cpu().numpy()), bits(g["hits"]))
+        assert np.array_equal(bits(b.trace(rays, rt.RT_TRACE_WATERTIGHT).cpu().numpy()), bits(g["wt_hits"]))
