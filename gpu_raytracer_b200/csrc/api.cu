@@ -477,8 +477,37 @@ struct Pipeline {
   unsigned long long* counters = nullptr;  // 2
   cudaEvent_t ev_in[2], ev_run[2], ev_out[2];
   bool ready = false;
+  // releases everything (on the device that owns it); also run when the host thread ends
+  void destroy() {
+    if (device < 0) return;
+    int prev = -1;
+    cudaGetDevice(&prev);
+    if (prev != device) cudaSetDevice(device);
+    for (int b = 0; b < 2; ++b) {
+      if (rays[b]) cudaFree(rays[b]);
+      if (hits[b]) cudaFree(hits[b]);
+      rays[b] = hits[b] = nullptr;
+      if (ready) {
+        cudaEventDestroy(ev_in[b]);
+        cudaEventDestroy(ev_run[b]);
+        cudaEventDestroy(ev_out[b]);
+      }
+    }
+    if (counters) cudaFree(counters);
+    counters = nullptr;
+    if (s_in) cudaStreamDestroy(s_in);
+    if (s_run) cudaStreamDestroy(s_run);
+    if (s_out) cudaStreamDestroy(s_out);
+    s_in = s_run = s_out = nullptr;
+    if (prev != device && prev >= 0) cudaSetDevice(prev);
+    cudaGetLastError();  // a context torn down at process exit is not an error here
+    ready = false;
+    device = -1;
+  }
+  ~Pipeline() { destroy(); }
   int init(int dev) {
     if (ready && device == dev) return 0;
+    destroy();  // the thread moved to another device: one pipeline per thread
     device = dev;
     RT_CUDA(cudaStreamCreateWithFlags(&s_in, cudaStreamNonBlocking));
     RT_CUDA(cudaStreamCreateWithFlags(&s_run, cudaStreamNonBlocking));
