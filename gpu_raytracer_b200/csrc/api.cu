@@ -10,6 +10,8 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
+#include <ctime>
 #include <mutex>
 #include <new>
 #include <vector>
@@ -115,6 +117,16 @@ void* mapped_alias(const void* p) {
   }
   if (a.type == cudaMemoryTypeHost && a.devicePointer != nullptr) return a.devicePointer;
   return nullptr;
+}
+
+// page-locked host memory (cudaHostAlloc / cudaHostRegister / torch pin_memory)
+bool is_pinned_host(const void* p) {
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return a.type == cudaMemoryTypeHost;
 }
 
 struct DeviceScope {
@@ -477,6 +489,16 @@ struct Pipeline {
   unsigned long long* counters = nullptr;  // 2
   cudaEvent_t ev_in[2], ev_run[2], ev_out[2];
   bool ready = false;
+  // streamed mode (trace_streamed): one device control block = watermark (u64), error
+  // (u32), pad, seg_done[kMaxSegs]; pinned host mirror = flags[kMaxSegs], marks[kMaxChunks]
+  static constexpr int kSegShift = 17, kUpShift = 18;          // smallest: 128K-ray segments, 256K-ray uploads
+  static constexpr uint64_t kMaxStream = 1ull << 26;           // rays per streamed super-batch
+  static constexpr uint32_t kMaxSegs = (uint32_t)(kMaxStream >> kSegShift);
+  static constexpr uint32_t kMaxChunks = (uint32_t)(kMaxStream >> kUpShift) + 8;  // + the tapered end
+  unsigned char* d_ctl = nullptr;
+  uint32_t* h_flags = nullptr;             // pinned, written by the kernel
+  unsigned long long* h_marks = nullptr;   // pinned, source of the watermark copies
+  static constexpr size_t kCtlBytes = 16 + (size_t)kMaxSegs * 4;
   // releases everything (on the device that owns it); also run when the host thread ends
   void destroy() {
     if (device < 0) return;
@@ -495,6 +517,12 @@ struct Pipeline {
     }
     if (counters) cudaFree(counters);
     counters = nullptr;
+    if (d_ctl) cudaFree(d_ctl);
+    if (h_flags) cudaFreeHost(h_flags);
+    if (h_marks) cudaFreeHost(h_marks);
+    d_ctl = nullptr;
+    h_flags = nullptr;
+    h_marks = nullptr;
     if (s_in) cudaStreamDestroy(s_in);
     if (s_run) cudaStreamDestroy(s_run);
     if (s_out) cudaStreamDestroy(s_out);
@@ -520,6 +548,9 @@ struct Pipeline {
       RT_CUDA(cudaEventCreateWithFlags(&ev_out[b], cudaEventDisableTiming));
     }
     RT_CUDA(cudaMalloc((void**)&counters, 2 * sizeof(unsigned long long)));
+    RT_CUDA(cudaMalloc((void**)&d_ctl, kCtlBytes));
+    RT_CUDA(cudaHostAlloc((void**)&h_flags, (size_t)kMaxSegs * 4, cudaHostAllocMapped));
+    RT_CUDA(cudaHostAlloc((void**)&h_marks, (size_t)kMaxChunks * 8, cudaHostAllocDefault));
     ready = true;
     return 0;
   }
@@ -579,6 +610,120 @@ int trace_staged(const rt_bvh* h, const float* rays, bool rays_dev, uint64_t n_r
   return 0;
 }
 
+// Pinned host rays and hits, BVH2 dynamic-fetch kernel: ONE launch per super-batch.  The
+// upload is queued in 256K-ray pieces, each followed by an 8-byte copy that advances the
+// device watermark; the kernel starts at once and follows the watermark; the host polls the
+// per-segment completion flags the kernel raises in pinned memory and queues each segment's
+// device-to-host copy as soon as it is complete.  Against one launch per staged chunk this
+// pays the tail of slow rays once, and the copies in both directions overlap the traversal
+// at 128K/256K-ray granularity (profiles/r01h_e2e_streamed.md).
+// The watermark's advance, ordered after the copy before it on s_in: a stream memory
+// operation where the driver has one (a few us), else an 8-byte copy (15-25 us each).
+typedef int (*StreamWriteValue64)(cudaStream_t, unsigned long long, unsigned long long, unsigned int);
+static StreamWriteValue64 stream_write_value64() {
+  static StreamWriteValue64 fn = [] {
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (getenv("RT_NO_STREAM_MEMOP") ||
+        cudaGetDriverEntryPoint("cuStreamWriteValue64", &f, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      f = nullptr;
+    cudaGetLastError();
+    return (StreamWriteValue64)f;
+  }();
+  return fn;
+}
+static int advance_watermark(Pipeline& p, uint32_t c, uint64_t value) {
+  if (StreamWriteValue64 wv = stream_write_value64()) {
+    if (wv(p.s_in, (unsigned long long)(uintptr_t)p.d_ctl, value, 0u) == 0) return 0;
+  }
+  if (c >= Pipeline::kMaxChunks) return fail(RT_ERR_INVALID, "trace_rays: too many upload pieces");
+  p.h_marks[c] = value;
+  RT_CUDA(cudaMemcpyAsync(p.d_ctl, &p.h_marks[c], 8, cudaMemcpyHostToDevice, p.s_in));
+  return 0;
+}
+int trace_streamed(const rt_bvh* h, const float* rays, uint64_t n_rays, uint32_t flags, float* hits) {
+  Pipeline& p = t_pipe;
+  RT_TRY(p.init(h->device));
+  RT_CUDA(cudaStreamSynchronize(0));  // the legacy default stream may still be producing the inputs
+  cudaEvent_t ev_ctl = p.ev_in[0], ev_k = p.ev_run[0];
+  for (uint64_t done = 0; done < n_rays; done += Pipeline::kMaxStream) {
+    const uint64_t n = (n_rays - done < Pipeline::kMaxStream) ? n_rays - done : Pipeline::kMaxStream;
+    const float* src = rays + 8 * done;
+    float* dst = hits + 4 * done;
+    // upload pieces of about n/8 rays, 256K..1M: each copy costs the copy engine ~15 us of set-up
+    // (10% of an 8 MiB piece), but the kernel can only trace what has arrived
+    const int seg_shift = Pipeline::kSegShift;
+    int up_shift = Pipeline::kUpShift;
+    while (up_shift < 20 && (n >> (up_shift + 1)) >= 6) ++up_shift;
+    const uint32_t nseg = (uint32_t)((n + (1ull << seg_shift) - 1) >> seg_shift);
+    float4 *d_rays = nullptr, *d_hits = nullptr;
+    RT_CUDA(cudaMallocAsync((void**)&d_rays, n * 32, p.s_in));
+    RT_CUDA(cudaMallocAsync((void**)&d_hits, n * 16, p.s_in));
+    RT_CUDA(cudaMemsetAsync(p.d_ctl, 0, 16 + (size_t)nseg * 4, p.s_in));
+    memset(p.h_flags, 0, (size_t)nseg * 4);
+    RT_CUDA(cudaEventRecord(ev_ctl, p.s_in));
+    RT_CUDA(cudaStreamWaitEvent(p.s_run, ev_ctl, 0));
+    RT_CUDA(cudaStreamWaitEvent(p.s_out, ev_ctl, 0));
+    // upload pieces, each followed by the watermark's advance.  The last piece is cut small:
+    // what is traced after the upload's end is the last piece, spread over all warps
+    {
+      const uint64_t piece = 1ull << up_shift, tail_piece = 1ull << 16;
+      uint32_t c = 0;
+      for (uint64_t first = 0; first < n; ++c) {
+        const uint64_t left = n - first;
+        const uint64_t cnt = left > piece ? piece : (left > tail_piece ? (left > 2 * tail_piece ? left / 2 : tail_piece) : left);
+        RT_CUDA(cudaMemcpyAsync(d_rays + 2 * first, src + 8 * first, cnt * 32, cudaMemcpyHostToDevice, p.s_in));
+        first += cnt;
+        RT_TRY(advance_watermark(p, c, first));
+      }
+    }
+    TracePipe pipe;
+    pipe.watermark = reinterpret_cast<const unsigned long long*>(p.d_ctl);
+    pipe.error = reinterpret_cast<uint32_t*>(p.d_ctl + 8);
+    pipe.seg_done = reinterpret_cast<uint32_t*>(p.d_ctl + 16);
+    RT_CUDA(cudaHostGetDevicePointer((void**)&pipe.host_flags, p.h_flags, 0));
+    pipe.seg_shift = seg_shift;
+    int rc = launch_trace(h->nodes, h->stris, h->n, h->root, d_rays, n, flags, d_hits, p.counters,
+                          p.s_run, nullptr, &pipe);
+    if (rc == 0 && cudaEventRecord(ev_k, p.s_run) != cudaSuccess) rc = RT_ERR_CUDA;
+    // hits flow back segment by segment while the kernel runs
+    volatile uint32_t* flag = p.h_flags;
+    uint32_t next = 0;
+    auto copy_seg = [&](uint32_t sgm) -> cudaError_t {
+      const uint64_t first = (uint64_t)sgm << seg_shift;
+      const uint64_t cnt = (n - first < (1ull << seg_shift)) ? n - first : (1ull << seg_shift);
+      return cudaMemcpyAsync(dst + 4 * first, d_hits + first, cnt * 16, cudaMemcpyDeviceToHost, p.s_out);
+    };
+    bool kernel_done = false;
+    while (rc == 0 && next < nseg) {
+      if (flag[next]) {
+        if (copy_seg(next) != cudaSuccess) rc = RT_ERR_CUDA;
+        ++next;
+        continue;
+      }
+      if (kernel_done) break;  // flags were all written before the kernel ended: a gap means an error
+      const cudaError_t q = cudaEventQuery(ev_k);
+      if (q == cudaSuccess) kernel_done = true;  // look at the flags once more
+      else if (q != cudaErrorNotReady) rc = RT_ERR_CUDA;
+    }
+    cudaError_t e = cudaStreamSynchronize(p.s_run);
+    uint32_t err = 0;
+    if (e == cudaSuccess) e = cudaMemcpy(&err, p.d_ctl + 8, 4, cudaMemcpyDeviceToHost);
+    if (rc == 0 && e == cudaSuccess && err == 0)
+      for (; next < nseg; ++next)
+        if (copy_seg(next) != cudaSuccess) rc = RT_ERR_CUDA;
+    if (cudaStreamSynchronize(p.s_out) != cudaSuccess) rc = RT_ERR_CUDA;
+    cudaStreamSynchronize(p.s_in);
+    cudaFreeAsync(d_rays, p.s_in);
+    cudaFreeAsync(d_hits, p.s_in);
+    if (e != cudaSuccess) return fail_cuda(e, "trace_streamed", __FILE__, __LINE__);
+    if (err != 0) return fail(RT_ERR_CUDA, "trace_rays: the ray upload stalled; batch abandoned");
+    if (rc != 0) return fail(rc, "trace_rays: streamed pipeline failed (%s)", cudaGetErrorString(cudaGetLastError()));
+  }
+  return 0;
+}
+
 }  // namespace
 
 extern "C" int trace_rays_async(const rt_bvh* h, const float* rays, uint64_t n_rays, uint32_t flags,
@@ -620,6 +765,11 @@ extern "C" int trace_rays(const rt_bvh* h, const float* rays, uint64_t n_rays, u
   }
   // partial zero-copy: e.g. rays staged by the copy engine, hits stored by the
   // kernel straight into pinned host memory (posted PCIe writes need no staging)
+  // both buffers pinned on the host: one kernel launch follows the upload (see trace_streamed)
+  if (!rays_dev && !hits_dev && !rays_k && !hits_k && params().streamed != 0 &&
+      params().trace_variant != 0 && !(h->is_wide && params().trace_wide != 0) &&
+      n_rays >= (1ull << 19) && is_pinned_host(rays) && is_pinned_host(hits))
+    return trace_streamed(h, rays, n_rays, flags, hits);
   if (hits_k) return trace_staged(h, rays, rays_dev, n_rays, flags, (float*)hits_k, true);
   if (rays_k) return trace_staged(h, (const float*)rays_k, true, n_rays, flags, hits, hits_dev);
   return trace_staged(h, rays, rays_dev, n_rays, flags, hits, hits_dev);
@@ -1018,6 +1168,7 @@ extern "C" int rt_set_param(const char* name, int64_t value) {
   else if (!strcmp(name, "trace.blocks_per_sm")) p.trace_blocks_per_sm = (int)value;
   else if (!strcmp(name, "trace.variant")) p.trace_variant = (int)value;
   else if (!strcmp(name, "trace.wide")) p.trace_wide = (int)value;
+  else if (!strcmp(name, "trace.streamed")) p.streamed = (int)value;
   else if (!strcmp(name, "wide.leaf_max")) p.wide_leaf_max = (int)value;
   else if (!strcmp(name, "trace.zero_copy")) p.zero_copy = (int)value;
   else if (!strcmp(name, "trace.stage_chunk")) p.stage_chunk = (int)value;

@@ -172,10 +172,19 @@ int launch_trace_wide(const Node4* wide, const SortedTri* stris, uint64_t n_tris
                       unsigned long long* stats = nullptr);
 
 // ---- traversal (traverse.cu) -------------------------------------------------
+// Hand-shake of the streamed mode (host-resident batches): rays arrive while the kernel runs.
+struct TracePipe {
+  const unsigned long long* watermark;  // device: rays [0, *watermark) have been uploaded
+  uint32_t* seg_done;                   // device: retired rays per segment, zeroed
+  uint32_t* host_flags;                 // mapped pinned host memory: 1 = segment's hits complete
+  uint32_t* error;                      // device: set when the upload stalled for seconds
+  int seg_shift;                        // segment = 1 << seg_shift rays
+};
 int launch_trace(const Node* nodes, const SortedTri* stris, uint64_t n_tris, int root,
                  const float4* rays,
                  uint64_t n_rays, uint32_t flags, float4* hits, unsigned long long* ray_counter,
-                 cudaStream_t s, unsigned long long* stats = nullptr);
+                 cudaStream_t s, unsigned long long* stats = nullptr,
+                 const TracePipe* pipe = nullptr);
 
 // tuning knobs (rt_set_param)
 struct Params {
@@ -191,6 +200,7 @@ struct Params {
   // so the default stages both.
   int zero_copy = 0;
   int stage_chunk = 0;          // rays per staged chunk (0 = 1M)
+  int streamed = 1;             // 1 = pinned host batches go through the single-launch streamed mode
   int num_sms = 0;              // filled at first use
 };
 Params& params();

@@ -128,13 +128,41 @@ trace_kernel(const Node* __restrict__ nodes, const SortedTri* __restrict__ stris
 // acceptance) is the shared code above, so results are bit-identical to
 // variant 0 and to the oracle whatever the scheduling.
 // ---------------------------------------------------------------------------
-template <bool ANY, bool STATS, bool WT>
+//
+// PIPE (host-resident batches, api.cu trace_streamed): the same kernel runs while the
+// copy engine is still delivering the rays.  A warp that has claimed rays beyond the
+// upload watermark leaves its idle lanes idle and keeps traversing (or naps when it has
+// nothing else), and every retired ray is counted into its segment; the thread that
+// completes a segment raises that segment's flag in pinned host memory, which is the
+// host's cue to start the device-to-host copy of those hits.  One launch, one tail,
+// instead of one launch (and one ~0.25 ms tail of slowest rays) per staged chunk.
+__device__ __forceinline__ unsigned long long ld_volatile_u64(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+__device__ __forceinline__ float4 ld_cg_f4(const float4* p) {
+  float4 r;
+  asm volatile("ld.global.cg.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+               : "l"(p)
+               : "memory");
+  return r;
+}
+
+template <bool ANY, bool STATS, bool WT, bool PIPE>
 __global__ void __launch_bounds__(kTraceThreads)
 trace_kernel_dyn(const Node* __restrict__ nodes, const SortedTri* __restrict__ stris,
                  uint32_t n_tris, int root, const float4* __restrict__ rays,
                  unsigned long long n_rays, float4* __restrict__ hits,
                  unsigned long long* __restrict__ ray_counter,
-                 unsigned long long* __restrict__ stats, int chunk, int refill_min, int leaf_min) {
+                 unsigned long long* __restrict__ stats, int chunk, int refill_min, int leaf_min,
+                 TracePipe pipe) {
   const int lane = threadIdx.x & 31;
   const uint32_t lt_mask = (1u << lane) - 1u;
   const float inf = __int_as_float(0x7f800000);
@@ -150,12 +178,61 @@ trace_kernel_dyn(const Node* __restrict__ nodes, const SortedTri* __restrict__ s
   WtRay wr = {0, 1, 2, 0.0f, 0.0f, 0.0f};
   unsigned long long chunk_next = 0, chunk_end = 0;  // warp-uniform
   bool exhausted = false;                            // warp-uniform
+  unsigned long long uploaded = 0;                   // warp-uniform: last watermark seen (PIPE)
+  unsigned long long next_poll = 0;                  // warp-uniform
+  uint32_t polls = 0;
+  // retired rays of the two segments the warp's live chunks belong to (warp-uniform); they
+  // reach the segment counters once per chunk, not once per ray: 2M returning atomics on
+  // one hot word would queue at its L2 slice and double the kernel's run time
+  unsigned long long seg_a = ~0ull, seg_b = ~0ull;
+  uint32_t cnt_a = 0, cnt_b = 0;    // retired, not yet added to the segment's counter
+  uint32_t live_a = 0, live_b = 0;  // handed to lanes, not yet retired
+  auto flush_segment = [&](unsigned long long seg, uint32_t cnt) {  // warp-uniform call
+    if (cnt == 0u) return;
+    asm volatile("fence.acq_rel.gpu;" ::: "memory");  // every lane: its hit stores first
+    __syncwarp();
+    if (lane == 0) {
+      const unsigned long long seg_first = seg << pipe.seg_shift;
+      const unsigned long long seg_rays = min(1ull << pipe.seg_shift, n_rays - seg_first);
+      if (atomicAdd(pipe.seg_done + seg, cnt) + cnt == (uint32_t)seg_rays) {
+        __threadfence_system();
+        *reinterpret_cast<volatile uint32_t*>(pipe.host_flags + seg) = 1u;
+      }
+    }
+  };
+  constexpr unsigned long long kPollNs = 8000;
+  constexpr uint32_t kPollLimit = 600000;
 
   while (true) {
     // ---- per-lane refill from the warp's chunk --------------------------------
     const uint32_t idle = __ballot_sync(0xFFFFFFFFu, !has_ray);
     if (idle != 0u && !exhausted && (__popc(idle) >= refill_min || idle == 0xFFFFFFFFu)) {
-      if (chunk_next >= chunk_end) {
+      bool may_claim = chunk_next >= chunk_end;
+      if (PIPE && may_claim && uploaded < n_rays) {
+        // claim only rays that have arrived: a warp that holds a chunk of the future sits
+        // out the next arrival, and the rays that did arrive are left to fewer warps
+        const unsigned long long now = global_timer_ns();
+        may_claim = false;
+        if (now >= next_poll) {
+          unsigned long long claimed = 0;
+          if (lane == 0) {
+            uploaded = ld_volatile_u64(pipe.watermark);
+            claimed = ld_volatile_u64(ray_counter);
+          }
+          uploaded = __shfl_sync(0xFFFFFFFFu, uploaded, 0);
+          claimed = __shfl_sync(0xFFFFFFFFu, claimed, 0);
+          may_claim = uploaded >= n_rays || claimed + (unsigned long long)chunk <= uploaded;
+          if (!may_claim) {
+            next_poll = now + kPollNs;
+            if (++polls > kPollLimit) {  // ~5 s without progress: give up loudly
+              if (lane == 0) atomicExch(pipe.error, 1u);
+              exhausted = true;
+            }
+          }
+        }
+        if (!may_claim && idle == 0xFFFFFFFFu) __nanosleep(kPollNs / 2);  // nothing else to do
+      }
+      if (may_claim && !exhausted) {
         unsigned long long base = 0;
         if (lane == 0) base = atomicAdd(ray_counter, (unsigned long long)chunk);
         base = __shfl_sync(0xFFFFFFFFu, base, 0);
@@ -165,13 +242,42 @@ trace_kernel_dyn(const Node* __restrict__ nodes, const SortedTri* __restrict__ s
         } else {
           chunk_next = base;
           chunk_end = min(base + (unsigned long long)chunk, n_rays);
+          if (PIPE && (base >> pipe.seg_shift) != seg_b) {  // the oldest segment's count goes out
+            flush_segment(seg_a, cnt_a);
+            // rays of the old seg_a still in flight count themselves (retire path)
+            seg_a = seg_b;
+            cnt_a = cnt_b;
+            live_a = live_b;
+            seg_b = base >> pipe.seg_shift;
+            cnt_b = live_b = 0u;
+          }
         }
       }
-      const unsigned long long avail = chunk_end - chunk_next;
+      bool ready = true;
+      if (PIPE && !exhausted && uploaded < chunk_end) {  // have the claimed rays arrived?
+        // look at the watermark at most once per kPollNs and warp: thousands of warps
+        // re-reading one word every loop trip would swamp its L2 slice
+        ready = false;
+        const unsigned long long now = global_timer_ns();
+        if (now >= next_poll) {
+          if (lane == 0) uploaded = ld_volatile_u64(pipe.watermark);
+          uploaded = __shfl_sync(0xFFFFFFFFu, uploaded, 0);
+          ready = uploaded >= chunk_end;
+          next_poll = now + kPollNs;
+          if (!ready && ++polls > kPollLimit) {  // ~5 s without progress: give up loudly
+            if (lane == 0) atomicExch(pipe.error, 1u);
+            exhausted = true;
+            chunk_next = chunk_end = 0;
+          }
+        }
+        if (!ready && idle == 0xFFFFFFFFu) __nanosleep(kPollNs / 2);  // nothing else to do
+      }
+      const unsigned long long avail = ready ? chunk_end - chunk_next : 0ull;
       const uint32_t slot = __popc(idle & lt_mask);
       if (!has_ray && slot < avail) {
         my_ray = chunk_next + slot;
-        const float4 ro = ld_stream(rays + 2 * my_ray), rd = ld_stream(rays + 2 * my_ray + 1);
+        const float4 ro = PIPE ? ld_cg_f4(rays + 2 * my_ray) : ld_stream(rays + 2 * my_ray);
+        const float4 rd = PIPE ? ld_cg_f4(rays + 2 * my_ray + 1) : ld_stream(rays + 2 * my_ray + 1);
         r.ox = ro.x; r.oy = ro.y; r.oz = ro.z; r.tmin = ro.w;
         r.dx = rd.x; r.dy = rd.y; r.dz = rd.z;
         const float fmx = 3.402823466e+38f;
@@ -185,7 +291,9 @@ trace_kernel_dyn(const Node* __restrict__ nodes, const SortedTri* __restrict__ s
         node = (n_tris != 0) ? root : kEmpty;
       }
       const unsigned long long need = (unsigned long long)__popc(idle);
-      chunk_next += (need < avail) ? need : avail;
+      const unsigned long long took = (need < avail) ? need : avail;
+      chunk_next += took;
+      if (PIPE) live_b += (uint32_t)took;
     }
     if (__ballot_sync(0xFFFFFFFFu, has_ray) == 0u) {
       if (exhausted) break;
@@ -234,7 +342,8 @@ trace_kernel_dyn(const Node* __restrict__ nodes, const SortedTri* __restrict__ s
     }
 
     // ---- retire finished rays ------------------------------------------------------
-    if (has_ray && node == kEmpty) {
+    const bool retiring = has_ray && node == kEmpty;
+    if (retiring) {
       float4 h;
       if (r.best_prim < 0) h = make_float4(inf, 0.0f, 0.0f, __int_as_float(-1));
       else if (ANY) h = make_float4(0.0f, 0.0f, 0.0f, __int_as_float(0x7FFFFFFF));
@@ -242,6 +351,39 @@ trace_kernel_dyn(const Node* __restrict__ nodes, const SortedTri* __restrict__ s
       st_stream(hits + my_ray, h);
       has_ray = false;
     }
+    if (PIPE) {  // count this trip's retired rays into their segments
+      const bool retired = retiring;
+      const unsigned long long sgm = my_ray >> pipe.seg_shift;
+      const uint32_t in_b = __ballot_sync(0xFFFFFFFFu, retired && sgm == seg_b);
+      const uint32_t in_a = __ballot_sync(0xFFFFFFFFu, retired && sgm == seg_a && sgm != seg_b);
+      cnt_b += __popc(in_b);
+      live_b -= __popc(in_b);
+      cnt_a += __popc(in_a);
+      live_a -= __popc(in_a);
+      // a segment's count goes out as soon as the warp holds no more of its rays, so the
+      // host can start that segment's download while later segments are still traced
+      if (cnt_a != 0u && live_a == 0u) {
+        flush_segment(seg_a, cnt_a);
+        cnt_a = 0u;
+      }
+      if (cnt_b != 0u && live_b == 0u && chunk_next >= chunk_end) {
+        flush_segment(seg_b, cnt_b);
+        cnt_b = 0u;
+      }
+      if (retired && sgm != seg_a && sgm != seg_b) {  // a straggler of an older chunk: rare
+        asm volatile("fence.acq_rel.gpu;" ::: "memory");
+        const unsigned long long seg_first = sgm << pipe.seg_shift;
+        const unsigned long long seg_rays = min(1ull << pipe.seg_shift, n_rays - seg_first);
+        if (atomicAdd(pipe.seg_done + sgm, 1u) + 1u == (uint32_t)seg_rays) {
+          __threadfence_system();
+          *reinterpret_cast<volatile uint32_t*>(pipe.host_flags + sgm) = 1u;
+        }
+      }
+    }
+  }
+  if (PIPE) {
+    flush_segment(seg_a, cnt_a);
+    flush_segment(seg_b, cnt_b);
   }
   if (STATS) {
     n_nodes = __reduce_add_sync(0xFFFFFFFFu, n_nodes);
@@ -258,8 +400,10 @@ trace_kernel_dyn(const Node* __restrict__ nodes, const SortedTri* __restrict__ s
 int launch_trace(const Node* nodes, const SortedTri* stris, uint64_t n_tris, int root,
                  const float4* rays,
                  uint64_t n_rays, uint32_t flags, float4* hits, unsigned long long* ray_counter,
-                 cudaStream_t s, unsigned long long* stats) {
+                 cudaStream_t s, unsigned long long* stats, const TracePipe* pipe) {
   if (n_rays == 0) return 0;
+  if (pipe && (stats || params().trace_variant == 0))
+    return fail(-1, "launch_trace: the streamed mode needs the dynamic-fetch kernel without stats");
   RT_CUDA(cudaMemsetAsync(ray_counter, 0, sizeof(unsigned long long), s));
   int bps = params().trace_blocks_per_sm;
   if (bps <= 0) bps = 8;
@@ -275,9 +419,22 @@ int launch_trace(const Node* nodes, const SortedTri* stris, uint64_t n_tris, int
     if (p.trace_chunk <= 0 && n_rays < blocks * (kTraceThreads / 32) * (uint64_t)chunk * 2) chunk = 32;
     const int refill_min = p.trace_refill_min > 0 ? p.trace_refill_min : 16;
     const int leaf_min = p.trace_leaf_min > 0 ? p.trace_leaf_min : 8;
-#define RT_TRACE_DYN(A, S, W)                                                 \
-  trace_kernel_dyn<A, S, W><<<(unsigned)blocks, kTraceThreads, 0, s>>>(       \
-      nodes, stris, (uint32_t)n_tris, root, rays, n_rays, hits, ray_counter, stats, chunk, refill_min, leaf_min)
+    if (pipe) {
+      // 32-ray chunks: when a piece arrives every resident warp gets a share of it
+      if (p.trace_chunk <= 0) chunk = 32;
+#define RT_TRACE_PIPE(A, W)                                                          \
+  trace_kernel_dyn<A, false, W, true><<<(unsigned)blocks, kTraceThreads, 0, s>>>(    \
+      nodes, stris, (uint32_t)n_tris, root, rays, n_rays, hits, ray_counter, stats, chunk, refill_min, leaf_min, *pipe)
+      if (any) { if (wt) RT_TRACE_PIPE(true, true); else RT_TRACE_PIPE(true, false); }
+      else     { if (wt) RT_TRACE_PIPE(false, true); else RT_TRACE_PIPE(false, false); }
+#undef RT_TRACE_PIPE
+      RT_LAUNCHED();
+      return 0;
+    }
+    const TracePipe no_pipe = {nullptr, nullptr, nullptr, nullptr, 0};
+#define RT_TRACE_DYN(A, S, W)                                                        \
+  trace_kernel_dyn<A, S, W, false><<<(unsigned)blocks, kTraceThreads, 0, s>>>(       \
+      nodes, stris, (uint32_t)n_tris, root, rays, n_rays, hits, ray_counter, stats, chunk, refill_min, leaf_min, no_pipe)
     RT_DISPATCH3(RT_TRACE_DYN, any, st, wt);
 #undef RT_TRACE_DYN
     RT_LAUNCHED();

@@ -309,6 +309,20 @@ def test_config2_million_triangles(rt, oracle):
             assert np.array_equal(bits(out.numpy()), bits(want)), zc
         mixed = gb.trace(pinned)            # pinned rays -> hits of the same kind (host tensor)
         assert np.array_equal(bits(mixed.numpy()), bits(want))
+        # streamed (one launch follows the upload's watermark) against staged chunks, on a ray
+        # count that ends inside a segment, for every kernel flavour
+        m = 1300017
+        for flags in (0, rt.RT_TRACE_ANY, rt.RT_TRACE_WATERTIGHT, rt.RT_TRACE_ANY | rt.RT_TRACE_WATERTIGHT):
+            ref = gb.trace(g_rays[:m], flags).cpu().numpy()
+            for streamed in (1, 0):
+                rt.set_param("trace.streamed", streamed)
+                try:
+                    out.zero_()
+                    gb.trace(pinned[:m], flags, out=out[:m])
+                finally:
+                    rt.set_param("trace.streamed", 1)
+                assert np.array_equal(bits(out[:m].numpy()), bits(ref)), (flags, streamed)
+                assert not out[m:].any(), "wrote past the batch"
 
 
 def test_refit_after_moving_vertices(rt, oracle):
