@@ -322,6 +322,8 @@ def run_ours(args):
     trace_bytes = count * 48 + 64 * nodes + 48 * tests
 
     # ---- e2e: host (pinned) buffers through the C ABI, copies inside the timing ----
+    if args.staged:
+        g.set_param("trace.streamed", 0)
     h_tris = tris.cpu().pin_memory()
     h_rays = rays.cpu().pin_memory()
     h_hits = torch.empty((count, 4), dtype=torch.float32).pin_memory()
@@ -417,6 +419,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="soup1m", choices=["soup1m", "flake10m", "cornell"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--staged", action="store_true",
+                    help="e2e leg through staged chunks instead of the streamed single launch "
+                         "(for runs under a replaying profiler)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":
