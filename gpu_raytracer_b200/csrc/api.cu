@@ -642,6 +642,10 @@ static int advance_watermark(Pipeline& p, uint32_t c, uint64_t value) {
   RT_CUDA(cudaMemcpyAsync(p.d_ctl, &p.h_marks[c], 8, cudaMemcpyHostToDevice, p.s_in));
   return 0;
 }
+// trace_streamed's verdict when the kernel saw no upload progress for seconds (a profiler
+// that serialises or replays kernels against the copy stream does that): not an error, the
+// batch is traced again through the staged pipeline and the mode stays off for the process.
+constexpr int kStreamStalled = 1;
 int trace_streamed(const rt_bvh* h, const float* rays, uint64_t n_rays, uint32_t flags, float* hits) {
   Pipeline& p = t_pipe;
   RT_TRY(p.init(h->device));
@@ -718,7 +722,7 @@ int trace_streamed(const rt_bvh* h, const float* rays, uint64_t n_rays, uint32_t
     cudaFreeAsync(d_rays, p.s_in);
     cudaFreeAsync(d_hits, p.s_in);
     if (e != cudaSuccess) return fail_cuda(e, "trace_streamed", __FILE__, __LINE__);
-    if (err != 0) return fail(RT_ERR_CUDA, "trace_rays: the ray upload stalled; batch abandoned");
+    if (err != 0) return kStreamStalled;  // the caller runs the batch again through staged chunks
     if (rc != 0) return fail(rc, "trace_rays: streamed pipeline failed (%s)", cudaGetErrorString(cudaGetLastError()));
   }
   return 0;
@@ -769,7 +773,11 @@ extern "C" int trace_rays(const rt_bvh* h, const float* rays, uint64_t n_rays, u
   if (!rays_dev && !hits_dev && !rays_k && !hits_k && params().streamed != 0 &&
       params().trace_variant != 0 && !(h->is_wide && params().trace_wide != 0) &&
       n_rays >= (1ull << 19) && is_pinned_host(rays) && is_pinned_host(hits))
-    return trace_streamed(h, rays, n_rays, flags, hits);
+  {
+    const int rc = trace_streamed(h, rays, n_rays, flags, hits);
+    if (rc != kStreamStalled) return rc;
+    params().streamed = 0;
+  }
   if (hits_k) return trace_staged(h, rays, rays_dev, n_rays, flags, (float*)hits_k, true);
   if (rays_k) return trace_staged(h, (const float*)rays_k, true, n_rays, flags, hits, hits_dev);
   return trace_staged(h, rays, rays_dev, n_rays, flags, hits, hits_dev);

@@ -201,7 +201,7 @@ trace_kernel_dyn(const Node* __restrict__ nodes, const SortedTri* __restrict__ s
     }
   };
   constexpr unsigned long long kPollNs = 8000;
-  constexpr uint32_t kPollLimit = 600000;
+  constexpr uint32_t kPollLimit = 250000;  // x kPollNs = 2 s without progress
 
   while (true) {
     // ---- per-lane refill from the warp's chunk --------------------------------
@@ -215,16 +215,18 @@ trace_kernel_dyn(const Node* __restrict__ nodes, const SortedTri* __restrict__ s
         may_claim = false;
         if (now >= next_poll) {
           unsigned long long claimed = 0;
+          const unsigned long long before = uploaded;
           if (lane == 0) {
             uploaded = ld_volatile_u64(pipe.watermark);
             claimed = ld_volatile_u64(ray_counter);
           }
           uploaded = __shfl_sync(0xFFFFFFFFu, uploaded, 0);
           claimed = __shfl_sync(0xFFFFFFFFu, claimed, 0);
+          if (uploaded != before) polls = 0u;
           may_claim = uploaded >= n_rays || claimed + (unsigned long long)chunk <= uploaded;
           if (!may_claim) {
             next_poll = now + kPollNs;
-            if (++polls > kPollLimit) {  // ~5 s without progress: give up loudly
+            if (++polls > kPollLimit) {  // 2 s without progress: give up loudly
               if (lane == 0) atomicExch(pipe.error, 1u);
               exhausted = true;
             }
@@ -260,11 +262,13 @@ trace_kernel_dyn(const Node* __restrict__ nodes, const SortedTri* __restrict__ s
         ready = false;
         const unsigned long long now = global_timer_ns();
         if (now >= next_poll) {
+          const unsigned long long before = uploaded;
           if (lane == 0) uploaded = ld_volatile_u64(pipe.watermark);
           uploaded = __shfl_sync(0xFFFFFFFFu, uploaded, 0);
+          if (uploaded != before) polls = 0u;
           ready = uploaded >= chunk_end;
           next_poll = now + kPollNs;
-          if (!ready && ++polls > kPollLimit) {  // ~5 s without progress: give up loudly
+          if (!ready && ++polls > kPollLimit) {  // 2 s without progress: give up loudly
             if (lane == 0) atomicExch(pipe.error, 1u);
             exhausted = true;
             chunk_next = chunk_end = 0;
