@@ -325,6 +325,39 @@ def test_config2_million_triangles(rt, oracle):
                 assert not out[m:].any(), "wrote past the batch"
 
 
+def test_config3_ten_million_triangles(rt, oracle):
+    """Config 3 (BASELINE.json:9) at full size: the 9,979,112-triangle sphereflake.  Keys, sorted
+    order, topology and node boxes against the oracle's build; a sample of the 4K primary rays
+    and their AO rays against the oracle's traversal."""
+    d_tris = rt.gen_scene(rt.RT_SCENE_SPHEREFLAKE, 4, 13, 2)
+    tris = d_tris.cpu().numpy()
+    n = tris.shape[0]
+    assert n == 9979112
+    for key_bits in (30, 63):
+        ob = oracle.OracleBvh(tris, key_bits)
+        with rt.Bvh.build(d_tris, key_bits=key_bits, keep_keys=True) as gb:
+            keys, idx = gb.read_sorted()
+            assert np.array_equal(keys, ob.keys) and np.array_equal(idx, ob.idx), key_bits
+            left, right, parent = gb.read_topology()
+            assert np.array_equal(left, ob.left) and np.array_equal(right, ob.right), key_bits
+            assert np.array_equal(parent, ob.parent), key_bits
+            assert np.array_equal(bits(gb.read_boxes()), bits(ob.boxes)), key_bits
+            if key_bits != 30:
+                continue
+            cam = rt.camera.frame_box(gb.bounds, 3840, 2160)
+            g_rays = rt.gen_primary_rays(cam, 3840, 2160)
+            got = gb.trace(g_rays)
+            pick = torch.arange(0, g_rays.shape[0], 17, device=g_rays.device)  # 488K rays
+            want = ob.trace(g_rays[pick].cpu().numpy())
+            assert np.array_equal(bits(got[pick].cpu().numpy()), bits(want))
+            radius = 0.05 * float(np.linalg.norm(gb.bounds[3:] - gb.bounds[:3]))
+            ao = rt.gen_ao_rays(d_tris, g_rays[pick], got[pick], 4, 2, radius)
+            got_ao = gb.trace(ao, rt.RT_TRACE_ANY).cpu().numpy()
+            want_ao = ob.trace(ao.cpu().numpy(), oracle.TRACE_ANY)
+            assert np.array_equal(bits(got_ao), bits(want_ao))
+            assert 0.02 < (oracle.hit_prims(got_ao) >= 0).mean() < 0.98
+
+
 def test_refit_after_moving_vertices(rt, oracle):
     tris = oracle.gen_scene(oracle.SCENE_SOUP, 5000, 0, seed=3)
     moved = tris.copy()
