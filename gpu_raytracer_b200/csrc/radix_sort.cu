@@ -195,15 +195,21 @@ enum : int { kOutSplit = 0, kOutRec = 1 };
 __device__ __forceinline__ uint32_t warp_rank(volatile uint16_t* wh, volatile uint32_t* peer_tbl,
                                               uint32_t d, uint32_t lane, uint32_t lt_mask) {
   const uint32_t c = (uint32_t)wh[d] >> 5;
-  peer_tbl[lane] = 0u;
-  __syncwarp();
   wh[d] = (uint16_t)(((c + 1u) << 5) | lane);
   __syncwarp();
   const uint32_t winner = (uint32_t)wh[d] & 31u;  // one lane id per group of equal digits
+  // 32 random digits out of 1024 are all different in 3 rounds of 5: every lane is alone in
+  // its group, and the counter it wrote (count + 1, the tag bits are never counted) stands
+  if (__ballot_sync(kFull, winner != lane) == 0u) {
+    __syncwarp();
+    return c;
+  }
   uint32_t peers;
   if (__all_sync(kFull, winner == __shfl_sync(kFull, winner, 0))) {
     peers = kFull;
   } else {
+    peer_tbl[lane] = 0u;
+    __syncwarp();
     atomicOr(const_cast<uint32_t*>(peer_tbl) + winner, 1u << lane);
     __syncwarp();
     peers = peer_tbl[winner];
