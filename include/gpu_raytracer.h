@@ -114,7 +114,10 @@ enum {
 RT_API int build_bvh(const float* tris, uint64_t n_tris, const rt_build_opts* opts, rt_bvh** out);
 
 /* Traces n_rays rays.  rays: [host|device] n_rays x 8 floats; hits:
- * [host|device] n_rays x 4 floats.  Safe to call concurrently on one handle. */
+ * [host|device] n_rays x 4 floats.  Safe to call concurrently on one handle.
+ * Host buffers: page-locked (cudaHostAlloc / cudaHostRegister) rays AND hits of at least
+ * 512K rays take the streamed path (one kernel launch follows the upload, hits return per
+ * 128K-ray segment); anything else is staged in 1M-ray chunks.  Same bytes either way. */
 RT_API int trace_rays(const rt_bvh* h, const float* rays, uint64_t n_rays, uint32_t flags, float* hits);
 
 /* Frees every device allocation of the handle.  NULL is a no-op. */
@@ -223,7 +226,10 @@ RT_API int rt_shade(const float* tris, const float* rays, const float* hits, con
 RT_API int rt_device_count(void);
 /* number of CUDA kernels this library has launched in this process */
 RT_API uint64_t rt_kernel_launches(void);
-/* tuning knobs for experiments: name = "sort.variant", "trace.blocks_per_sm" … */
+/* tuning knobs for experiments (process-wide): "sort.variant", "sort.bits",
+ * "trace.variant", "trace.blocks_per_sm", "trace.chunk", "trace.refill_min", "trace.leaf_min",
+ * "trace.wide", "wide.leaf_max", "trace.streamed" (0 = always stage host batches),
+ * "trace.stage_chunk", "trace.zero_copy".  Returns RT_ERR_INVALID for an unknown name. */
 RT_API int rt_set_param(const char* name, int64_t value);
 /* sorts n (key,value) pairs already on the device with the build's radix sort;
  * used by tests and the sort micro-benchmark.  key_bits 30 -> u32 keys, 63 ->
