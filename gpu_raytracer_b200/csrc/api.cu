@@ -23,6 +23,7 @@
 namespace rt {
 
 std::atomic<uint64_t> g_kernel_launches{0};
+int g_pdl = 1;
 
 namespace {
 thread_local char t_error[512] = "";
@@ -335,11 +336,14 @@ int build_impl(rt_bvh* h, const float* tris_in, uint32_t flags, cudaStream_t s) 
     return 0;
   };
 
+  // every memset first: from here on the stream holds kernels only, launched as
+  // programmatic dependents of each other (common.cuh pdl_enter)
+  RT_CUDA(cudaMemsetAsync(ws.hist, 0, sort_hist_words(h->key_bits) * sizeof(uint32_t), s));
+  RT_TRY(prepare_build_tree(n, (uint32_t*)flags_buf, queue_buf, s));
   RT_TRY(mark(0));
   RT_TRY(launch_bounds(tris, n, (uint32_t*)bkeys, centroids, s));
   RT_TRY(mark(1));
   int hist_ready = 0;
-  RT_CUDA(cudaMemsetAsync(ws.hist, 0, sort_hist_words(h->key_bits) * sizeof(uint32_t), s));
   RT_TRY(launch_morton(centroids, n, (const uint32_t*)bkeys, h->key_bits, keys, ws.chunk_hist,
                        ws.hist, &hist_ready, s));
   RT_TRY(mark(2));
@@ -1183,6 +1187,8 @@ extern "C" int rt_set_param(const char* name, int64_t value) {
   else if (!strcmp(name, "trace.chunk")) p.trace_chunk = (int)value;
   else if (!strcmp(name, "trace.refill_min")) p.trace_refill_min = (int)value;
   else if (!strcmp(name, "trace.leaf_min")) p.trace_leaf_min = (int)value;
+  else if (!strcmp(name, "trace.sh_stack")) p.trace_sh_stack = (int)value;
+  else if (!strcmp(name, "build.pdl")) g_pdl = value != 0;
   else return fail(RT_ERR_INVALID, "rt_set_param: unknown parameter '%s'", name);
   return RT_OK;
 }

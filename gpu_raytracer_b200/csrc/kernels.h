@@ -120,6 +120,8 @@ int launch_build_tree(const float4* tris, const uint32_t* sorted_idx, const void
 // launch_export_topology only, so the handle derives them on first use
 int launch_derive_parents(const Node* nodes, uint64_t n, int root, uint32_t* parent,
                           cudaStream_t s);
+// must precede launch_build_tree on the same stream (zeroes flags and the queue head)
+int prepare_build_tree(uint64_t n, uint32_t* flags, void* queue_buf, cudaStream_t s);
 // bytes of the continuation queue launch_build_tree / launch_refit_update need (queue_buf)
 size_t refit_queue_bytes(uint64_t n);
 // refit with moved vertices: the primitive index comes from stris[j].v0p.w
@@ -193,6 +195,7 @@ struct Params {
   int trace_blocks_per_sm = 0;  // 0 = kernel default
   int trace_variant = 1;        // 0 = plain while-while, 1 = dynamic fetch + voted leaf loop
   int trace_chunk = 0, trace_refill_min = 0, trace_leaf_min = 0;  // 0 = defaults
+  int trace_sh_stack = 0;       // stack levels kept in shared memory (0, 8, 16, 24)
   int trace_wide = 1;           // 1 = use the BVH4 of handles built with RT_BUILD_WIDE4
   int wide_leaf_max = kWideLeafDefault;  // triangles per BVH4 leaf (1..4), read when collapsing
   // bit 0: kernels read pinned host rays in place, bit 1: store hits to pinned host in

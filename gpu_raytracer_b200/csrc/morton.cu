@@ -27,6 +27,7 @@ constexpr int kBoundsThreads = 256;
 __global__ void __launch_bounds__(kBoundsThreads)
 bounds_kernel(const float4* __restrict__ tris, uint64_t n, uint32_t* __restrict__ out,
               float* __restrict__ cx, float* __restrict__ cy, float* __restrict__ cz) {
+  pdl_enter();
   uint32_t mn[3] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu}, mx[3] = {0u, 0u, 0u};
   const uint64_t stride = (uint64_t)gridDim.x * kBoundsThreads;
   auto one = [&](uint64_t t, const float4 a, const float4 b, const float4 c) {
@@ -74,6 +75,7 @@ bounds_kernel(const float4* __restrict__ tris, uint64_t n, uint32_t* __restrict_
 }
 
 __global__ void init_bounds_kernel(uint32_t* out) {
+  pdl_enter();
   if (threadIdx.x < 3) out[threadIdx.x] = 0xFFFFFFFFu;
   else if (threadIdx.x < 6) out[threadIdx.x] = 0u;
 }
@@ -135,6 +137,7 @@ __global__ void __launch_bounds__(kMortonThreads)
 morton_kernel(const float* __restrict__ cx, const float* __restrict__ cy,
               const float* __restrict__ cz, uint64_t n, const uint32_t* __restrict__ bkeys,
               void* __restrict__ keys_out) {
+  pdl_enter();
   const Quant q = load_quant<KEY_BITS>(bkeys);
   for (uint64_t t = (uint64_t)blockIdx.x * kMortonThreads + threadIdx.x; t < n;
        t += (uint64_t)gridDim.x * kMortonThreads) {
@@ -154,6 +157,7 @@ morton_hist_kernel(const float* __restrict__ cx, const float* __restrict__ cy,
                    const float* __restrict__ cz, ChunkGeom g, const uint32_t* __restrict__ bkeys,
                    void* __restrict__ keys_out, uint32_t* __restrict__ chunk_hist,
                    uint32_t* __restrict__ totals) {
+  pdl_enter();
   constexpr int kBins = 1 << BITS;
   __shared__ uint32_t sh[kBins];
   for (int b = threadIdx.x; b < kBins; b += kMortonHistThreads) sh[b] = 0u;
@@ -211,13 +215,13 @@ inline unsigned persistent_grid(uint64_t items, int threads, int blocks_per_sm) 
 
 int launch_bounds(const float4* tris, uint64_t n, uint32_t* bounds_keys, float* centroids,
                   cudaStream_t s) {
-  init_bounds_kernel<<<1, 32, 0, s>>>(bounds_keys);
+  RT_CUDA(launch_pdl(init_bounds_kernel, 1, 32, 0, s, bounds_keys));
   RT_LAUNCHED();
   if (n == 0) return 0;
   // 2 triangles per thread per trip: size the grid for the unrolled loop
   unsigned grid = persistent_grid((n + 1) / 2, kBoundsThreads, 8);
-  bounds_kernel<<<grid, kBoundsThreads, 0, s>>>(tris, n, bounds_keys, centroids, centroids + n,
-                                               centroids + 2 * n);
+  RT_CUDA(launch_pdl(bounds_kernel, grid, kBoundsThreads, 0, s, tris, n, bounds_keys, centroids,
+                     centroids + n, centroids + 2 * n));
   RT_LAUNCHED();
   return 0;
 }
@@ -232,20 +236,20 @@ int launch_morton(const float* centroids, uint64_t n, const uint32_t* bounds_key
   if (fuse) {
     const ChunkGeom g = sort_geometry(n, key_bits);
     if (key_bits == 30)
-      morton_hist_kernel<30, 10><<<g.chunks, kMortonHistThreads, 0, s>>>(cx, cy, cz, g, bounds_keys,
-                                                                        keys, chunk_hist, totals);
+      RT_CUDA(launch_pdl(morton_hist_kernel<30, 10>, g.chunks, kMortonHistThreads, 0, s, cx, cy, cz, g,
+                         bounds_keys, keys, chunk_hist, totals));
     else
-      morton_hist_kernel<63, 9><<<g.chunks, kMortonHistThreads, 0, s>>>(cx, cy, cz, g, bounds_keys,
-                                                                       keys, chunk_hist, totals);
+      RT_CUDA(launch_pdl(morton_hist_kernel<63, 9>, g.chunks, kMortonHistThreads, 0, s, cx, cy, cz, g,
+                         bounds_keys, keys, chunk_hist, totals));
     RT_LAUNCHED();
     *fused = 1;
     return 0;
   }
   unsigned grid = persistent_grid(n, kMortonThreads, 8);
   if (key_bits == 30)
-    morton_kernel<30><<<grid, kMortonThreads, 0, s>>>(cx, cy, cz, n, bounds_keys, keys);
+    RT_CUDA(launch_pdl(morton_kernel<30>, grid, kMortonThreads, 0, s, cx, cy, cz, n, bounds_keys, keys));
   else
-    morton_kernel<63><<<grid, kMortonThreads, 0, s>>>(cx, cy, cz, n, bounds_keys, keys);
+    RT_CUDA(launch_pdl(morton_kernel<63>, grid, kMortonThreads, 0, s, cx, cy, cz, n, bounds_keys, keys));
   RT_LAUNCHED();
   return 0;
 }

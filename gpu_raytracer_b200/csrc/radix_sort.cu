@@ -65,6 +65,7 @@ chunk_hist_kernel(const KeyT* __restrict__ keys, ChunkGeom g, int shift,
                   uint32_t* __restrict__ chunk_hist, uint32_t* __restrict__ totals) {
   constexpr int kBins = 1 << BITS;
   __shared__ uint32_t sh[kBins];
+  pdl_enter();
   for (int b = threadIdx.x; b < kBins; b += kHistThreads) sh[b] = 0u;
   __syncthreads();
   const uint32_t c = blockIdx.x, begin = g.begin(c), end = g.end(c);
@@ -103,6 +104,7 @@ __global__ void __launch_bounds__(kOffWarps * 32)
 chunk_offsets_kernel(uint32_t* __restrict__ chunk_hist, const uint32_t* __restrict__ totals,
                      uint32_t chunks) {
   constexpr int kBins = 1 << BITS;
+  pdl_enter();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int bin = blockIdx.x * kOffWarps + warp;
   const int rounds = (int)((chunks + 31) / 32);
@@ -234,6 +236,7 @@ scatter_kernel(const KeyT* __restrict__ keys_in, const uint32_t* __restrict__ va
   constexpr int kTile = C::kTile, kBins = C::kBins, kBPT = C::kBPT, kPPT = C::kPPT;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   Smem& sm = *reinterpret_cast<Smem*>(smem_raw);
+  pdl_enter();
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const uint32_t lt_mask = (1u << lane) - 1u;
@@ -468,9 +471,8 @@ int launch_scatter_io(const PassIO& io, const uint32_t* offsets, const ChunkGeom
   const size_t smem = sizeof(Smem);
   auto kern = scatter_kernel<KeyT, BITS, THREADS, IPT, MIN_BLOCKS, IN, OUT>;
   RT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  kern<<<g.chunks, THREADS, smem, s>>>((const KeyT*)io.keys_in, io.vals_in, io.recs_in,
-                                      (KeyT*)io.keys_out, io.vals_out, io.recs_out, offsets, g,
-                                      shift);
+  RT_CUDA(launch_pdl(kern, g.chunks, THREADS, smem, s, (const KeyT*)io.keys_in, io.vals_in,
+                     io.recs_in, (KeyT*)io.keys_out, io.vals_out, io.recs_out, offsets, g, shift));
   RT_LAUNCHED();
   return 0;
 }
@@ -504,13 +506,14 @@ int run_pass(int variant, const PassIO& io, uint32_t* chunk_hist, uint32_t* tota
   if (hist_ready) {
     // the producer of the keys (morton_hist_kernel) already counted this digit
   } else if (io.in == kInRec)  // the key is the high word of the record
-    chunk_hist_kernel<uint64_t, BITS><<<g.chunks, kHistThreads, 0, s>>>(
-        (const uint64_t*)io.recs_in, g, shift + 32, chunk_hist, totals);
+    RT_CUDA(launch_pdl(chunk_hist_kernel<uint64_t, BITS>, g.chunks, kHistThreads, 0, s,
+                       (const uint64_t*)io.recs_in, g, shift + 32, chunk_hist, totals));
   else
-    chunk_hist_kernel<KeyT, BITS><<<g.chunks, kHistThreads, 0, s>>>((const KeyT*)io.keys_in, g,
-                                                                   shift, chunk_hist, totals);
+    RT_CUDA(launch_pdl(chunk_hist_kernel<KeyT, BITS>, g.chunks, kHistThreads, 0, s,
+                       (const KeyT*)io.keys_in, g, shift, chunk_hist, totals));
   if (!hist_ready) RT_LAUNCHED();
-  chunk_offsets_kernel<BITS><<<kBins / kOffWarps, kOffWarps * 32, 0, s>>>(chunk_hist, totals, g.chunks);
+  RT_CUDA(launch_pdl(chunk_offsets_kernel<BITS>, kBins / kOffWarps, kOffWarps * 32, 0, s, chunk_hist,
+                     totals, g.chunks));
   RT_LAUNCHED();
   if (variant == 1)
     return launch_scatter<KeyT, BITS, 256, k64 ? 11 : 16, 4>(io, chunk_hist, g, shift, s);

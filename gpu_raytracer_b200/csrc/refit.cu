@@ -189,6 +189,7 @@ build_top_kernel(const Continuation* __restrict__ queue, const uint32_t* __restr
                  uint32_t capacity, const KeyT* __restrict__ keys, uint32_t n,
                  uint32_t* __restrict__ flags, Node* __restrict__ nodes,
                  BvhHeader* __restrict__ header) {
+  pdl_enter();
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   const uint32_t count = min(*queue_count, capacity);
   if (i >= count) return;
@@ -227,6 +228,7 @@ build_walk_kernel(const float4* __restrict__ tris, const uint32_t* __restrict__ 
                   uint32_t capacity) {
   extern __shared__ __align__(16) unsigned char refit_smem_raw[];
   RefitSmem& sm = *reinterpret_cast<RefitSmem*>(refit_smem_raw);
+  pdl_enter();
   const uint32_t tid = threadIdx.x;
   const uint32_t base = blockIdx.x * kRefitLeaves;
   const uint32_t j = base + tid;
@@ -506,17 +508,29 @@ static int build_tree_impl(const float4* tris, const uint32_t* sorted_idx, const
   uint32_t* queue_count;
   Continuation* queue;
   queue_layout(queue_buf, &queue_count, &queue);
-  if (n > 1) RT_CUDA(cudaMemsetAsync(flags, 0, (size_t)(n - 1) * sizeof(uint32_t), s));
-  RT_CUDA(cudaMemsetAsync(queue_count, 0, 32, s));
   const size_t smem = sizeof(RefitSmem);
   RT_CUDA(cudaFuncSetAttribute(build_walk_kernel<KeyT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                (int)smem));
-  build_walk_kernel<KeyT><<<blocks, kRefitLeaves, smem, s>>>(
-      tris, sorted_idx, keys, (uint32_t)n, flags, nodes, stris, header, queue, queue_count, capacity);
+  RT_CUDA(launch_pdl(build_walk_kernel<KeyT>, blocks, kRefitLeaves, smem, s, tris, sorted_idx, keys,
+                     (uint32_t)n, flags, nodes, stris, header, queue, queue_count, capacity));
   RT_LAUNCHED();
-  build_top_kernel<KeyT><<<(capacity + 255) / 256, 256, 0, s>>>(
-      queue, queue_count, capacity, keys, (uint32_t)n, flags, nodes, header);
+  RT_CUDA(launch_pdl(build_top_kernel<KeyT>, (capacity + 255) / 256, 256, 0, s,
+                     (const Continuation*)queue, (const uint32_t*)queue_count, capacity, keys,
+                     (uint32_t)n, flags, nodes, header));
   RT_LAUNCHED();
+  return 0;
+}
+
+// Zeroes the meeting counters and the queue head.  A separate call so that build_bvh can
+// issue it before the first kernel: the kernels of the build then follow each other with
+// nothing in between, which is what programmatic dependent launch needs (common.cuh).
+int prepare_build_tree(uint64_t n, uint32_t* flags, void* queue_buf, cudaStream_t s) {
+  if (n == 0) return 0;
+  uint32_t* queue_count;
+  Continuation* queue;
+  queue_layout(queue_buf, &queue_count, &queue);
+  if (n > 1) RT_CUDA(cudaMemsetAsync(flags, 0, (size_t)(n - 1) * sizeof(uint32_t), s));
+  RT_CUDA(cudaMemsetAsync(queue_count, 0, 32, s));
   return 0;
 }
 

@@ -155,7 +155,7 @@ __device__ __forceinline__ float4 ld_cg_f4(const float4* p) {
   return r;
 }
 
-template <bool ANY, bool STATS, bool WT, bool PIPE>
+template <bool ANY, bool STATS, bool WT, bool PIPE, int SHS>
 __global__ void __launch_bounds__(kTraceThreads)
 trace_kernel_dyn(const Node* __restrict__ nodes, const SortedTri* __restrict__ stris,
                  uint32_t n_tris, int root, const float4* __restrict__ rays,
@@ -168,8 +168,20 @@ trace_kernel_dyn(const Node* __restrict__ nodes, const SortedTri* __restrict__ s
   const float inf = __int_as_float(0x7f800000);
   uint32_t n_nodes = 0, n_tests = 0;
 
-  int stack[kStack];
+  // the first SHS stack levels live in shared memory ([level][thread]: bank = lane, one
+  // wavefront whatever the lanes' depths), the rest in local memory
+  __shared__ int sh_stack[SHS > 0 ? SHS : 1][kTraceThreads];
+  int stack[kStack - SHS];
   int sp = 0;
+  auto push = [&](int v) {
+    if (SHS > 0 && sp < SHS) sh_stack[sp][threadIdx.x] = v;
+    else stack[sp - SHS] = v;
+    ++sp;
+  };
+  auto pop = [&]() -> int {
+    --sp;
+    return (SHS > 0 && sp < SHS) ? sh_stack[sp][threadIdx.x] : stack[sp - SHS];
+  };
   int node = kEmpty;
   bool has_ray = false;
   unsigned long long my_ray = 0;
@@ -321,13 +333,13 @@ trace_kernel_dyn(const Node* __restrict__ nodes, const SortedTri* __restrict__ s
         if (h0 && h1) {
           const bool swap = tn1 < tn0;
           node = swap ? c1 : c0;
-          stack[sp++] = swap ? c0 : c1;
+          push(swap ? c0 : c1);
         } else if (h0) {
           node = c0;
         } else if (h1) {
           node = c1;
         } else {
-          node = (sp > 0) ? stack[--sp] : kEmpty;
+          node = (sp > 0) ? pop() : kEmpty;
         }
       }
     }
@@ -341,7 +353,7 @@ trace_kernel_dyn(const Node* __restrict__ nodes, const SortedTri* __restrict__ s
         node = kEmpty;
         sp = 0;
       } else {
-        node = (sp > 0) ? stack[--sp] : kEmpty;
+        node = (sp > 0) ? pop() : kEmpty;
       }
     }
 
@@ -427,7 +439,7 @@ int launch_trace(const Node* nodes, const SortedTri* stris, uint64_t n_tris, int
       // 32-ray chunks: when a piece arrives every resident warp gets a share of it
       if (p.trace_chunk <= 0) chunk = 32;
 #define RT_TRACE_PIPE(A, W)                                                          \
-  trace_kernel_dyn<A, false, W, true><<<(unsigned)blocks, kTraceThreads, 0, s>>>(    \
+  trace_kernel_dyn<A, false, W, true, 0><<<(unsigned)blocks, kTraceThreads, 0, s>>>( \
       nodes, stris, (uint32_t)n_tris, root, rays, n_rays, hits, ray_counter, stats, chunk, refill_min, leaf_min, *pipe)
       if (any) { if (wt) RT_TRACE_PIPE(true, true); else RT_TRACE_PIPE(true, false); }
       else     { if (wt) RT_TRACE_PIPE(false, true); else RT_TRACE_PIPE(false, false); }
@@ -436,11 +448,19 @@ int launch_trace(const Node* nodes, const SortedTri* stris, uint64_t n_tris, int
       return 0;
     }
     const TracePipe no_pipe = {nullptr, nullptr, nullptr, nullptr, 0};
-#define RT_TRACE_DYN(A, S, W)                                                        \
-  trace_kernel_dyn<A, S, W, false><<<(unsigned)blocks, kTraceThreads, 0, s>>>(       \
+#define RT_TRACE_DYN_K(A, S, W, K)                                                   \
+  trace_kernel_dyn<A, S, W, false, K><<<(unsigned)blocks, kTraceThreads, 0, s>>>(    \
       nodes, stris, (uint32_t)n_tris, root, rays, n_rays, hits, ray_counter, stats, chunk, refill_min, leaf_min, no_pipe)
-    RT_DISPATCH3(RT_TRACE_DYN, any, st, wt);
+#define RT_TRACE_DYN(A, S, W) RT_TRACE_DYN_K(A, S, W, 0)
+    const int shs = p.trace_sh_stack;
+    if (!st && !wt && shs > 0) {  // experiment: stack top in shared memory
+      if (any) { if (shs == 8) RT_TRACE_DYN_K(true, false, false, 8); else if (shs == 16) RT_TRACE_DYN_K(true, false, false, 16); else RT_TRACE_DYN_K(true, false, false, 24); }
+      else     { if (shs == 8) RT_TRACE_DYN_K(false, false, false, 8); else if (shs == 16) RT_TRACE_DYN_K(false, false, false, 16); else RT_TRACE_DYN_K(false, false, false, 24); }
+    } else {
+      RT_DISPATCH3(RT_TRACE_DYN, any, st, wt);
+    }
 #undef RT_TRACE_DYN
+#undef RT_TRACE_DYN_K
     RT_LAUNCHED();
     return 0;
   }
