@@ -1189,7 +1189,6 @@ extern "C" int rt_set_param(const char* name, int64_t value) {
   else if (!strcmp(name, "trace.leaf_min")) p.trace_leaf_min = (int)value;
   else if (!strcmp(name, "trace.sh_stack")) p.trace_sh_stack = (int)value;
   else if (!strcmp(name, "build.pdl")) g_pdl = value != 0;
-  else if (!strcmp(name, "build.tree_variant")) p.tree_variant = (int)value;
   else return fail(RT_ERR_INVALID, "rt_set_param: unknown parameter '%s'", name);
   return RT_OK;
 }

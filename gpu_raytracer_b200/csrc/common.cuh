@@ -101,6 +101,14 @@ __device__ __forceinline__ float ord_unkey(uint32_t k) {
 __device__ __forceinline__ float omin(float a, float b) { return ord_key(a) < ord_key(b) ? a : b; }
 __device__ __forceinline__ float omax(float a, float b) { return ord_key(a) > ord_key(b) ? a : b; }
 
+// 32 bytes in one store (STG.E.256, sm_100): a full sector per request where two
+// 16-byte stores are two partial-sector writes.  p must be 32-byte aligned.
+__device__ __forceinline__ void st_v8(void* p, const float4& a, const float4& b) {
+  asm volatile("st.global.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+               :: "l"(p), "f"(a.x), "f"(a.y), "f"(a.z), "f"(a.w), "f"(b.x), "f"(b.y), "f"(b.z), "f"(b.w)
+               : "memory");
+}
+
 __device__ __forceinline__ void normalize3(float& x, float& y, float& z) {
   float l2 = x * x + y * y + z * z;  // -fmad=false: ((x*x + y*y) + z*z)
   float l = sqrtf(l2);

@@ -191,7 +191,6 @@ int launch_trace(const Node* nodes, const SortedTri* stris, uint64_t n_tris, int
 // tuning knobs (rt_set_param)
 struct Params {
   int sort_variant = 0;
-  int tree_variant = 0;         // 0 = walk with meetings, 1 / 2 = self-computing nodes, 128 / 256 leaves
   int sort_bits = 0;            // 0 = default digit width (sort_plan)
   int trace_blocks_per_sm = 0;  // 0 = kernel default
   int trace_variant = 1;        // 0 = plain while-while, 1 = dynamic fetch + voted leaf loop

@@ -165,8 +165,8 @@ __device__ __forceinline__ void climb_build_global(Box bx, int enc, uint32_t L, 
       left = delta_adj<KeyT>(kr0, kr1, R) > delta_adj<KeyT>(kl0, kl1, L - 1);
     const uint32_t g = left ? R : L - 1u, slot = left ? 0u : 1u;
     float4* np = reinterpret_cast<float4*>(nodes + g);
-    np[2 * slot] = make_float4(bx.lx, bx.ly, bx.lz, __int_as_float(enc));
-    np[2 * slot + 1] = make_float4(bx.hx, bx.hy, bx.hz, __uint_as_float(left ? L : R));
+    st_v8(np + 2 * slot, make_float4(bx.lx, bx.ly, bx.lz, __int_as_float(enc)),
+          make_float4(bx.hx, bx.hy, bx.hz, __uint_as_float(left ? L : R)));
     fence_acq_rel_gpu();
     const uint32_t old = atomicExch(flags + g, (left ? L : R) + 1u);
     if (old == 0u) return;  // first arriver stops
@@ -250,10 +250,17 @@ build_walk_kernel(const float4* __restrict__ tris, const uint32_t* __restrict__ 
     const uint32_t prim = sorted_idx[j];
     const float4 a = __ldg(tris + 3 * (uint64_t)prim), b = __ldg(tris + 3 * (uint64_t)prim + 1),
                  c = __ldg(tris + 3 * (uint64_t)prim + 2);
+    // 48-byte records: the 32-byte aligned part goes out as one full sector
     float4* st = reinterpret_cast<float4*>(stris + j);
-    st[0] = make_float4(a.x, a.y, a.z, __uint_as_float(prim));
-    st[1] = make_float4(b.x, b.y, b.z, 0.0f);
-    st[2] = make_float4(c.x, c.y, c.z, 0.0f);
+    const float4 r0 = make_float4(a.x, a.y, a.z, __uint_as_float(prim));
+    const float4 r1 = make_float4(b.x, b.y, b.z, 0.0f), r2 = make_float4(c.x, c.y, c.z, 0.0f);
+    if ((j & 1u) == 0u) {
+      st_v8(st, r0, r1);
+      st[2] = r2;
+    } else {
+      st[0] = r0;
+      st_v8(st + 1, r1, r2);
+    }
     bx.lx = omin(omin(a.x, b.x), c.x); bx.ly = omin(omin(a.y, b.y), c.y); bx.lz = omin(omin(a.z, b.z), c.z);
     bx.hx = omax(omax(a.x, b.x), c.x); bx.hy = omax(omax(a.y, b.y), c.y); bx.hz = omax(omax(a.z, b.z), c.z);
   }
@@ -283,8 +290,7 @@ build_walk_kernel(const float4* __restrict__ tris, const uint32_t* __restrict__ 
     sm.dep_hi[slot][k] = my_hi;
     const uint32_t seen = arrive_or_cta(&sm.flag[k], 1u << slot);
     // the node half goes out after the meeting, so no fence ever waits for it
-    np[0] = my_lo;
-    np[1] = my_hi;
+    st_v8(np, my_lo, my_hi);
     if (seen == 0u) break;  // first arriver stops
     const float4 slo = lds_volatile_v4(&sm.dep_lo[slot ^ 1u][k]);
     const float4 shi = lds_volatile_v4(&sm.dep_hi[slot ^ 1u][k]);
@@ -306,199 +312,6 @@ build_walk_kernel(const float4* __restrict__ tris, const uint32_t* __restrict__ 
     park_or_climb<KeyT>(b2, __float_as_int(dlo.w), l2, r2, queue, queue_count, capacity, keys, n, flags,
                         nodes, header);
   }
-}
-
-// ---- build, variant without meetings: every node computes itself ----------------------
-// One CTA per G = 2^LOG2G consecutive sorted leaves.  The splits between them carry
-// d(u) = delta + 1 (0 where there is no split: before leaf 0, at and after leaf n-1);
-// u = 0 and u = G are the splits shared with the neighbouring groups.  Within a range of
-// splits the smallest delta is attained once (distinct augmented keys), so
-//   * the leaves of the node at split u0 reach from the nearest split with a smaller d on
-//     its left to the nearest one on its right (binary lifting over a sparse table of
-//     minima of d, two u16 reads per step);
-//   * its children are split at the argmin of d over the rest of each side (the table
-//     stores d << 9 | u, so the minimum is the position);
-//   * the box of any leaf range is two overlapping power-of-two entries of a sparse table
-//     of leaf boxes (min/max are idempotent), kept as order-preserving integer keys so a
-//     merge is IMNMX.
-// No atomics, no arrival order, all lanes busy; a node whose leaves leave the group on
-// either side is not computed here, and every subtree whose parent is such a node is
-// parked for build_top_kernel exactly as in build_walk_kernel (one queue slot each,
-// claimed with one global atomic per CTA).
-template <int LOG2G>
-struct RmqSmem {
-  static constexpr int G = 1 << LOG2G;
-  uint4 lo[LOG2G][G];             // level k, entry i: ordered keys of min over leaves i .. i+2^k-1
-  uint4 hi[LOG2G][G];
-  uint16_t m[LOG2G + 1][G + 8];   // level k, entry u: min of (d << 9 | u) over splits u .. u+2^k-1
-  uint8_t ingroup[G + 8];         // split u: the node's leaves lie inside the group
-  uint32_t warp_cnt[32];
-  uint32_t queue_base;
-};
-
-template <typename KeyT, int LOG2G>
-__global__ void __launch_bounds__(1 << LOG2G)
-build_rmq_kernel(const float4* __restrict__ tris, const uint32_t* __restrict__ sorted_idx,
-                 const KeyT* __restrict__ keys, uint32_t n, uint32_t* __restrict__ flags,
-                 Node* __restrict__ nodes, SortedTri* __restrict__ stris,
-                 BvhHeader* __restrict__ header, Continuation* __restrict__ queue,
-                 uint32_t* __restrict__ queue_count, uint32_t capacity) {
-  constexpr int G = 1 << LOG2G;
-  using Smem = RmqSmem<LOG2G>;
-  extern __shared__ __align__(16) unsigned char refit_smem_raw[];
-  Smem& sm = *reinterpret_cast<Smem*>(refit_smem_raw);
-  pdl_enter();
-  const uint32_t t = threadIdx.x, base = blockIdx.x * G, j = base + t;
-  {  // d of the split left of leaf j (u = t); thread 0 also the split after the group
-    uint32_t d = 0;
-    if (j >= 1u && j < n) d = delta_adj<KeyT>(keys[j - 1u], keys[j], j - 1u) + 1u;
-    sm.m[0][t] = (uint16_t)((d << 9) | t);
-    if (t == 0) {
-      const uint32_t e = base + G;
-      uint32_t de = 0;
-      if (e < n) de = delta_adj<KeyT>(keys[e - 1u], keys[e], e - 1u) + 1u;
-      sm.m[0][G] = (uint16_t)((de << 9) | (uint32_t)G);
-      sm.ingroup[G] = 0;
-    }
-  }
-  uint4 klo = make_uint4(0u, 0u, 0u, 0u), khi = klo;  // this leaf's box as ordered keys
-  if (j < n) {
-    const uint32_t prim = sorted_idx[j];
-    const float4 a = __ldg(tris + 3 * (uint64_t)prim), b = __ldg(tris + 3 * (uint64_t)prim + 1),
-                 c = __ldg(tris + 3 * (uint64_t)prim + 2);
-    float4* st = reinterpret_cast<float4*>(stris + j);
-    st[0] = make_float4(a.x, a.y, a.z, __uint_as_float(prim));
-    st[1] = make_float4(b.x, b.y, b.z, 0.0f);
-    st[2] = make_float4(c.x, c.y, c.z, 0.0f);
-    klo.x = min(min(ord_key(a.x), ord_key(b.x)), ord_key(c.x));
-    klo.y = min(min(ord_key(a.y), ord_key(b.y)), ord_key(c.y));
-    klo.z = min(min(ord_key(a.z), ord_key(b.z)), ord_key(c.z));
-    khi.x = max(max(ord_key(a.x), ord_key(b.x)), ord_key(c.x));
-    khi.y = max(max(ord_key(a.y), ord_key(b.y)), ord_key(c.y));
-    khi.z = max(max(ord_key(a.z), ord_key(b.z)), ord_key(c.z));
-  }
-  sm.lo[0][t] = klo;
-  sm.hi[0][t] = khi;
-  __syncthreads();
-
-  // ---- sparse tables ------------------------------------------------------------------
-#pragma unroll
-  for (int k = 1; k <= LOG2G; ++k) {
-    const uint32_t half = 1u << (k - 1), full = 1u << k;
-    if (k < LOG2G && t + full <= (uint32_t)G) {
-      const uint4 a = sm.lo[k - 1][t], b = sm.lo[k - 1][t + half];
-      const uint4 c = sm.hi[k - 1][t], d = sm.hi[k - 1][t + half];
-      sm.lo[k][t] = make_uint4(min(a.x, b.x), min(a.y, b.y), min(a.z, b.z), 0u);
-      sm.hi[k][t] = make_uint4(max(c.x, d.x), max(c.y, d.y), max(c.z, d.z), 0u);
-    }
-    if (t + full <= (uint32_t)G + 1u)
-      sm.m[k][t] = min(sm.m[k - 1][t], sm.m[k - 1][t + half]);
-    __syncthreads();
-  }
-  auto box_of = [&](uint32_t l, uint32_t r, uint4& blo, uint4& bhi) {  // leaves l..r (local)
-    const uint32_t k = 31u - (uint32_t)__clz((int)(r - l + 1u)), o = r + 1u - (1u << k);
-    const uint4 a = sm.lo[k][l], b = sm.lo[k][o], c = sm.hi[k][l], d = sm.hi[k][o];
-    blo = make_uint4(min(a.x, b.x), min(a.y, b.y), min(a.z, b.z), 0u);
-    bhi = make_uint4(max(c.x, d.x), max(c.y, d.y), max(c.z, d.z), 0u);
-  };
-  auto split_of = [&](uint32_t ul, uint32_t ur) -> uint32_t {  // argmin of d over splits ul..ur
-    const uint32_t k = 31u - (uint32_t)__clz((int)(ur - ul + 1u));
-    return (uint32_t)min(sm.m[k][ul], sm.m[k][ur + 1u - (1u << k)]) & 511u;
-  };
-
-  // ---- the node at split u0 = t --------------------------------------------------------
-  const uint32_t d0 = (uint32_t)sm.m[0][t] >> 9;
-  bool mine = false;          // this thread's node lies inside the group
-  uint32_t nL = 0, nR = 0;    // its leaves (local)
-  uint4 nlo = klo, nhi = khi;
-  if (t >= 1u && d0 != 0u) {
-    uint32_t cur = t;  // extend left while the minimum of d over [cur - step, cur - 1] stays above d0
-#pragma unroll
-    for (int k = LOG2G; k >= 0; --k) {
-      const uint32_t step = 1u << k;
-      if (cur >= step && ((uint32_t)sm.m[k][cur - step] >> 9) > d0) cur -= step;
-    }
-    uint32_t cr = t + 1u;  // extend right while the minimum over [cr, cr + step - 1] stays above d0
-#pragma unroll
-    for (int k = LOG2G; k >= 0; --k) {
-      const uint32_t step = 1u << k;
-      if (cr + step <= (uint32_t)G + 1u && ((uint32_t)sm.m[k][cr] >> 9) > d0) cr += step;
-    }
-    if (cur >= 1u && cr <= (uint32_t)G) {
-      mine = true;
-      nL = cur - 1u;  // the leaf right of the smaller split on the left
-      nR = cr - 1u;   // the leaf left of the smaller split on the right
-      uint4 llo, lhi, rlo, rhi;
-      box_of(nL, t - 1u, llo, lhi);
-      box_of(t, nR, rlo, rhi);
-      const int enc_l = (nL == t - 1u) ? ~(int)(base + nL) : (int)(base + split_of(nL + 1u, t - 1u) - 1u);
-      const int enc_r = (nR == t) ? ~(int)(base + t) : (int)(base + split_of(t + 1u, nR) - 1u);
-      float4* np = reinterpret_cast<float4*>(nodes + (base + t - 1u));
-      np[0] = make_float4(ord_unkey(llo.x), ord_unkey(llo.y), ord_unkey(llo.z), __int_as_float(enc_l));
-      np[1] = make_float4(ord_unkey(lhi.x), ord_unkey(lhi.y), ord_unkey(lhi.z), __uint_as_float(base + nL));
-      np[2] = make_float4(ord_unkey(rlo.x), ord_unkey(rlo.y), ord_unkey(rlo.z), __int_as_float(enc_r));
-      np[3] = make_float4(ord_unkey(rhi.x), ord_unkey(rhi.y), ord_unkey(rhi.z), __uint_as_float(base + nR));
-      nlo = make_uint4(min(llo.x, rlo.x), min(llo.y, rlo.y), min(llo.z, rlo.z), 0u);
-      nhi = make_uint4(max(lhi.x, rhi.x), max(lhi.y, rhi.y), max(lhi.z, rhi.z), 0u);
-    }
-  }
-  sm.ingroup[t] = mine ? 1 : 0;
-  __syncthreads();
-
-  // ---- subtrees whose parent is not computed here: the root, or parked --------------------
-  // candidate 0: leaf t, candidate 1: the node at split t
-  auto orphan = [&](uint32_t l, uint32_t r, bool& is_root) -> bool {
-    const uint32_t dl = (uint32_t)sm.m[0][l] >> 9, dr = (uint32_t)sm.m[0][r + 1u] >> 9;
-    is_root = (dl == 0u && dr == 0u);
-    if (is_root) return false;
-    const uint32_t up = (dr > dl) ? r + 1u : l;  // the parent's split
-    return sm.ingroup[up] == 0;
-  };
-  bool root0 = false, root1 = false;
-  const bool park0 = (j < n) && orphan(t, t, root0);
-  const bool park1 = mine && orphan(nL, nR, root1);
-  if (j < n && root0)
-    store_root(Box{ord_unkey(klo.x), ord_unkey(klo.y), ord_unkey(klo.z), ord_unkey(khi.x),
-                   ord_unkey(khi.y), ord_unkey(khi.z)}, ~(int)j, header);
-  if (mine && root1)
-    store_root(Box{ord_unkey(nlo.x), ord_unkey(nlo.y), ord_unkey(nlo.z), ord_unkey(nhi.x),
-                   ord_unkey(nhi.y), ord_unkey(nhi.z)}, (int)(base + t - 1u), header);
-  const uint32_t cnt = (park0 ? 1u : 0u) + (park1 ? 1u : 0u);
-  const uint32_t lane = t & 31u, warp = t >> 5;
-  uint32_t incl = cnt;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    const uint32_t v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
-    if (lane >= (uint32_t)o) incl += v;
-  }
-  if (lane == 31u) sm.warp_cnt[warp] = incl;
-  __syncthreads();
-  if (t == 0) {
-    uint32_t total = 0;
-    for (int w = 0; w < G / 32; ++w) {
-      const uint32_t c = sm.warp_cnt[w];
-      sm.warp_cnt[w] = total;
-      total += c;
-    }
-    sm.queue_base = total ? atomicAdd(queue_count, total) : 0u;
-  }
-  __syncthreads();
-  uint32_t q = sm.queue_base + sm.warp_cnt[warp] + incl - cnt;
-  auto park = [&](const uint4& blo, const uint4& bhi, int enc, uint32_t l, uint32_t r) {
-    const Box bx{ord_unkey(blo.x), ord_unkey(blo.y), ord_unkey(blo.z),
-                 ord_unkey(bhi.x), ord_unkey(bhi.y), ord_unkey(bhi.z)};
-    if (q < capacity) {
-      float4* dst = reinterpret_cast<float4*>(queue + q);
-      dst[0] = make_float4(bx.lx, bx.ly, bx.lz, __int_as_float(enc));
-      dst[1] = make_float4(bx.hx, bx.hy, bx.hz, 0.0f);
-      reinterpret_cast<uint4*>(dst)[2] = make_uint4(base + l, base + r, 0u, 0u);
-    } else {
-      climb_build_global<KeyT>(bx, enc, base + l, base + r, keys, n, flags, nodes, header);  // queue full
-    }
-    ++q;
-  };
-  if (park0) park(klo, khi, ~(int)j, t, t);
-  if (park1) park(nlo, nhi, (int)(base + t - 1u), nL, nR);
 }
 
 // ---- refit_bvh: table-driven (parent words recorded by the build) -------------------
@@ -704,29 +517,8 @@ static int build_tree_impl(const float4* tris, const uint32_t* sorted_idx, const
   const size_t smem = sizeof(RefitSmem);
   RT_CUDA(cudaFuncSetAttribute(build_walk_kernel<KeyT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                (int)smem));
-  const int variant = params().tree_variant;
-  if (variant == 1 || variant == 2) {
-    if (variant == 1) {
-      constexpr int kLog = 7;
-      const size_t sm2 = sizeof(RmqSmem<kLog>);
-      RT_CUDA(cudaFuncSetAttribute(build_rmq_kernel<KeyT, kLog>,
-                                   cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2));
-      RT_CUDA(launch_pdl(build_rmq_kernel<KeyT, kLog>, (unsigned)((n + (1 << kLog) - 1) >> kLog),
-                         1 << kLog, sm2, s, tris, sorted_idx, keys, (uint32_t)n, flags, nodes, stris,
-                         header, queue, queue_count, capacity));
-    } else {
-      constexpr int kLog = 8;
-      const size_t sm2 = sizeof(RmqSmem<kLog>);
-      RT_CUDA(cudaFuncSetAttribute(build_rmq_kernel<KeyT, kLog>,
-                                   cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2));
-      RT_CUDA(launch_pdl(build_rmq_kernel<KeyT, kLog>, (unsigned)((n + (1 << kLog) - 1) >> kLog),
-                         1 << kLog, sm2, s, tris, sorted_idx, keys, (uint32_t)n, flags, nodes, stris,
-                         header, queue, queue_count, capacity));
-    }
-  } else {
-    RT_CUDA(launch_pdl(build_walk_kernel<KeyT>, blocks, kRefitLeaves, smem, s, tris, sorted_idx, keys,
-                       (uint32_t)n, flags, nodes, stris, header, queue, queue_count, capacity));
-  }
+  RT_CUDA(launch_pdl(build_walk_kernel<KeyT>, blocks, kRefitLeaves, smem, s, tris, sorted_idx, keys,
+                     (uint32_t)n, flags, nodes, stris, header, queue, queue_count, capacity));
   RT_LAUNCHED();
   RT_CUDA(launch_pdl(build_top_kernel<KeyT>, (capacity + 255) / 256, 256, 0, s,
                      (const Continuation*)queue, (const uint32_t*)queue_count, capacity, keys,
