@@ -63,9 +63,9 @@ def test_ray_generators_match_oracle(rt, oracle):
 
 
 # ---- T2-T4: build ------------------------------------------------------------------
-def _build_and_compare(rt, oracle, tris, key_bits):
+def _build_and_compare(rt, oracle, tris, key_bits, timings=True):
     ob = oracle.OracleBvh(tris, key_bits)
-    with rt.Bvh.build(dev(tris), key_bits=key_bits, keep_keys=True, timings=True) as gb:
+    with rt.Bvh.build(dev(tris), key_bits=key_bits, keep_keys=True, timings=timings) as gb:
         n = gb.n_tris
         assert n == ob.n
         assert np.array_equal(bits(gb.bounds), bits(ob.bounds)), "A1 scene bounds"
@@ -79,8 +79,9 @@ def _build_and_compare(rt, oracle, tris, key_bits):
         assert np.array_equal(bits(boxes), bits(ob.boxes)), "A5 node boxes"
         check_tree_invariants(n, left, right, parent, idx)
         check_boxes(n, left, right, boxes, tris, idx)
-        t = gb.build_times()
-        assert t["total"] > 0
+        if timings:
+            t = gb.build_times()
+            assert t["total"] > 0
     return ob
 
 
@@ -397,3 +398,36 @@ def test_launch_counter_counts(rt, oracle):
     with rt.Bvh.build(tris) as gb:
         gb.trace(rt.gen_primary_rays(rt.camera.cornell_camera(64, 64), 64, 64))
     assert rt.kernel_launches() - before >= 10
+
+
+# ---- knobs that must not change a bit ---------------------------------------------------
+@pytest.mark.parametrize("pdl", [0, 1])
+def test_build_with_and_without_dependent_launch(rt, oracle, pdl):
+    """`build.pdl`: the build chain launched as programmatic dependents (default) or
+    as plain stream-ordered launches; both must give the oracle's tree, also when the
+    same pool memory is rebuilt back to back with different scenes."""
+    rt.set_param("build.pdl", pdl)
+    try:
+        for rep in range(3):
+            for n, key_bits in [(40001, 30), (7681, 63), (200000, 30)]:
+                tris = oracle.gen_scene(oracle.SCENE_SOUP, n, 0, seed=100 + rep)
+                # no stage events: nothing but kernels between the first and the last launch
+                _build_and_compare(rt, oracle, tris, key_bits, timings=False)
+    finally:
+        rt.set_param("build.pdl", 1)
+
+
+@pytest.mark.parametrize("levels", [8, 16, 24])
+def test_shared_memory_stack_top(rt, oracle, levels):
+    """`trace.sh_stack`: the first levels of the traversal stack in shared memory."""
+    tris = oracle.gen_scene(oracle.SCENE_SOUP, 20000, 0, seed=5)
+    v = tris.reshape(-1, 4)[:, :3]
+    box = np.concatenate([v.min(0), v.max(0)])
+    rays = oracle.gen_random_rays(box, 4, 0, 60000)
+    rt.set_param("trace.sh_stack", levels)
+    try:
+        for flags in (0, 1):
+            got, want = _trace_both(rt, oracle, tris, rays, flags)
+            assert np.array_equal(bits(got), bits(want)), (levels, flags)
+    finally:
+        rt.set_param("trace.sh_stack", 0)
