@@ -7,7 +7,7 @@ include/gpu_raytracer.h: build_bvh / trace_rays / free_bvh.  This package is the
 ctypes mirror of that ABI plus host logic (camera, sharding, image output).
 """
 from ._lib import (RT_ANY_HIT_PRIM, RT_SCENE_CORNELL, RT_SCENE_SOUP, RT_SCENE_SPHEREFLAKE,
-                   RT_SCENE_TERRAIN, RT_TRACE_ANY, RT_TRACE_CLOSEST, RT_TRACE_WATERTIGHT, RtError,
+                   RT_SCENE_TERRAIN, RT_TRACE_ANY, RT_TRACE_CLOSEST, RT_TRACE_REORDER, RT_TRACE_WATERTIGHT, RtError,
                    SO_PATH, lib)
 from .api import (Bvh, gen_ao_rays, gen_primary_rays, gen_random_rays, gen_scene, hit_prims,
                   kernel_launches, load_obj, load_tris, save_tris, scene_size, set_param, shade,
@@ -17,6 +17,6 @@ from . import camera, image, sharding
 __all__ = [
     "Bvh", "gen_scene", "gen_primary_rays", "gen_random_rays", "gen_ao_rays", "shade", "scene_size",
     "hit_prims", "sort_pairs", "set_param", "load_obj", "load_tris", "save_tris", "kernel_launches", "camera", "image", "sharding", "lib",
-    "RtError", "SO_PATH", "RT_TRACE_CLOSEST", "RT_TRACE_ANY", "RT_TRACE_WATERTIGHT", "RT_ANY_HIT_PRIM", "RT_SCENE_CORNELL",
+    "RtError", "SO_PATH", "RT_TRACE_CLOSEST", "RT_TRACE_ANY", "RT_TRACE_WATERTIGHT", "RT_TRACE_REORDER", "RT_ANY_HIT_PRIM", "RT_SCENE_CORNELL",
     "RT_SCENE_SOUP", "RT_SCENE_SPHEREFLAKE", "RT_SCENE_TERRAIN",
 ]

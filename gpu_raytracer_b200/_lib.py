@@ -13,7 +13,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 SO_PATH = os.environ.get("RT_LIB") or os.path.join(_HERE, "libgpu_raytracer_b200.so")
 
 RT_OK, RT_ERR_INVALID, RT_ERR_CUDA, RT_ERR_OOM, RT_ERR_NO_DEVICE, RT_ERR_LIMIT = 0, -1, -2, -3, -4, -5
-RT_TRACE_CLOSEST, RT_TRACE_ANY, RT_TRACE_WATERTIGHT = 0, 1, 2
+RT_TRACE_CLOSEST, RT_TRACE_ANY, RT_TRACE_WATERTIGHT, RT_TRACE_REORDER = 0, 1, 2, 4
 RT_ANY_HIT_PRIM = 0x7FFFFFFF
 RT_BUILD_KEEP_KEYS, RT_BUILD_TIMINGS, RT_BUILD_WIDE4 = 1, 2, 4
 RT_SCENE_CORNELL, RT_SCENE_SOUP, RT_SCENE_SPHEREFLAKE, RT_SCENE_TERRAIN = 0, 1, 2, 3

@@ -561,11 +561,47 @@ struct Pipeline {
 };
 thread_local Pipeline t_pipe;
 
+// RT_TRACE_REORDER on device buffers: per batch of up to 64M rays, coherence keys (origin
+// cell, direction bin), the build's radix sort on (key, ray index), and the traversal walks the
+// rays in key order through the sorted index; hits land at the rays' own positions.
+constexpr uint64_t kReorderBatch = 1ull << 26;
+constexpr uint64_t kReorderMin = 1ull << 16;  // below this the sort's fixed cost outweighs the gain
+int trace_reordered(const rt_bvh* h, const float4* rays, uint64_t n_rays, uint32_t flags,
+                    float4* hits, unsigned long long* counter, cudaStream_t s) {
+  TempPool tmp(s);
+  const uint64_t cap = n_rays < kReorderBatch ? n_rays : kReorderBatch;
+  void* keys = nullptr;
+  SortWorkspace ws;
+  RT_TRY(tmp.alloc(&keys, cap * 4));
+  RT_TRY(tmp.alloc(&ws.rec_a, cap * 8));
+  RT_TRY(tmp.alloc(&ws.rec_b, cap * 8));
+  RT_TRY(tmp.alloc((void**)&ws.vals, cap * 4));
+  RT_TRY(tmp.alloc((void**)&ws.hist, sort_hist_words(30) * 4));
+  ws.chunk_words = sort_chunk_words(cap, 30);
+  RT_TRY(tmp.alloc((void**)&ws.chunk_hist, ws.chunk_words * 4));
+  for (uint64_t first = 0; first < n_rays; first += kReorderBatch) {
+    const uint64_t n = (n_rays - first < kReorderBatch) ? n_rays - first : kReorderBatch;
+    RT_TRY(launch_ray_keys(rays + 2 * first, n, h->bounds, (uint32_t*)keys, s));
+    void* skeys = nullptr;
+    uint32_t* perm = nullptr;
+    RT_TRY(launch_sort(keys, n, 30, ws, /*iota_payload=*/true, &skeys, &perm, s, false,
+                       /*max_passes=*/2));  // 20-bit keys
+    RT_TRY(launch_trace(h->nodes, h->stris, h->n, h->root, rays + 2 * first, n, flags & 3u,
+                        hits + first, counter, s, nullptr, nullptr, perm));
+  }
+  return 0;
+}
+
 int trace_device(const rt_bvh* h, const float4* rays, uint64_t n_rays, uint32_t flags,
                  float4* hits, cudaStream_t s) {
   unsigned long long* counter = nullptr;
   RT_CUDA(cudaMallocAsync((void**)&counter, sizeof(unsigned long long), s));
-  int rc = launch_trace_h(h, rays, n_rays, flags, hits, counter, s);
+  int rc;
+  if ((flags & RT_TRACE_REORDER) && n_rays >= kReorderMin && h->n != 0 &&
+      params().trace_variant != 0 && !(h->is_wide && params().trace_wide != 0))
+    rc = trace_reordered(h, rays, n_rays, flags, hits, counter, s);
+  else
+    rc = launch_trace_h(h, rays, n_rays, flags & 3u, hits, counter, s);
   cudaFreeAsync(counter, s);
   return rc;
 }
@@ -739,7 +775,7 @@ extern "C" int trace_rays_async(const rt_bvh* h, const float* rays, uint64_t n_r
   if (!h) return fail(RT_ERR_INVALID, "trace_rays: handle is NULL");
   if (n_rays == 0) return RT_OK;
   if (!rays || !hits) return fail(RT_ERR_INVALID, "trace_rays: rays or hits is NULL");
-  if (flags > 3u) return fail(RT_ERR_INVALID, "trace_rays: unknown flags 0x%x", flags);
+  if (flags > 7u) return fail(RT_ERR_INVALID, "trace_rays: unknown flags 0x%x", flags);
   DeviceScope scope;
   RT_TRY(scope.enter(h->device));
   return trace_device(h, reinterpret_cast<const float4*>(rays), n_rays, flags,
@@ -751,7 +787,7 @@ extern "C" int trace_rays(const rt_bvh* h, const float* rays, uint64_t n_rays, u
   if (!h) return fail(RT_ERR_INVALID, "trace_rays: handle is NULL");
   if (n_rays == 0) return RT_OK;
   if (!rays || !hits) return fail(RT_ERR_INVALID, "trace_rays: rays or hits is NULL");
-  if (flags > 3u) return fail(RT_ERR_INVALID, "trace_rays: unknown flags 0x%x", flags);
+  if (flags > 7u) return fail(RT_ERR_INVALID, "trace_rays: unknown flags 0x%x", flags);
   DeviceScope scope;
   RT_TRY(scope.enter(h->device));
   int d0 = -1, d1 = -1;
@@ -771,6 +807,7 @@ extern "C" int trace_rays(const rt_bvh* h, const float* rays, uint64_t n_rays, u
     RT_CUDA(cudaStreamSynchronize(0));
     return RT_OK;
   }
+  flags &= 3u;  // RT_TRACE_REORDER applies to device-resident batches only
   // partial zero-copy: e.g. rays staged by the copy engine, hits stored by the
   // kernel straight into pinned host memory (posted PCIe writes need no staging)
   // both buffers pinned on the host: one kernel launch follows the upload (see trace_streamed)

@@ -108,7 +108,7 @@ uint64_t sort_chunk_words(uint64_t n, uint32_t key_bits);
 // (launch_morton produced them); ws.hist must then have been zeroed before that.
 int launch_sort(void* keys, uint64_t n, uint32_t key_bits, const SortWorkspace& ws,
                 bool iota_payload, void** keys_out, uint32_t** vals_out, cudaStream_t s,
-                bool first_hist_ready = false);
+                bool first_hist_ready = false, int max_passes = 0);
 
 // A4 + A5 fused: topology, triangle reorder, boxes (refit.cu).  keys: the sorted Morton
 // codes; flags: n-1 u32, zeroed by the launcher.  Writes nodes (indexed by split
@@ -186,7 +186,10 @@ int launch_trace(const Node* nodes, const SortedTri* stris, uint64_t n_tris, int
                  const float4* rays,
                  uint64_t n_rays, uint32_t flags, float4* hits, unsigned long long* ray_counter,
                  cudaStream_t s, unsigned long long* stats = nullptr,
-                 const TracePipe* pipe = nullptr);
+                 const TracePipe* pipe = nullptr, const uint32_t* perm = nullptr);
+// RT_TRACE_REORDER: 20-bit coherence keys (origin cell, direction bin) of n device rays;
+// box = the scene bounds {min.xyz, max.xyz} (host values)
+int launch_ray_keys(const float4* rays, uint64_t n, const float* box, uint32_t* keys, cudaStream_t s);
 
 // tuning knobs (rt_set_param)
 struct Params {

@@ -557,12 +557,14 @@ uint64_t sort_chunk_words(uint64_t n, uint32_t key_bits) {
 
 int launch_sort(void* keys, uint64_t n, uint32_t key_bits, const SortWorkspace& ws,
                 bool iota_payload, void** keys_out, uint32_t** vals_out, cudaStream_t s,
-                bool first_hist_ready) {
+                bool first_hist_ready, int max_passes) {
   *keys_out = keys;
   *vals_out = ws.vals;
   if (n > ((1ull << 30) - 1)) return fail(-5, "sort: n = %llu beyond 2^30-1", (unsigned long long)n);
   if (n == 0) return 0;
-  const SortPlan plan = sort_plan(key_bits);
+  SortPlan plan = sort_plan(key_bits);
+  // keys known to be narrower than key_bits (the ray coherence keys): only the low digits
+  if (max_passes > 0 && max_passes < plan.passes) plan.passes = max_passes;
   const int variant = clamp_variant();
   const uint64_t bins = 1ull << plan.bits;
   const ChunkGeom g = make_geom(n, key_bits);

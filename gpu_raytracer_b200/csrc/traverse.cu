@@ -162,7 +162,7 @@ trace_kernel_dyn(const Node* __restrict__ nodes, const SortedTri* __restrict__ s
                  unsigned long long n_rays, float4* __restrict__ hits,
                  unsigned long long* __restrict__ ray_counter,
                  unsigned long long* __restrict__ stats, int chunk, int refill_min, int leaf_min,
-                 TracePipe pipe) {
+                 TracePipe pipe, const uint32_t* __restrict__ perm) {
   const int lane = threadIdx.x & 31;
   const uint32_t lt_mask = (1u << lane) - 1u;
   const float inf = __int_as_float(0x7f800000);
@@ -292,6 +292,7 @@ trace_kernel_dyn(const Node* __restrict__ nodes, const SortedTri* __restrict__ s
       const uint32_t slot = __popc(idle & lt_mask);
       if (!has_ray && slot < avail) {
         my_ray = chunk_next + slot;
+        if (!PIPE && perm) my_ray = perm[my_ray];  // RT_TRACE_REORDER: position in key order -> ray
         const float4 ro = PIPE ? ld_cg_f4(rays + 2 * my_ray) : ld_stream(rays + 2 * my_ray);
         const float4 rd = PIPE ? ld_cg_f4(rays + 2 * my_ray + 1) : ld_stream(rays + 2 * my_ray + 1);
         r.ox = ro.x; r.oy = ro.y; r.oz = ro.z; r.tmin = ro.w;
@@ -411,13 +412,61 @@ trace_kernel_dyn(const Node* __restrict__ nodes, const SortedTri* __restrict__ s
   }
 }
 
+// RT_TRACE_REORDER: coherence key of a ray = Morton code of its origin in the scene box
+// (4 bits per axis) above 8 interleaved bits of its direction on the unit cube (3, 3, 2
+// bits): 20 bits, two passes of the radix sort, about one warp of rays per key at 32M rays.  Rays that start in the same cell and point the same way become neighbours in key
+// order and share their node fetches in L1.  The key only orders the work: every ray's
+// result is what it would be in any other order.
+__device__ __forceinline__ uint32_t spread3_5(uint32_t x) {  // 5 bits -> every third bit
+  x &= 0x1Fu;
+  x = (x | (x << 8)) & 0x0000100Fu;
+  x = (x | (x << 4)) & 0x000010C3u;
+  x = (x | (x << 2)) & 0x00001249u;  // input bit b now at position 3b
+  return x;
+}
+__global__ void __launch_bounds__(256)
+ray_key_kernel(const float4* __restrict__ rays, uint32_t n, float lx, float ly, float lz, float sx,
+               float sy, float sz, uint32_t* __restrict__ keys) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float4 o = ld_stream(rays + 2 * (size_t)i), d = ld_stream(rays + 2 * (size_t)i + 1);
+  const uint32_t qx = (uint32_t)fminf(fmaxf((o.x - lx) * sx, 0.0f), 15.0f);
+  const uint32_t qy = (uint32_t)fminf(fmaxf((o.y - ly) * sy, 0.0f), 15.0f);
+  const uint32_t qz = (uint32_t)fminf(fmaxf((o.z - lz) * sz, 0.0f), 15.0f);
+  const float m = fmaxf(fmaxf(fabsf(d.x), fabsf(d.y)), fmaxf(fabsf(d.z), 1e-30f));
+  const float k = 4.0f / m;
+  const uint32_t dx = (uint32_t)fminf(fmaxf(d.x * k + 4.0f, 0.0f), 7.0f);
+  const uint32_t dy = (uint32_t)fminf(fmaxf(d.y * k + 4.0f, 0.0f), 7.0f);
+  const uint32_t dz = (uint32_t)fminf(fmaxf(d.z * k + 4.0f, 0.0f), 7.0f) >> 1;
+  const uint32_t om = (spread3_5(qx) << 2) | (spread3_5(qy) << 1) | spread3_5(qz);  // 12 bits
+  const uint32_t dm = ((dx >> 2) << 7) | ((dy >> 2) << 6) | ((dz >> 1) << 5) | (((dx >> 1) & 1u) << 4) |
+                      (((dy >> 1) & 1u) << 3) | ((dz & 1u) << 2) | ((dx & 1u) << 1) | (dy & 1u);
+  keys[i] = (om << 8) | dm;
+}
+
 }  // namespace
+
+int launch_ray_keys(const float4* rays, uint64_t n, const float* box, uint32_t* keys, cudaStream_t s) {
+  if (n == 0) return 0;
+  float sc[3];
+  for (int a = 0; a < 3; ++a) {
+    const float e = box[3 + a] - box[a];
+    sc[a] = e > 0.0f ? 16.0f / e : 0.0f;
+  }
+  ray_key_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(rays, (uint32_t)n, box[0], box[1], box[2],
+                                                            sc[0], sc[1], sc[2], keys);
+  RT_LAUNCHED();
+  return 0;
+}
 
 int launch_trace(const Node* nodes, const SortedTri* stris, uint64_t n_tris, int root,
                  const float4* rays,
                  uint64_t n_rays, uint32_t flags, float4* hits, unsigned long long* ray_counter,
-                 cudaStream_t s, unsigned long long* stats, const TracePipe* pipe) {
+                 cudaStream_t s, unsigned long long* stats, const TracePipe* pipe,
+                 const uint32_t* perm) {
   if (n_rays == 0) return 0;
+  if (perm && (pipe || params().trace_variant == 0))
+    return fail(-1, "launch_trace: a ray permutation needs the dynamic-fetch kernel, device buffers");
   if (pipe && (stats || params().trace_variant == 0))
     return fail(-1, "launch_trace: the streamed mode needs the dynamic-fetch kernel without stats");
   RT_CUDA(cudaMemsetAsync(ray_counter, 0, sizeof(unsigned long long), s));
@@ -440,7 +489,7 @@ int launch_trace(const Node* nodes, const SortedTri* stris, uint64_t n_tris, int
       if (p.trace_chunk <= 0) chunk = 32;
 #define RT_TRACE_PIPE(A, W)                                                          \
   trace_kernel_dyn<A, false, W, true, 0><<<(unsigned)blocks, kTraceThreads, 0, s>>>( \
-      nodes, stris, (uint32_t)n_tris, root, rays, n_rays, hits, ray_counter, stats, chunk, refill_min, leaf_min, *pipe)
+      nodes, stris, (uint32_t)n_tris, root, rays, n_rays, hits, ray_counter, stats, chunk, refill_min, leaf_min, *pipe, nullptr)
       if (any) { if (wt) RT_TRACE_PIPE(true, true); else RT_TRACE_PIPE(true, false); }
       else     { if (wt) RT_TRACE_PIPE(false, true); else RT_TRACE_PIPE(false, false); }
 #undef RT_TRACE_PIPE
@@ -450,7 +499,7 @@ int launch_trace(const Node* nodes, const SortedTri* stris, uint64_t n_tris, int
     const TracePipe no_pipe = {nullptr, nullptr, nullptr, nullptr, 0};
 #define RT_TRACE_DYN_K(A, S, W, K)                                                   \
   trace_kernel_dyn<A, S, W, false, K><<<(unsigned)blocks, kTraceThreads, 0, s>>>(    \
-      nodes, stris, (uint32_t)n_tris, root, rays, n_rays, hits, ray_counter, stats, chunk, refill_min, leaf_min, no_pipe)
+      nodes, stris, (uint32_t)n_tris, root, rays, n_rays, hits, ray_counter, stats, chunk, refill_min, leaf_min, no_pipe, perm)
 #define RT_TRACE_DYN(A, S, W) RT_TRACE_DYN_K(A, S, W, 0)
     const int shs = p.trace_sh_stack;
     if (!st && !wt && shs > 0) {  // experiment: stack top in shared memory

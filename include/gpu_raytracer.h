@@ -58,6 +58,12 @@ extern "C" {
 #define RT_TRACE_ANY 1u
 #define RT_TRACE_WATERTIGHT 2u /* A7 option: Woop-Benthin-Wald watertight triangle test instead of
                                   Moeller-Trumbore; may be combined with RT_TRACE_ANY */
+#define RT_TRACE_REORDER 4u    /* incoherent batches: trace the rays in the order of a coherence key
+                                  (origin cell, direction bin; one radix sort of (key, index) per
+                                  batch of <= 64M rays).  Hits are written at the rays' own
+                                  positions and are bit-identical with and without the flag.
+                                  Device buffers, BVH2, >= 64K rays; ignored otherwise.  Pays for
+                                  random rays (1.2-1.3x), costs ~15 % on coherent ones. */
 #define RT_ANY_HIT_PRIM 0x7FFFFFFF
 
 /* build flags */

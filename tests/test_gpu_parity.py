@@ -431,3 +431,28 @@ def test_shared_memory_stack_top(rt, oracle, levels):
             assert np.array_equal(bits(got), bits(want)), (levels, flags)
     finally:
         rt.set_param("trace.sh_stack", 0)
+
+
+@pytest.mark.parametrize("name", ["soup20k", "flake"])
+def test_reordered_trace_is_bit_identical(rt, oracle, name):
+    """RT_TRACE_REORDER walks the rays in coherence-key order; every hit must land at its
+    ray's own position with the oracle's bits, for closest-hit, any-hit and watertight."""
+    kind, p0, p1, seed = SCENES[name]
+    tris = oracle.gen_scene(kind, p0, p1, seed)
+    v = tris.reshape(-1, 4)[:, :3]
+    box = np.concatenate([v.min(0), v.max(0)])
+    rays = oracle.gen_random_rays(box, 4, 0, 150001)  # ragged, above the 64K threshold
+    rays[7, 4:7] = 0.0          # a zero direction
+    rays[11, 0:3] = box[3:] * 4  # an origin far outside the scene box
+    ob = oracle.OracleBvh(tris, 30)
+    with rt.Bvh.build(dev(tris)) as gb:
+        d_rays = dev(rays)
+        for flags in (0, rt.RT_TRACE_ANY, rt.RT_TRACE_WATERTIGHT):
+            want = ob.trace(rays, flags)
+            plain = gb.trace(d_rays, flags).cpu().numpy()
+            got = gb.trace(d_rays, flags | rt.RT_TRACE_REORDER).cpu().numpy()
+            assert np.array_equal(bits(got), bits(plain)), flags
+            assert np.array_equal(bits(got), bits(want)), flags
+        # host buffers: the flag is accepted and ignored
+        got = gb.trace(rays, rt.RT_TRACE_REORDER)
+        assert np.array_equal(bits(np.asarray(got)), bits(ob.trace(rays, 0)))

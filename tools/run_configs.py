@@ -62,7 +62,8 @@ def config4():
         assert sorted_ok and perm_ok and topo_ok and once_ok and union_ok
 
 
-def config5(total):
+def config5(total, reorder=False):
+    flags = g.RT_TRACE_REORDER if reorder else 0
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
     if world > 1:
         import torch.distributed as dist
@@ -80,14 +81,14 @@ def config5(total):
     trace_ms, nhit, done = 0.0, 0, 0
     # warm-up
     g.gen_random_rays(box, wl.random_seed, first, min(batch, count), out=rays)
-    bvh.trace_async(rays[: min(batch, count)], hits)
+    bvh.trace_async(rays[: min(batch, count)], hits, flags)
     torch.cuda.synchronize()
     t0 = time.perf_counter()
     while done < count:
         c = min(batch, count - done)
         g.gen_random_rays(box, wl.random_seed, first + done, c, out=rays)
         e0.record()
-        bvh.trace_async(rays[:c], hits[:c])
+        bvh.trace_async(rays[:c], hits[:c], flags)
         e1.record()
         torch.cuda.synchronize()
         trace_ms += e0.elapsed_time(e1)
@@ -100,7 +101,7 @@ def config5(total):
         dist.all_reduce(vals, op=dist.ReduceOp.MAX)
         dist.all_reduce(tot)
     if rank == 0:
-        emit(config=5, scene=wl.name, n_tris=int(tris.shape[0]), rays=total, n_gpus=world,
+        emit(config=5, scene=wl.name, reorder=bool(reorder), n_tris=int(tris.shape[0]), rays=total, n_gpus=world,
              trace_ms=float(vals[0]), mrays_s=total / float(vals[0]) / 1e3,
              wall_s_incl_generation=float(vals[1]), hit_fraction=float(tot[0]) / total)
     bvh.close()
@@ -113,4 +114,5 @@ if __name__ == "__main__":
     if which == "4":
         config4()
     else:
-        config5(int(float(sys.argv[2])) if len(sys.argv) > 2 else 10**9)
+        config5(int(float(sys.argv[2])) if len(sys.argv) > 2 else 10**9,
+                reorder=len(sys.argv) > 3 and sys.argv[3] == "reorder")
