@@ -424,9 +424,8 @@ struct Shape {
   int threads, ipt32, ipt64, ctas_per_sm;
 };
 // variant 0: 512 threads, 2 CTAs/SM; variant 1: 256 threads, 4 CTAs/SM
-// variant 2: 1024 threads, 1 CTA/SM (twice the tile: twice the keys per bin and output run)
-constexpr int kNumVariants = 3;
-constexpr Shape kShapes[kNumVariants] = {{512, 15, 10, 2}, {256, 16, 11, 4}, {1024, 15, 12, 1}};
+constexpr int kNumVariants = 2;
+constexpr Shape kShapes[kNumVariants] = {{512, 15, 10, 2}, {256, 16, 11, 4}};
 
 int clamp_variant() {
   int v = params().sort_variant;
@@ -518,8 +517,6 @@ int run_pass(int variant, const PassIO& io, uint32_t* chunk_hist, uint32_t* tota
   RT_LAUNCHED();
   if (variant == 1)
     return launch_scatter<KeyT, BITS, 256, k64 ? 11 : 16, 4>(io, chunk_hist, g, shift, s);
-  if (variant == 2)
-    return launch_scatter<KeyT, BITS, 1024, k64 ? 12 : 15, 1>(io, chunk_hist, g, shift, s);
   return launch_scatter<KeyT, BITS, 512, k64 ? 10 : 15, 2>(io, chunk_hist, g, shift, s);
 }
 

@@ -13,8 +13,8 @@ from tools.probe import scene  # noqa: E402
 name = sys.argv[1] if len(sys.argv) > 1 else "terrain100m"
 key_bits = int(sys.argv[2]) if len(sys.argv) > 2 else 63
 tris = scene(name)
-for variant in (0, 1, 2):
-    for bits in ((9, 10) if key_bits == 63 else (10,)):
+for variant in (0, 1):
+    for bits in ((9, 10, 11) if key_bits == 63 else (8, 10)):
         g.set_param("sort.variant", variant)
         g.set_param("sort.bits", bits)
         best = None
