@@ -42,3 +42,22 @@ def frame_box(box, width: int, height: int, vfov_deg: float = 40.0, direction=(0
 # the §8(d) camera of config 1: Cornell box seen from (0.5, 0.5, -1.5)
 def cornell_camera(width: int = 256, height: int = 256) -> np.ndarray:
     return pinhole((0.5, 0.5, -1.5), (0.5, 0.5, 0.5), (0.0, 1.0, 0.0), 40.0, width, height)
+
+
+def interlaced_field(cam, rank: int, world: int) -> np.ndarray:
+    """Camera of ``rank``'s field of a frame with ``world`` times the rows of ``cam``'s.
+
+    The tall frame (same frustum, ``height * world`` rows) is dealt to the ranks row by
+    row: rank r renders rows r, r + world, r + 2 world, ...  Every field covers the whole
+    frustum, so the ranks get statistically equal work, where contiguous bands give the
+    ranks that see the middle of the scene several times the work of those that see its
+    border ("contiguous ranges of the ray batch (or image tiles)").  The
+    field is itself a ``width x height`` pinhole image: row y of the field looks through
+    corner + (y * world + rank + 0.5) * dv / world, i.e. through the tall frame's row
+    y * world + rank."""
+    if world <= 0 or not (0 <= rank < world):
+        raise ValueError("bad rank/world")
+    c = np.asarray(cam, dtype=np.float64).reshape(12).copy()
+    dv = c[9:12]
+    c[3:6] = c[3:6] + dv * ((rank + 0.5) / world - 0.5)
+    return c.astype(np.float32)

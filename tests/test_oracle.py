@@ -263,3 +263,21 @@ def test_ao_rays(oracle):
     frac = (oracle.hit_prims(occ)[live] == oracle.ANY_HIT_PRIM).mean()
     assert 0.05 < frac < 0.9
     assert (oracle.hit_prims(occ)[~live] == -1).all()
+
+
+def test_interlaced_fields_tile_the_tall_frame():
+    """camera.interlaced_field: the fields of all ranks together are the rows of the frame
+    with world x the rows (same frustum), each exactly once."""
+    from gpu_raytracer_b200 import camera
+    import oracle as O
+    w, h, world = 16, 6, 4
+    cam = camera.pinhole((0.5, 0.4, -2.0), (0.5, 0.5, 0.5), (0, 1, 0), 35.0, w, h)
+    tall = cam.copy()
+    tall[9:12] /= world
+    want = O.gen_primary_rays(tall, w, h * world).reshape(h * world, w, 8)
+    for r in range(world):
+        got = O.gen_primary_rays(camera.interlaced_field(cam, r, world), w, h).reshape(h, w, 8)
+        assert np.allclose(got, want[r::world], rtol=0, atol=2e-6), r
+    assert np.array_equal(camera.interlaced_field(cam, 0, 1), cam)
+    with pytest.raises(ValueError):
+        camera.interlaced_field(cam, 4, 4)
