@@ -482,7 +482,9 @@ int launch_trace(const Node* nodes, const SortedTri* stris, uint64_t n_tris, int
     int chunk = p.trace_chunk > 0 ? p.trace_chunk : 64;
     // small batches: keep every resident warp busy rather than a few warps long
     if (p.trace_chunk <= 0 && n_rays < blocks * (kTraceThreads / 32) * (uint64_t)chunk * 2) chunk = 32;
-    const int refill_min = p.trace_refill_min > 0 ? p.trace_refill_min : 16;
+    // closest-hit rays live longer than occlusion rays: refilling at 8 idle lanes instead of 16
+    // measured +3.6 % on flake10m primary rays and within 1 % elsewhere; any-hit prefers 16
+    const int refill_min = p.trace_refill_min > 0 ? p.trace_refill_min : (any ? 16 : 8);
     const int leaf_min = p.trace_leaf_min > 0 ? p.trace_leaf_min : 8;
     if (pipe) {
       // 32-ray chunks: when a piece arrives every resident warp gets a share of it
