@@ -316,9 +316,19 @@ int build_impl(rt_bvh* h, const float* tris_in, uint32_t flags, cudaStream_t s) 
     RT_TRY(tmp.alloc(&ws.keys_alt, n * ksz));
     RT_TRY(tmp.alloc((void**)&ws.vals_alt, n * 4));
   }
+  // 63-bit keys, hybrid order (launch_sort63_hybrid): the 30-bit passes' buffers as well
+  const bool hybrid = h->key_bits == 63 && params().sort_hybrid != 0 && n >= 2;
+  uint32_t *k32 = nullptr, *long_run = nullptr;
+  if (hybrid) {
+    RT_TRY(tmp.alloc(&ws.rec_a, n * 8));
+    RT_TRY(tmp.alloc(&ws.rec_b, n * 8));
+    RT_TRY(tmp.alloc((void**)&k32, n * 4));
+    RT_TRY(tmp.alloc((void**)&long_run, 32));
+  }
   RT_TRY(tmp.alloc((void**)&ws.vals, n * 4));
   RT_TRY(tmp.alloc((void**)&ws.hist, sort_hist_words(h->key_bits) * 4));
   ws.chunk_words = sort_chunk_words(n, h->key_bits);
+  if (hybrid && sort_chunk_words(n, 30) > ws.chunk_words) ws.chunk_words = sort_chunk_words(n, 30);
   RT_TRY(tmp.alloc((void**)&ws.chunk_hist, ws.chunk_words * 4));
   RT_TRY(tmp.alloc(&bkeys, 32));
   float* centroids = nullptr;
@@ -344,13 +354,17 @@ int build_impl(rt_bvh* h, const float* tris_in, uint32_t flags, cudaStream_t s) 
   RT_TRY(launch_bounds(tris, n, (uint32_t*)bkeys, centroids, s));
   RT_TRY(mark(1));
   int hist_ready = 0;
-  RT_TRY(launch_morton(centroids, n, (const uint32_t*)bkeys, h->key_bits, keys, ws.chunk_hist,
-                       ws.hist, &hist_ready, s));
+  RT_TRY(launch_morton(centroids, n, (const uint32_t*)bkeys, h->key_bits, keys,
+                       hybrid ? nullptr : ws.chunk_hist, ws.hist, &hist_ready, s));
   RT_TRY(mark(2));
   void* skeys = nullptr;
   uint32_t* svals = nullptr;
-  RT_TRY(launch_sort(keys, n, h->key_bits, ws, /*iota_payload=*/true, &skeys, &svals, s,
-                     hist_ready != 0));
+  bool sorted = false;
+  if (hybrid)
+    RT_TRY(launch_sort63_hybrid((uint64_t*)keys, n, ws, k32, long_run, &skeys, &svals, &sorted, s));
+  if (!sorted)
+    RT_TRY(launch_sort(keys, n, h->key_bits, ws, /*iota_payload=*/true, &skeys, &svals, s,
+                       hist_ready != 0));
   RT_TRY(mark(3));
   RT_TRY(mark(4));  // A4 is fused into the bottom-up pass: the topology stage is empty
   RT_TRY(launch_build_tree(tris, svals, skeys, h->key_bits, n, (uint32_t*)flags_buf, h->nodes,
@@ -1214,6 +1228,7 @@ extern "C" int rt_set_param(const char* name, int64_t value) {
   Params& p = params();
   if (!strcmp(name, "sort.variant")) p.sort_variant = (int)value;
   else if (!strcmp(name, "sort.bits")) p.sort_bits = (int)value;
+  else if (!strcmp(name, "sort.hybrid")) p.sort_hybrid = (int)value;
   else if (!strcmp(name, "trace.blocks_per_sm")) p.trace_blocks_per_sm = (int)value;
   else if (!strcmp(name, "trace.variant")) p.trace_variant = (int)value;
   else if (!strcmp(name, "trace.wide")) p.trace_wide = (int)value;

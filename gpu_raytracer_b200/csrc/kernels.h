@@ -110,6 +110,15 @@ int launch_sort(void* keys, uint64_t n, uint32_t key_bits, const SortWorkspace& 
                 bool iota_payload, void** keys_out, uint32_t** vals_out, cudaStream_t s,
                 bool first_hist_ready = false, int max_passes = 0);
 
+// 63-bit keys with an iota payload, hybrid order (radix_sort.cu): three packed passes on the
+// top 30 bits, then ranks inside the runs of equal top bits.  ws must hold BOTH layouts
+// (rec_a, rec_b, vals for the 30-bit passes; keys_alt, vals_alt for the result), chunk_hist
+// sized for either key width; k32: n u32; long_run: one u32.  *used = false when a run was
+// too long: nothing of k64 has changed and the caller runs launch_sort on all 63 bits.
+int launch_sort63_hybrid(uint64_t* k64, uint64_t n, const SortWorkspace& ws, uint32_t* k32,
+                         uint32_t* long_run, void** keys_out, uint32_t** vals_out, bool* used,
+                         cudaStream_t s);
+
 // A4 + A5 fused: topology, triangle reorder, boxes (refit.cu).  keys: the sorted Morton
 // codes; flags: n-1 u32, zeroed by the launcher.  Writes nodes (indexed by split
 // position), sorted tris, header box and root id.
@@ -195,6 +204,7 @@ int launch_ray_keys(const float4* rays, uint64_t n, const float* box, uint32_t* 
 struct Params {
   int sort_variant = 0;
   int sort_bits = 0;            // 0 = default digit width (sort_plan)
+  int sort_hybrid = 0;          // 63-bit builds: 1 = top-30 LSD + ranks inside runs
   int trace_blocks_per_sm = 0;  // 0 = kernel default
   int trace_variant = 1;        // 0 = plain while-while, 1 = dynamic fetch + voted leaf loop
   int trace_chunk = 0, trace_refill_min = 0, trace_leaf_min = 0;  // 0 = defaults

@@ -615,4 +615,118 @@ int launch_sort(void* keys, uint64_t n, uint32_t key_bits, const SortWorkspace& 
   return 0;
 }
 
+
+// ---- 63-bit keys, hybrid order: LSD on the top 30 bits, ranks inside the runs -----------
+// Seven 12-byte passes are what the 63-bit sort costs (8.0 ms at 100M).  The top 30 bits of
+// a 63-bit Morton code are the 30-bit code, which the packed-record path sorts in three
+// 8-byte passes; what is left is to order, inside every run of equal top bits, by the full
+// key (the index order inside a run is already ascending, LSD being stable).  Runs are short
+// where a scene needs 63 bits at all (terrain 100M: median 12, longest 98), so every element
+// counts the members of its run that go before it.  A scene with a run longer than kMaxRun
+// (e.g. all centroids equal) takes the seven-pass sort instead: same result either way.
+constexpr uint32_t kMaxRun = 256;
+constexpr int kRankThreads = 256;
+
+__global__ void __launch_bounds__(256)
+hi30_kernel(const uint64_t* __restrict__ k64, uint32_t n, uint32_t* __restrict__ k32) {
+  pdl_enter();
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) k32[i] = (uint32_t)(k64[i] >> 33);
+}
+
+// keys into top-30 order; flags a run longer than kMaxRun (sorted: equal ends = equal run)
+__global__ void __launch_bounds__(256)
+gather_runs_kernel(const uint64_t* __restrict__ k64, const uint32_t* __restrict__ idx,
+                   const uint32_t* __restrict__ k32s, uint32_t n, uint64_t* __restrict__ k64g,
+                   uint32_t* __restrict__ long_run) {
+  pdl_enter();
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  k64g[i] = k64[idx[i]];
+  if (i + kMaxRun < n && k32s[i] == k32s[i + kMaxRun]) *long_run = 1u;
+}
+
+// One thread per element; the CTA's elements and kMaxRun neighbours on either side sit in
+// shared memory.  Position inside the run = members with a smaller key, or an equal key
+// and an earlier place.
+__global__ void __launch_bounds__(kRankThreads)
+rank_runs_kernel(const uint64_t* __restrict__ k64g, const uint32_t* __restrict__ idx,
+                 const uint32_t* __restrict__ k32s, uint32_t n, uint64_t* __restrict__ keys_out,
+                 uint32_t* __restrict__ vals_out) {
+  constexpr int kSpan = kRankThreads + 2 * (int)kMaxRun;
+  __shared__ uint64_t s_key[kSpan];
+  __shared__ uint32_t s_top[kSpan];
+  pdl_enter();
+  const long long base = (long long)blockIdx.x * kRankThreads - (long long)kMaxRun;
+  for (int t = threadIdx.x; t < kSpan; t += kRankThreads) {
+    const long long g = base + t;
+    const bool ok = g >= 0 && g < (long long)n;
+    s_top[t] = ok ? k32s[g] : 0xFFFFFFFFu;  // never equal to a 30-bit value
+    s_key[t] = ok ? k64g[g] : 0ull;
+  }
+  __syncthreads();
+  const uint32_t i = blockIdx.x * kRankThreads + threadIdx.x;
+  if (i >= n) return;
+  const int c = (int)threadIdx.x + (int)kMaxRun;
+  const uint32_t top = s_top[c];
+  // the run's ends by bisection over the sorted top bits (a run is at most kMaxRun long, so
+  // both ends lie within kMaxRun of c): the same nine steps for every lane, where walking to
+  // the ends costs every warp its longest run
+  const int v_lo = (base < 0) ? (int)(-base) : 0;                                   // first valid slot
+  const int v_hi = (base + kSpan > (long long)n) ? (int)((long long)n - base) : kSpan;  // one past the last
+  int lo = max(c - (int)kMaxRun, v_lo), len = c - lo;  // first slot in [lo, c] with s_top >= top
+  while (len > 0) {
+    const int half = len >> 1;
+    const bool less = s_top[lo + half] < top;
+    lo = less ? lo + half + 1 : lo;
+    len = less ? len - half - 1 : half;
+  }
+  int hi = c + 1;
+  len = min(c + 1 + (int)kMaxRun, v_hi) - hi;          // first slot in [c+1, ..) with s_top > top
+  while (len > 0) {
+    const int half = len >> 1;
+    const bool le = s_top[hi + half] <= top;
+    hi = le ? hi + half + 1 : hi;
+    len = le ? len - half - 1 : half;
+  }
+  const uint64_t mine = s_key[c];
+  uint32_t before = 0;
+  for (int j = lo; j < hi; ++j) {
+    const uint64_t k = s_key[j];
+    before += (k < mine || (k == mine && j < c)) ? 1u : 0u;
+  }
+  const uint32_t dst = i - (uint32_t)(c - lo) + before;
+  keys_out[dst] = mine;
+  vals_out[dst] = idx[i];
+}
+
+int launch_sort63_hybrid(uint64_t* k64, uint64_t n, const SortWorkspace& ws, uint32_t* k32,
+                         uint32_t* long_run, void** keys_out, uint32_t** vals_out, bool* used,
+                         cudaStream_t s) {
+  *used = false;
+  if (n < 2 || n > ((1ull << 30) - 1)) return 0;
+  const unsigned grid = (unsigned)((n + 255) / 256);
+  RT_CUDA(cudaMemsetAsync(long_run, 0, 4, s));
+  RT_CUDA(launch_pdl(hi30_kernel, grid, 256, 0, s, (const uint64_t*)k64, (uint32_t)n, k32));
+  RT_LAUNCHED();
+  void* sk32 = nullptr;
+  uint32_t* sidx = nullptr;
+  RT_TRY(launch_sort(k32, n, 30, ws, /*iota_payload=*/true, &sk32, &sidx, s, false));
+  RT_CUDA(launch_pdl(gather_runs_kernel, grid, 256, 0, s, (const uint64_t*)k64, (const uint32_t*)sidx,
+                     (const uint32_t*)sk32, (uint32_t)n, (uint64_t*)ws.keys_alt, long_run));
+  RT_LAUNCHED();
+  uint32_t flag = 0;
+  RT_CUDA(cudaMemcpyAsync(&flag, long_run, 4, cudaMemcpyDeviceToHost, s));
+  RT_CUDA(cudaStreamSynchronize(s));
+  if (flag) return 0;  // a long run: the caller sorts all 63 bits (k64 is untouched)
+  RT_CUDA(launch_pdl(rank_runs_kernel, (unsigned)((n + kRankThreads - 1) / kRankThreads), kRankThreads,
+                     0, s, (const uint64_t*)ws.keys_alt, (const uint32_t*)sidx, (const uint32_t*)sk32,
+                     (uint32_t)n, k64, ws.vals_alt));
+  RT_LAUNCHED();
+  *keys_out = k64;
+  *vals_out = ws.vals_alt;
+  *used = true;
+  return 0;
+}
+
 }  // namespace rt

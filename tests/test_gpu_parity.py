@@ -456,3 +456,23 @@ def test_reordered_trace_is_bit_identical(rt, oracle, name):
         # host buffers: the flag is accepted and ignored
         got = gb.trace(rays, rt.RT_TRACE_REORDER)
         assert np.array_equal(bits(np.asarray(got)), bits(ob.trace(rays, 0)))
+
+
+def test_hybrid_63_bit_sort(rt, oracle):
+    """`sort.hybrid`: 63-bit builds sort the top 30 bits with the packed passes and rank
+    inside the runs of equal top bits; long runs (all centroids equal) fall back to the
+    seven-pass sort.  Either way the oracle's order, tree and boxes."""
+    rt.set_param("sort.hybrid", 1)
+    try:
+        for name in SCENES:
+            kind, p0, p1, seed = SCENES[name]
+            _build_and_compare(rt, oracle, oracle.gen_scene(kind, p0, p1, seed), 63, timings=False)
+        for n in (2, 3, 255, 256, 257, 5121, 40001, 300000):
+            _build_and_compare(rt, oracle, oracle.gen_scene(oracle.SCENE_SOUP, n, 0, seed=n), 63)
+        base = oracle.gen_scene(oracle.SCENE_SOUP, 300, 0, seed=2)
+        _build_and_compare(rt, oracle, np.repeat(base, 40, axis=0), 63)       # runs of 40
+        _build_and_compare(rt, oracle, np.repeat(base[:7], 256, axis=0), 63)  # runs of exactly 256
+        _build_and_compare(rt, oracle, np.repeat(base[:7], 257, axis=0), 63)  # 257: falls back
+        _build_and_compare(rt, oracle, np.repeat(base[:1], 5000, axis=0), 63)  # one run: falls back
+    finally:
+        rt.set_param("sort.hybrid", 0)
