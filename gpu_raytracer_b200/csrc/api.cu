@@ -350,21 +350,23 @@ int build_impl(rt_bvh* h, const float* tris_in, uint32_t flags, cudaStream_t s) 
   // programmatic dependents of each other (common.cuh pdl_enter)
   RT_CUDA(cudaMemsetAsync(ws.hist, 0, sort_hist_words(h->key_bits) * sizeof(uint32_t), s));
   RT_TRY(prepare_build_tree(n, (uint32_t*)flags_buf, queue_buf, s));
+  if (hybrid) RT_CUDA(cudaMemsetAsync(long_run, 0, 4, s));
   RT_TRY(mark(0));
   RT_TRY(launch_bounds(tris, n, (uint32_t*)bkeys, centroids, s));
   RT_TRY(mark(1));
   int hist_ready = 0;
-  RT_TRY(launch_morton(centroids, n, (const uint32_t*)bkeys, h->key_bits, keys,
-                       hybrid ? nullptr : ws.chunk_hist, ws.hist, &hist_ready, s));
+  RT_TRY(launch_morton(centroids, n, (const uint32_t*)bkeys, h->key_bits, keys, ws.chunk_hist,
+                       ws.hist, &hist_ready, s, hybrid ? k32 : nullptr));
   RT_TRY(mark(2));
   void* skeys = nullptr;
   uint32_t* svals = nullptr;
   bool sorted = false;
   if (hybrid)
-    RT_TRY(launch_sort63_hybrid((uint64_t*)keys, n, ws, k32, long_run, &skeys, &svals, &sorted, s));
+    RT_TRY(launch_sort63_hybrid((uint64_t*)keys, n, ws, k32, long_run, &skeys, &svals, &sorted, s,
+                                hist_ready == 2));
   if (!sorted)
     RT_TRY(launch_sort(keys, n, h->key_bits, ws, /*iota_payload=*/true, &skeys, &svals, s,
-                       hist_ready != 0));
+                       hist_ready == 1));
   RT_TRY(mark(3));
   RT_TRY(mark(4));  // A4 is fused into the bottom-up pass: the topology stage is empty
   RT_TRY(launch_build_tree(tris, svals, skeys, h->key_bits, n, (uint32_t*)flags_buf, h->nodes,

@@ -82,7 +82,8 @@ ChunkGeom sort_geometry(uint64_t n, uint32_t key_bits);
 // (chunk_hist [chunks][bins]) and bin totals (totals [bins], zeroed by the caller); returns
 // 1 in *fused when it did (default digit widths only), else 0 and the sort histograms itself.
 int launch_morton(const float* centroids, uint64_t n, const uint32_t* bounds_keys, uint32_t key_bits,
-                  void* keys, uint32_t* chunk_hist, uint32_t* totals, int* fused, cudaStream_t s);
+                  void* keys, uint32_t* chunk_hist, uint32_t* totals, int* fused, cudaStream_t s,
+                  uint32_t* k32_hybrid = nullptr);  // 63-bit hybrid sort: *fused = 2, see morton.cu
 
 struct SortWorkspace {
   void* keys_alt = nullptr;     // 63-bit keys: n keys, ping-pong partner of the input
@@ -117,7 +118,7 @@ int launch_sort(void* keys, uint64_t n, uint32_t key_bits, const SortWorkspace& 
 // too long: nothing of k64 has changed and the caller runs launch_sort on all 63 bits.
 int launch_sort63_hybrid(uint64_t* k64, uint64_t n, const SortWorkspace& ws, uint32_t* k32,
                          uint32_t* long_run, void** keys_out, uint32_t** vals_out, bool* used,
-                         cudaStream_t s);
+                         cudaStream_t s, bool k32_ready = false);
 
 // A4 + A5 fused: topology, triangle reorder, boxes (refit.cu).  keys: the sorted Morton
 // codes; flags: n-1 u32, zeroed by the launcher.  Writes nodes (indexed by split

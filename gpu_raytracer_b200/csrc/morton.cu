@@ -151,12 +151,14 @@ morton_kernel(const float* __restrict__ cx, const float* __restrict__ cy,
 // the lowest digit of the keys it produces: the sort's first chunk_hist_kernel, and its read
 // of every key, disappear.
 constexpr int kMortonHistThreads = 1024;
-template <int KEY_BITS, int BITS>
+// HYB (63-bit keys, hybrid sort order): also stores the top 30 bits of every key as the
+// 32-bit key of the packed passes and counts THEIR lowest digit, on the 30-bit geometry.
+template <int KEY_BITS, int BITS, bool HYB = false>
 __global__ void __launch_bounds__(kMortonHistThreads)
 morton_hist_kernel(const float* __restrict__ cx, const float* __restrict__ cy,
                    const float* __restrict__ cz, ChunkGeom g, const uint32_t* __restrict__ bkeys,
                    void* __restrict__ keys_out, uint32_t* __restrict__ chunk_hist,
-                   uint32_t* __restrict__ totals) {
+                   uint32_t* __restrict__ totals, uint32_t* __restrict__ k32) {
   pdl_enter();
   constexpr int kBins = 1 << BITS;
   __shared__ uint32_t sh[kBins];
@@ -185,6 +187,10 @@ morton_hist_kernel(const float* __restrict__ cx, const float* __restrict__ cy,
         if (KEY_BITS == 30) reinterpret_cast<uint32_t*>(keys_out)[t] = (uint32_t)key;
         else reinterpret_cast<uint64_t*>(keys_out)[t] = key;
         d = (uint32_t)key & (kBins - 1);
+        if (HYB) {
+          k32[t] = (uint32_t)(key >> 33);
+          d = (uint32_t)(key >> 33) & (kBins - 1);
+        }
       }
       // coherent meshes put one cell, hence one digit, in a whole warp: count it once
       const uint32_t d0 = __shfl_sync(0xFFFFFFFFu, d, 0);
@@ -227,20 +233,29 @@ int launch_bounds(const float4* tris, uint64_t n, uint32_t* bounds_keys, float* 
 }
 
 int launch_morton(const float* centroids, uint64_t n, const uint32_t* bounds_keys, uint32_t key_bits,
-                  void* keys, uint32_t* chunk_hist, uint32_t* totals, int* fused, cudaStream_t s) {
+                  void* keys, uint32_t* chunk_hist, uint32_t* totals, int* fused, cudaStream_t s,
+                  uint32_t* k32_hybrid) {
   if (fused) *fused = 0;
   if (n == 0) return 0;
   const float *cx = centroids, *cy = centroids + n, *cz = centroids + 2 * n;
+  if (k32_hybrid && key_bits == 63 && chunk_hist && totals && fused && sort_plan(30).bits == 10) {
+    const ChunkGeom g = sort_geometry(n, 30);
+    RT_CUDA(launch_pdl(morton_hist_kernel<63, 10, true>, g.chunks, kMortonHistThreads, 0, s, cx, cy,
+                       cz, g, bounds_keys, keys, chunk_hist, totals, k32_hybrid));
+    RT_LAUNCHED();
+    *fused = 2;  // keys, their top 30 bits and the first histogram of the packed passes
+    return 0;
+  }
   const SortPlan plan = sort_plan(key_bits);
   const bool fuse = chunk_hist && totals && fused && plan.bits == (key_bits == 30 ? 10 : 9);
   if (fuse) {
     const ChunkGeom g = sort_geometry(n, key_bits);
     if (key_bits == 30)
       RT_CUDA(launch_pdl(morton_hist_kernel<30, 10>, g.chunks, kMortonHistThreads, 0, s, cx, cy, cz, g,
-                         bounds_keys, keys, chunk_hist, totals));
+                         bounds_keys, keys, chunk_hist, totals, (uint32_t*)nullptr));
     else
       RT_CUDA(launch_pdl(morton_hist_kernel<63, 9>, g.chunks, kMortonHistThreads, 0, s, cx, cy, cz, g,
-                         bounds_keys, keys, chunk_hist, totals));
+                         bounds_keys, keys, chunk_hist, totals, (uint32_t*)nullptr));
     RT_LAUNCHED();
     *fused = 1;
     return 0;

@@ -702,16 +702,20 @@ rank_runs_kernel(const uint64_t* __restrict__ k64g, const uint32_t* __restrict__
 
 int launch_sort63_hybrid(uint64_t* k64, uint64_t n, const SortWorkspace& ws, uint32_t* k32,
                          uint32_t* long_run, void** keys_out, uint32_t** vals_out, bool* used,
-                         cudaStream_t s) {
+                         cudaStream_t s, bool k32_ready) {
   *used = false;
   if (n < 2 || n > ((1ull << 30) - 1)) return 0;
   const unsigned grid = (unsigned)((n + 255) / 256);
-  RT_CUDA(cudaMemsetAsync(long_run, 0, 4, s));
-  RT_CUDA(launch_pdl(hi30_kernel, grid, 256, 0, s, (const uint64_t*)k64, (uint32_t)n, k32));
-  RT_LAUNCHED();
+  // k32_ready: the Morton kernel stored the top bits and counted their first digit; long_run
+  // was zeroed by the caller before the first kernel
+  if (!k32_ready) {
+    RT_CUDA(cudaMemsetAsync(long_run, 0, 4, s));
+    RT_CUDA(launch_pdl(hi30_kernel, grid, 256, 0, s, (const uint64_t*)k64, (uint32_t)n, k32));
+    RT_LAUNCHED();
+  }
   void* sk32 = nullptr;
   uint32_t* sidx = nullptr;
-  RT_TRY(launch_sort(k32, n, 30, ws, /*iota_payload=*/true, &sk32, &sidx, s, false));
+  RT_TRY(launch_sort(k32, n, 30, ws, /*iota_payload=*/true, &sk32, &sidx, s, k32_ready));
   RT_CUDA(launch_pdl(gather_runs_kernel, grid, 256, 0, s, (const uint64_t*)k64, (const uint32_t*)sidx,
                      (const uint32_t*)sk32, (uint32_t)n, (uint64_t*)ws.keys_alt, long_run));
   RT_LAUNCHED();
