@@ -205,7 +205,7 @@ int launch_ray_keys(const float4* rays, uint64_t n, const float* box, uint32_t* 
 struct Params {
   int sort_variant = 0;
   int sort_bits = 0;            // 0 = default digit width (sort_plan)
-  int sort_hybrid = 0;          // 63-bit builds: 1 = top-30 LSD + ranks inside runs
+  int sort_hybrid = 1;          // 63-bit builds: 1 = top-30 LSD + ranks inside runs (default), 0 = 7 passes
   int trace_blocks_per_sm = 0;  // 0 = kernel default
   int trace_variant = 1;        // 0 = plain while-while, 1 = dynamic fetch + voted leaf loop
   int trace_chunk = 0, trace_refill_min = 0, trace_leaf_min = 0;  // 0 = defaults

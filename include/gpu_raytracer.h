@@ -237,7 +237,8 @@ RT_API uint64_t rt_kernel_launches(void);
  * "trace.wide", "wide.leaf_max", "trace.streamed" (0 = always stage host batches),
  * "trace.stage_chunk", "trace.zero_copy", "trace.sh_stack" (0 | 8 | 16 | 24 stack levels in
  * shared memory), "build.pdl" (1 = build kernels launched as programmatic dependents, the
- * default).  Returns RT_ERR_INVALID for an unknown name. */
+ * default), "sort.hybrid" (63-bit builds: 1 = packed passes on the top 30 bits, then ranks inside
+ * runs of equal top bits, the default; 0 = seven passes over all 63 bits; same order either way).  Returns RT_ERR_INVALID for an unknown name. */
 RT_API int rt_set_param(const char* name, int64_t value);
 /* sorts n (key,value) pairs already on the device with the build's radix sort;
  * used by tests and the sort micro-benchmark.  key_bits 30 -> u32 keys, 63 ->

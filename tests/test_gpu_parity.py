@@ -474,5 +474,11 @@ def test_hybrid_63_bit_sort(rt, oracle):
         _build_and_compare(rt, oracle, np.repeat(base[:7], 256, axis=0), 63)  # runs of exactly 256
         _build_and_compare(rt, oracle, np.repeat(base[:7], 257, axis=0), 63)  # 257: falls back
         _build_and_compare(rt, oracle, np.repeat(base[:1], 5000, axis=0), 63)  # one run: falls back
-    finally:
+        # and the plain seven-pass order, which the default no longer exercises
         rt.set_param("sort.hybrid", 0)
+        for name in SCENES:
+            kind, p0, p1, seed = SCENES[name]
+            _build_and_compare(rt, oracle, oracle.gen_scene(kind, p0, p1, seed), 63, timings=False)
+        _build_and_compare(rt, oracle, oracle.gen_scene(oracle.SCENE_SOUP, 40001, 0, seed=9), 63)
+    finally:
+        rt.set_param("sort.hybrid", 1)

@@ -34,6 +34,6 @@ for name in sys.argv[1:] or ["terrain100m", "flake10m", "soup1m"]:
         print(json.dumps(dict(scene=name, hybrid=hyb, sort_ms=round(best["sort"], 4),
                               tree_ms=round(best["topology"] + best["refit"], 4),
                               total_ms=round(best["total"], 4), same_as_first=same)), flush=True)
-    g.set_param("sort.hybrid", 0)
+    g.set_param("sort.hybrid", 1)
     del tris, ref
     torch.cuda.empty_cache()
