@@ -690,10 +690,21 @@ rank_runs_kernel(const uint64_t* __restrict__ k64g, const uint32_t* __restrict__
     len = le ? len - half - 1 : half;
   }
   const uint64_t mine = s_key[c];
+  // (key, place) < (mine, c) as the borrow of one 96-bit subtraction: branch-free, five
+  // instructions per member where two 64-bit compares and the tie rule took eight
+  const uint32_t mlo = (uint32_t)mine, mhi = (uint32_t)(mine >> 32);
   uint32_t before = 0;
+#pragma unroll 4
   for (int j = lo; j < hi; ++j) {
     const uint64_t k = s_key[j];
-    before += (k < mine || (k == mine && j < c)) ? 1u : 0u;
+    uint32_t t0, t1, t2, less;
+    asm("sub.cc.u32 %0, %4, %5;\n\t"
+        "subc.cc.u32 %1, %6, %7;\n\t"
+        "subc.cc.u32 %2, %8, %9;\n\t"
+        "subc.u32 %3, 0, 0;"
+        : "=r"(t0), "=r"(t1), "=r"(t2), "=r"(less)
+        : "r"((uint32_t)j), "r"((uint32_t)c), "r"((uint32_t)k), "r"(mlo), "r"((uint32_t)(k >> 32)), "r"(mhi));
+    before -= less;  // less = 0xFFFFFFFF when (k, j) < (mine, c)
   }
   const uint32_t dst = i - (uint32_t)(c - lo) + before;
   keys_out[dst] = mine;
