@@ -654,41 +654,38 @@ rank_runs_kernel(const uint64_t* __restrict__ k64g, const uint32_t* __restrict__
                  const uint32_t* __restrict__ k32s, uint32_t n, uint64_t* __restrict__ keys_out,
                  uint32_t* __restrict__ vals_out) {
   constexpr int kSpan = kRankThreads + 2 * (int)kMaxRun;
+  constexpr int kWords = kSpan / 32;
   __shared__ uint64_t s_key[kSpan];
-  __shared__ uint32_t s_top[kSpan];
+  __shared__ uint32_t s_head[kWords];  // bit = this slot starts a run (or lies outside the array)
   pdl_enter();
   const long long base = (long long)blockIdx.x * kRankThreads - (long long)kMaxRun;
-  for (int t = threadIdx.x; t < kSpan; t += kRankThreads) {
+  for (int t = threadIdx.x; t < kSpan; t += kRankThreads) {  // kSpan is a multiple of the CTA: whole warps
     const long long g = base + t;
     const bool ok = g >= 0 && g < (long long)n;
-    s_top[t] = ok ? k32s[g] : 0xFFFFFFFFu;  // never equal to a 30-bit value
-    s_key[t] = ok ? k64g[g] : 0ull;
+    bool head = true;
+    if (ok) {
+      s_key[t] = k64g[g];
+      head = (g == 0) || (k32s[g - 1] != k32s[g]);
+    }
+    const uint32_t word = __ballot_sync(0xFFFFFFFFu, head);
+    if ((threadIdx.x & 31) == 0) s_head[t >> 5] = word;
   }
   __syncthreads();
   const uint32_t i = blockIdx.x * kRankThreads + threadIdx.x;
   if (i >= n) return;
+  // the run's ends from the head bits: the nearest one at or before the slot, the next one
+  // after it.  A run is at most kMaxRun long, so both lie inside the span; one or two words
+  // each, where bisecting the top bits took nine dependent steps per end.
   const int c = (int)threadIdx.x + (int)kMaxRun;
-  const uint32_t top = s_top[c];
-  // the run's ends by bisection over the sorted top bits (a run is at most kMaxRun long, so
-  // both ends lie within kMaxRun of c): the same nine steps for every lane, where walking to
-  // the ends costs every warp its longest run
-  const int v_lo = (base < 0) ? (int)(-base) : 0;                                   // first valid slot
-  const int v_hi = (base + kSpan > (long long)n) ? (int)((long long)n - base) : kSpan;  // one past the last
-  int lo = max(c - (int)kMaxRun, v_lo), len = c - lo;  // first slot in [lo, c] with s_top >= top
-  while (len > 0) {
-    const int half = len >> 1;
-    const bool less = s_top[lo + half] < top;
-    lo = less ? lo + half + 1 : lo;
-    len = less ? len - half - 1 : half;
-  }
-  int hi = c + 1;
-  len = min(c + 1 + (int)kMaxRun, v_hi) - hi;          // first slot in [c+1, ..) with s_top > top
-  while (len > 0) {
-    const int half = len >> 1;
-    const bool le = s_top[hi + half] <= top;
-    hi = le ? hi + half + 1 : hi;
-    len = le ? len - half - 1 : half;
-  }
+  int w = c >> 5;
+  const int bit = c & 31;
+  uint32_t m = s_head[w] & (0xFFFFFFFFu >> (31 - bit));
+  while (m == 0u) m = s_head[--w];
+  const int lo = (w << 5) + 31 - __clz((int)m);
+  w = c >> 5;
+  m = (bit == 31) ? 0u : (s_head[w] & (0xFFFFFFFFu << (bit + 1)));
+  while (m == 0u && w + 1 < kWords) m = s_head[++w];
+  const int hi = m ? (w << 5) + __ffs((int)m) - 1 : kSpan;
   const uint64_t mine = s_key[c];
   // (key, place) < (mine, c) as the borrow of one 96-bit subtraction: branch-free, five
   // instructions per member where two 64-bit compares and the tie rule took eight
