@@ -16,4 +16,9 @@ ncu -i /tmp/${tag}_trace.ncu-rep --page raw --csv > $out/${tag}_ncu_trace_raw.cs
 timeout 1500 ncu --set full --clock-control none --import-source on -k regex:'bounds_kernel|morton|chunk_|scatter_kernel|build_walk|build_top' -c 26 -f -o /tmp/${tag}_build \
   python tools/prof_build.py flake10m 30 2 > $out/${tag}_ncu_build.log 2>&1; echo "ncu build rc=$?"
 ncu -i /tmp/${tag}_build.ncu-rep --page raw --csv > $out/${tag}_ncu_build_raw.csv 2>/dev/null
+# configs 4 and 5 of BASELINE.json (100M-triangle builds with 63- and 30-bit keys; 1e9 random rays,
+# plain and with RT_TRACE_REORDER)
+timeout 900 python tools/run_configs.py 4 > $out/${tag}_config4_terrain100m.jsonl 2> $out/${tag}_config4.err; echo "config 4 rc=$?"
+timeout 900 python tools/run_configs.py 5 1e9 > $out/${tag}_config5_random1b_n1.jsonl 2> $out/${tag}_config5.err; echo "config 5 rc=$?"
+timeout 900 python tools/run_configs.py 5 1e9 reorder >> $out/${tag}_config5_random1b_n1.jsonl 2>> $out/${tag}_config5.err; echo "config 5 reorder rc=$?"
 ls -la $out | tail -20
