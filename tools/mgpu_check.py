@@ -30,6 +30,10 @@ def main():
         local = torch.cat(parts)
         counts = [sharding.shard_range(n_rays, r, world)[1] for r in range(world)]
         assert local.shape[0] == counts[rank]
+        # the same shard in one call with RT_TRACE_REORDER: same bytes
+        f0, c0 = sharding.shard_range(n_rays, rank, world)
+        again = bvh.trace(g.gen_random_rays(box, 4, f0, c0), g.RT_TRACE_REORDER)
+        assert torch.equal(again.view(torch.int32), local.view(torch.int32)), "reordered shard differs"
         pad = torch.zeros((max(counts), 4), dtype=torch.float32, device="cuda")
         pad[: local.shape[0]] = local
         outs = [torch.empty_like(pad) for _ in range(world)]
