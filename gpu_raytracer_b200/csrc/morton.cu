@@ -69,15 +69,11 @@ bounds_kernel(const float4* __restrict__ tris, uint64_t n, uint32_t* __restrict_
   }
   __syncthreads();
   if (threadIdx.x < 3) {
-    atomicMin(&out[threadIdx.x], s_mn[threadIdx.x]);
+    // the minimum is kept complemented, so both halves are maxima and start from zero:
+    // one memset with the build's other memsets instead of an initialising kernel
+    atomicMax(&out[threadIdx.x], ~s_mn[threadIdx.x]);
     atomicMax(&out[3 + threadIdx.x], s_mx[threadIdx.x]);
   }
-}
-
-__global__ void init_bounds_kernel(uint32_t* out) {
-  pdl_enter();
-  if (threadIdx.x < 3) out[threadIdx.x] = 0xFFFFFFFFu;
-  else if (threadIdx.x < 6) out[threadIdx.x] = 0u;
 }
 
 __device__ __forceinline__ uint32_t expand10(uint32_t v) {
@@ -116,7 +112,7 @@ __device__ __forceinline__ Quant load_quant(const uint32_t* __restrict__ bkeys) 
   Quant q;
 #pragma unroll
   for (int k = 0; k < 3; ++k) {
-    q.smin[k] = ord_unkey(bkeys[k]);
+    q.smin[k] = ord_unkey(~bkeys[k]);  // stored complemented (bounds_kernel)
     const float ext = ord_unkey(bkeys[3 + k]) - q.smin[k];
     q.scale[k] = (ext > 0.0f) ? (kCells / ext) : 0.0f;
   }
@@ -221,8 +217,7 @@ inline unsigned persistent_grid(uint64_t items, int threads, int blocks_per_sm) 
 
 int launch_bounds(const float4* tris, uint64_t n, uint32_t* bounds_keys, float* centroids,
                   cudaStream_t s) {
-  RT_CUDA(launch_pdl(init_bounds_kernel, 1, 32, 0, s, bounds_keys));
-  RT_LAUNCHED();
+  RT_CUDA(cudaMemsetAsync(bounds_keys, 0, 6 * sizeof(uint32_t), s));
   if (n == 0) return 0;
   // 2 triangles per thread per trip: size the grid for the unrolled loop
   unsigned grid = persistent_grid((n + 1) / 2, kBoundsThreads, 8);
