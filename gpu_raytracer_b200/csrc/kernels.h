@@ -209,7 +209,7 @@ struct Params {
   int trace_blocks_per_sm = 0;  // 0 = kernel default
   int trace_variant = 1;        // 0 = plain while-while, 1 = dynamic fetch + voted leaf loop
   int trace_chunk = 0, trace_refill_min = 0, trace_leaf_min = 0;  // 0 = defaults
-  int trace_sh_stack = 0;       // stack levels kept in shared memory (0, 8, 16, 24)
+  int trace_sh_stack = -1;      // stack levels kept in shared memory (0, 8, 16, 24); -1 = 8 with RT_TRACE_REORDER, else 0
   int trace_wide = 1;           // 1 = use the BVH4 of handles built with RT_BUILD_WIDE4
   int wide_leaf_max = kWideLeafDefault;  // triangles per BVH4 leaf (1..4), read when collapsing
   // bit 0: kernels read pinned host rays in place, bit 1: store hits to pinned host in

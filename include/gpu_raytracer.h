@@ -236,7 +236,7 @@ RT_API uint64_t rt_kernel_launches(void);
  * "trace.variant", "trace.blocks_per_sm", "trace.chunk", "trace.refill_min", "trace.leaf_min",
  * "trace.wide", "wide.leaf_max", "trace.streamed" (0 = always stage host batches),
  * "trace.stage_chunk", "trace.zero_copy", "trace.sh_stack" (0 | 8 | 16 | 24 stack levels in
- * shared memory), "build.pdl" (1 = build kernels launched as programmatic dependents, the
+ * shared memory; -1, the default: 8 for RT_TRACE_REORDER launches, else 0), "build.pdl" (1 = build kernels launched as programmatic dependents, the
  * default), "sort.hybrid" (63-bit builds: 1 = packed passes on the top 30 bits, then ranks inside
  * runs of equal top bits, the default; 0 = seven passes over all 63 bits; same order either way).  Returns RT_ERR_INVALID for an unknown name. */
 RT_API int rt_set_param(const char* name, int64_t value);

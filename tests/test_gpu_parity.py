@@ -430,7 +430,7 @@ def test_shared_memory_stack_top(rt, oracle, levels):
             got, want = _trace_both(rt, oracle, tris, rays, flags)
             assert np.array_equal(bits(got), bits(want)), (levels, flags)
     finally:
-        rt.set_param("trace.sh_stack", 0)
+        rt.set_param("trace.sh_stack", -1)
 
 
 @pytest.mark.parametrize("name", ["soup20k", "flake"])

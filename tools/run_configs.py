@@ -64,6 +64,8 @@ def config4():
 
 def config5(total, reorder=False):
     flags = g.RT_TRACE_REORDER if reorder else 0
+    if os.environ.get("RT_SH_STACK"):
+        g.set_param("trace.sh_stack", int(os.environ["RT_SH_STACK"]))
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
     if world > 1:
         import torch.distributed as dist
