@@ -64,6 +64,9 @@ def config4():
 
 def config5(total, reorder=False):
     flags = g.RT_TRACE_REORDER if reorder else 0
+    for env, name in (("RT_LEAF_MIN", "trace.leaf_min"), ("RT_REFILL_MIN", "trace.refill_min"), ("RT_CHUNK", "trace.chunk")):
+        if os.environ.get(env):
+            g.set_param(name, int(os.environ[env]))
     if os.environ.get("RT_SH_STACK"):
         g.set_param("trace.sh_stack", int(os.environ["RT_SH_STACK"]))
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
