@@ -17,6 +17,7 @@ RT_TRACE_CLOSEST, RT_TRACE_ANY, RT_TRACE_WATERTIGHT, RT_TRACE_REORDER = 0, 1, 2,
 RT_ANY_HIT_PRIM = 0x7FFFFFFF
 RT_BUILD_KEEP_KEYS, RT_BUILD_TIMINGS, RT_BUILD_WIDE4 = 1, 2, 4
 RT_SCENE_CORNELL, RT_SCENE_SOUP, RT_SCENE_SPHEREFLAKE, RT_SCENE_TERRAIN = 0, 1, 2, 3
+RT_MULTI_REDUNDANT, RT_MULTI_BROADCAST = 0, 1
 RT_STAGE_NAMES = ("bounds", "morton", "sort", "topology", "refit", "total", "wide")
 RT_MAX_TRIS = (1 << 30) - 1
 
@@ -67,6 +68,14 @@ SIGNATURES = {
     "rt_kernel_launches": (_u64, []),
     "rt_set_param": (_i32, [C.c_char_p, C.c_int64]),
     "rt_sort_pairs": (_i32, [_vp, _vp, _u64, _u32, _vp]),
+    "rt_trim": (_i32, [_i32]),
+    "trace_camera": (_i32, [_vp, _vp, _u32, _u32, _u64, _u64, _u32, _vp]),
+    "rt_shard_range": (_i32, [_u64, _i32, _i32, C.POINTER(_u64), C.POINTER(_u64)]),
+    "build_bvh_multi": (_i32, [_vp, _u64, C.POINTER(BuildOpts), C.POINTER(_i32), _i32, _i32,
+                               C.POINTER(_vp)]),
+    "trace_rays_sharded": (_i32, [C.POINTER(_vp), _i32, _vp, _u64, _u32, _vp]),
+    "trace_random_sharded": (_i32, [C.POINTER(_vp), _i32, _vp, _u64, _u64, _u64, _u32, _u64, _vp,
+                                    C.POINTER(_u64), C.POINTER(_f)]),
     "rt_version": (C.c_char_p, []),
 }
 

@@ -200,6 +200,20 @@ class Bvh:
         L.check(L.lib().trace_rays(self._h, _ptr(rays), n, flags, _ptr(out)))
         return out
 
+    def trace_camera(self, cam, width: int, height: int, flags: int = L.RT_TRACE_CLOSEST, out=None,
+                     first: int = 0, count: Optional[int] = None, device: Optional[str] = None):
+        """Hits of the primary rays of a pinhole image, generated on the device (trace_camera):
+        only the hits cross the bus.  ``out``: numpy / pinned tensor / CUDA tensor [count, 4]."""
+        cam = np.ascontiguousarray(cam, dtype=np.float32).reshape(12)
+        if count is None:
+            count = width * height - first
+        if out is None:
+            out = (torch.empty((count, 4), dtype=torch.float32, device=device) if device is not None
+                   else np.empty((count, 4), dtype=np.float32))
+        L.check(L.lib().trace_camera(self._h, cam.ctypes.data, width, height, first, count, flags,
+                                     _ptr(out)))
+        return out
+
     def trace_async(self, rays, out, flags: int = L.RT_TRACE_CLOSEST, stream: int = 0):
         n = _rows(rays, 8)
         L.check(L.lib().trace_rays_async(self._h, _ptr(rays), n, flags, _ptr(out), stream or None))
@@ -297,6 +311,68 @@ class Bvh:
             self.close()
         except Exception:
             pass
+
+
+# ---------------------------------------------------------------------------
+# single-process multi-GPU (build_bvh_multi / trace_rays_sharded / trace_random_sharded)
+# ---------------------------------------------------------------------------
+def shard_range(n: int, rank: int, world: int):
+    """(first, count) of rank's share of n rays: the library's rule (rt_shard_range)."""
+    first, count = C.c_uint64(), C.c_uint64()
+    L.check(L.lib().rt_shard_range(n, rank, world, C.byref(first), C.byref(count)))
+    return int(first.value), int(count.value)
+
+
+class MultiBvh:
+    """One BVH per entry of ``devices`` in this process; rays are sharded over them."""
+
+    def __init__(self, handles):
+        self.handles = handles            # list of Bvh
+        self._arr = (C.c_void_p * len(handles))(*[h._h for h in handles])
+
+    @classmethod
+    def build(cls, tris, devices, key_bits: int = 30, strategy: int = L.RT_MULTI_REDUNDANT) -> "MultiBvh":
+        n = _rows(tris, 12)
+        opts = L.BuildOpts(key_bits=key_bits, flags=0, device=-1, reserved=0, stream=None)
+        devs = (C.c_int32 * len(devices))(*devices)
+        out = (C.c_void_p * len(devices))()
+        L.check(L.lib().build_bvh_multi(_ptr(tris) if n else None, n, C.byref(opts), devs, len(devices),
+                                        strategy, out))
+        return cls([Bvh(out[i]) for i in range(len(devices))])
+
+    def trace(self, rays, flags: int = L.RT_TRACE_CLOSEST, out=None):
+        """Host rays [n, 8] -> host hits [n, 4]; share i of the batch on handle i."""
+        n = _rows(rays, 8)
+        if out is None:
+            out = _empty_like_kind(rays, (n, 4), None)
+        L.check(L.lib().trace_rays_sharded(self._arr, len(self.handles), _ptr(rays), n, flags, _ptr(out)))
+        return out
+
+    def trace_random(self, box, seed: int, first: int, n_rays: int, flags: int = L.RT_TRACE_CLOSEST,
+                     batch: int = 0, out=None):
+        """Config 5: rays generated on the devices.  Returns (hits or None, n_hit[], trace_ms[])."""
+        box = np.ascontiguousarray(box, dtype=np.float32).reshape(6)
+        k = len(self.handles)
+        n_hit, ms = (C.c_uint64 * k)(), (C.c_float * k)()
+        L.check(L.lib().trace_random_sharded(self._arr, k, box.ctypes.data, seed, first, n_rays, flags,
+                                             batch, _ptr(out) if out is not None else None, n_hit, ms))
+        return out, [int(x) for x in n_hit], [float(x) for x in ms]
+
+    def close(self) -> None:
+        for h in self.handles:
+            h.close()
+        self.handles = []
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+
+def trim(device: int = -1) -> None:
+    """Returns the library's cached pool memory to the driver (rt_trim)."""
+    L.check(L.lib().rt_trim(device))
 
 
 def hit_prims(hits):

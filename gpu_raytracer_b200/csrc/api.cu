@@ -16,9 +16,7 @@
 #include <new>
 #include <vector>
 
-#include "../../include/gpu_raytracer.h"
-#include "common.cuh"
-#include "kernels.h"
+#include "host.h"
 
 namespace rt {
 
@@ -52,20 +50,27 @@ Params& params() {
   return p;
 }
 
-int num_sms() {
-  Params& p = params();
-  if (p.num_sms == 0) {
-    int dev = 0, sms = 0;
-    if (cudaGetDevice(&dev) == cudaSuccess &&
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && sms > 0)
-      p.num_sms = sms;
-    else
-      p.num_sms = kNumSMsB200;
-  }
-  return p.num_sms;
-}
-
 namespace {
+constexpr int kMaxDevices = 64;
+std::atomic<int> g_sms[kMaxDevices];
+}  // namespace
+
+int num_sms() {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) {
+    cudaGetLastError();
+    return kNumSMsB200;
+  }
+  int sms = g_sms[dev].load(std::memory_order_relaxed);
+  if (sms == 0) {
+    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0) {
+      cudaGetLastError();
+      sms = kNumSMsB200;
+    }
+    g_sms[dev].store(sms, std::memory_order_relaxed);
+  }
+  return sms;
+}
 
 int ensure_device() {
   int count = 0;
@@ -78,18 +83,44 @@ int ensure_device() {
   return 0;
 }
 
-// keeps pool memory cached between calls (set once per device)
-int tune_pool(int device) {
-  static std::mutex mu;
-  static std::vector<int> done;
-  std::lock_guard<std::mutex> lock(mu);
-  for (int d : done)
-    if (d == device) return 0;
+// The library's own stream-ordered memory pool, one per device: handles and temporaries come
+// from it, so what it keeps cached between calls (which is what makes repeated builds
+// allocation-free) is the library's alone, can be bounded (rt_set_param "pool.keep_mb") and
+// can be given back (rt_trim); the device's default pool, which other code in the process
+// may share, is left as it was found.
+namespace {
+std::mutex g_pool_mu;
+cudaMemPool_t g_pools[kMaxDevices] = {};
+}  // namespace
+
+int device_pool(int device, cudaMemPool_t* out) {
+  if (device < 0 || device >= kMaxDevices) return fail(RT_ERR_INVALID, "device ordinal %d out of range", device);
+  std::lock_guard<std::mutex> lock(g_pool_mu);
+  if (!g_pools[device]) {
+    cudaMemPoolProps props;
+    memset(&props, 0, sizeof(props));
+    props.allocType = cudaMemAllocationTypePinned;
+    props.handleTypes = cudaMemHandleTypeNone;
+    props.location.type = cudaMemLocationTypeDevice;
+    props.location.id = device;
+    cudaMemPool_t pool;
+    RT_CUDA(cudaMemPoolCreate(&pool, &props));
+    const int keep = params().pool_keep_mb;
+    uint64_t thr = keep > 0 ? (uint64_t)keep << 20 : UINT64_MAX;
+    RT_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr));
+    g_pools[device] = pool;
+  }
+  *out = g_pools[device];
+  return 0;
+}
+
+// stream-ordered allocation from the library's pool of the current device
+int pool_alloc(void** out, size_t bytes, cudaStream_t s) {
+  int dev = 0;
+  RT_CUDA(cudaGetDevice(&dev));
   cudaMemPool_t pool;
-  RT_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
-  uint64_t thr = UINT64_MAX;
-  RT_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr));
-  done.push_back(device);
+  RT_TRY(device_pool(dev, &pool));
+  RT_CUDA(cudaMallocFromPoolAsync(out, bytes ? bytes : 16, pool, s));
   return 0;
 }
 
@@ -107,6 +138,8 @@ int classify(const void* p, int* dev) {
   }
   return 0;
 }
+
+namespace {
 
 // Pinned (page-locked, mapped) host memory can be read and written by kernels
 // directly over PCIe.  Returns the device-side alias, or nullptr.
@@ -130,64 +163,10 @@ bool is_pinned_host(const void* p) {
   return a.type == cudaMemoryTypeHost;
 }
 
-struct DeviceScope {
-  int prev = -1;
-  bool switched = false;
-  int enter(int device) {
-    RT_CUDA(cudaGetDevice(&prev));
-    if (device >= 0 && device != prev) {
-      RT_CUDA(cudaSetDevice(device));
-      switched = true;
-    }
-    return 0;
-  }
-  ~DeviceScope() {
-    if (switched) cudaSetDevice(prev);
-  }
-};
-
-// stream-ordered temporary allocations, released on scope exit
-struct TempPool {
-  cudaStream_t s;
-  std::vector<void*> ptrs;
-  explicit TempPool(cudaStream_t stream) : s(stream) {}
-  int alloc(void** out, size_t bytes) {
-    if (bytes == 0) bytes = 16;
-    RT_CUDA(cudaMallocAsync(out, bytes, s));
-    ptrs.push_back(*out);
-    return 0;
-  }
-  ~TempPool() {
-    for (void* p : ptrs) cudaFreeAsync(p, s);
-  }
-};
-
 }  // namespace
 }  // namespace rt
 
 using namespace rt;
-
-struct rt_bvh {
-  uint64_t n = 0;
-  uint32_t key_bits = 30;
-  int device = 0;
-  Node* nodes = nullptr;
-  SortedTri* stris = nullptr;
-  BvhHeader* header = nullptr;
-  // parent words: derived from the nodes on first use (refit_bvh, bvh_read_topology/boxes)
-  mutable uint32_t* parent = nullptr;
-  mutable std::mutex parent_mu;
-  void* keys = nullptr;  // only with RT_BUILD_KEEP_KEYS
-  Node4* wide = nullptr;      // only with RT_BUILD_WIDE4 / bvh_widen: n-1 slots
-  uint32_t wide_root = 0;     // reference the BVH4 traversal starts from
-  bool is_wide = false;
-  uint32_t wide_leaf_max = kWideLeafDefault;
-  float bounds[6] = {0, 0, 0, 0, 0, 0};
-  int root = 0;  // node id where traversal starts (header.root_node)
-  float times[RT_STAGE_COUNT] = {0, 0, 0, 0, 0, 0, 0};
-  bool has_times = false;
-  uint64_t bytes = 0;
-};
 
 namespace {
 
@@ -213,7 +192,7 @@ int ensure_parents(const rt_bvh* h, cudaStream_t s) {
   std::lock_guard<std::mutex> lock(h->parent_mu);
   if (h->parent || h->n == 0) return 0;
   uint32_t* p = nullptr;
-  RT_CUDA(cudaMallocAsync((void**)&p, (2 * h->n - 1) * sizeof(uint32_t), s));
+  RT_TRY(pool_alloc((void**)&p, (2 * h->n - 1) * sizeof(uint32_t), s));
   int rc = launch_derive_parents(h->nodes, h->n, h->root, p, s);
   if (rc != 0) {
     cudaFreeAsync(p, s);
@@ -231,7 +210,7 @@ int widen(rt_bvh* h, cudaStream_t s) {
   h->wide_leaf_max = (uint32_t)(lm < 1 ? 1 : (lm > kWideLeafMax ? kWideLeafMax : lm));
   if (!h->wide && h->n > 1) {
     const size_t bytes = (h->n - 1) * sizeof(Node4);
-    RT_CUDA(cudaMallocAsync((void**)&h->wide, bytes, s));
+    RT_TRY(pool_alloc((void**)&h->wide, bytes, s));
     h->bytes += bytes;
   }
   RT_TRY(launch_collapse4(h->nodes, h->n, h->wide_leaf_max, h->wide, s));
@@ -240,10 +219,11 @@ int widen(rt_bvh* h, cudaStream_t s) {
   return 0;
 }
 
+}  // namespace
 // traversal of whichever layout the handle holds
-int launch_trace_h(const rt_bvh* h, const float4* rays, uint64_t n_rays, uint32_t flags,
-                   float4* hits, unsigned long long* counter, cudaStream_t s,
-                   unsigned long long* stats = nullptr) {
+int rt::launch_trace_h(const rt_bvh* h, const float4* rays, uint64_t n_rays, uint32_t flags,
+                       float4* hits, unsigned long long* counter, cudaStream_t s,
+                       unsigned long long* stats) {
   if (h->is_wide && params().trace_wide != 0)
     return launch_trace_wide(h->wide, h->stris, h->n, h->wide_root, rays, n_rays, flags, hits,
                              counter, s, stats);
@@ -251,16 +231,17 @@ int launch_trace_h(const rt_bvh* h, const float4* rays, uint64_t n_rays, uint32_
                       stats);
 }
 
+namespace {
 int alloc_handle_buffers(rt_bvh* h, bool keep_keys, cudaStream_t s) {
   const uint64_t n = h->n;
   const size_t node_bytes = (n > 1 ? (n - 1) : 1) * sizeof(Node);
   const size_t tri_bytes = (n ? n : 1) * sizeof(SortedTri);
-  RT_CUDA(cudaMallocAsync((void**)&h->nodes, node_bytes, s));
-  RT_CUDA(cudaMallocAsync((void**)&h->stris, tri_bytes, s));
-  RT_CUDA(cudaMallocAsync((void**)&h->header, sizeof(BvhHeader), s));
+  RT_TRY(pool_alloc((void**)&h->nodes, node_bytes, s));
+  RT_TRY(pool_alloc((void**)&h->stris, tri_bytes, s));
+  RT_TRY(pool_alloc((void**)&h->header, sizeof(BvhHeader), s));
   h->bytes = node_bytes + tri_bytes + sizeof(BvhHeader);
   if (keep_keys) {
-    RT_CUDA(cudaMallocAsync(&h->keys, (n ? n : 1) * key_size(h->key_bits), s));
+    RT_TRY(pool_alloc(&h->keys, (n ? n : 1) * key_size(h->key_bits), s));
     h->bytes += (n ? n : 1) * key_size(h->key_bits);
   }
   return 0;
@@ -338,9 +319,9 @@ int build_impl(rt_bvh* h, const float* tris_in, uint32_t flags, cudaStream_t s) 
   RT_TRY(tmp.alloc(&queue_buf, refit_queue_bytes(n)));
 
   const bool timed = (flags & RT_BUILD_TIMINGS) != 0;
-  cudaEvent_t ev[RT_STAGE_COUNT];
-  if (timed)
-    for (int i = 0; i < RT_STAGE_COUNT; ++i) RT_CUDA(cudaEventCreate(&ev[i]));
+  EventSet evs;  // destroyed on every return path
+  if (timed) RT_TRY(evs.create(RT_STAGE_COUNT));
+  cudaEvent_t* ev = evs.ev;
   auto mark = [&](int i) -> int {
     if (timed) RT_CUDA(cudaEventRecord(ev[i], s));
     return 0;
@@ -360,34 +341,63 @@ int build_impl(rt_bvh* h, const float* tris_in, uint32_t flags, cudaStream_t s) 
   RT_TRY(mark(2));
   void* skeys = nullptr;
   uint32_t* svals = nullptr;
-  bool sorted = false;
+  // 63-bit keys, hybrid order: launched on the assumption that no run of equal top bits is
+  // longer than the ranking window.  The flag that says otherwise makes the kernels after it
+  // return at once (they would read ranks that were never written) and is read with the
+  // header at the end of the build: no host round trip in the middle of the stream.
   if (hybrid)
-    RT_TRY(launch_sort63_hybrid((uint64_t*)keys, n, ws, k32, long_run, &skeys, &svals, &sorted, s,
+    RT_TRY(launch_sort63_hybrid((uint64_t*)keys, n, ws, k32, long_run, &skeys, &svals, s,
                                 hist_ready == 2));
-  if (!sorted)
+  else
     RT_TRY(launch_sort(keys, n, h->key_bits, ws, /*iota_payload=*/true, &skeys, &svals, s,
                        hist_ready == 1));
   RT_TRY(mark(3));
   RT_TRY(mark(4));  // A4 is fused into the bottom-up pass: the topology stage is empty
   RT_TRY(launch_build_tree(tris, svals, skeys, h->key_bits, n, (uint32_t*)flags_buf, h->nodes,
-                           h->stris, h->header, queue_buf, s));
+                           h->stris, h->header, queue_buf, s, hybrid ? long_run : nullptr));
   RT_TRY(mark(5));
-  if (flags & RT_BUILD_WIDE4) RT_TRY(widen(h, s));  // A5w, optional
-  RT_TRY(mark(6));
+  const bool want_wide = (flags & RT_BUILD_WIDE4) != 0;
+  if (!want_wide) RT_TRY(mark(6));
+  uint32_t long_flag = 0;
+  if (hybrid) RT_CUDA(cudaMemcpyAsync(&long_flag, long_run, 4, cudaMemcpyDeviceToHost, s));
   if (h->keys) RT_CUDA(cudaMemcpyAsync(h->keys, skeys, n * ksz, cudaMemcpyDeviceToDevice, s));
   RT_CUDA(cudaMemcpyAsync(&hdr, h->header, sizeof(hdr), cudaMemcpyDeviceToHost, s));
   RT_CUDA(cudaStreamSynchronize(s));
+  if (long_flag) {
+    // a run longer than the window (e.g. thousands of equal centroids).  Encode again (the
+    // hybrid pass works on the keys in place) and sort all 63 bits: the same order the hybrid
+    // gives where it applies, bit for bit.
+    RT_CUDA(cudaMemsetAsync(ws.hist, 0, sort_hist_words(h->key_bits) * sizeof(uint32_t), s));
+    RT_TRY(prepare_build_tree(n, (uint32_t*)flags_buf, queue_buf, s));
+    RT_TRY(launch_morton(centroids, n, (const uint32_t*)bkeys, h->key_bits, keys, ws.chunk_hist,
+                         ws.hist, &hist_ready, s, nullptr));
+    RT_TRY(launch_sort(keys, n, h->key_bits, ws, /*iota_payload=*/true, &skeys, &svals, s,
+                       hist_ready == 1));
+    RT_TRY(mark(3));
+    RT_TRY(mark(4));
+    RT_TRY(launch_build_tree(tris, svals, skeys, h->key_bits, n, (uint32_t*)flags_buf, h->nodes,
+                             h->stris, h->header, queue_buf, s, nullptr));
+    RT_TRY(mark(5));
+    if (!want_wide) RT_TRY(mark(6));
+    if (h->keys) RT_CUDA(cudaMemcpyAsync(h->keys, skeys, n * ksz, cudaMemcpyDeviceToDevice, s));
+    RT_CUDA(cudaMemcpyAsync(&hdr, h->header, sizeof(hdr), cudaMemcpyDeviceToHost, s));
+    RT_CUDA(cudaStreamSynchronize(s));
+  }
   for (int k = 0; k < 3; ++k) {
     h->bounds[k] = hdr.root_min[k];
     h->bounds[3 + k] = hdr.root_max[k];
   }
   h->root = (int)hdr.root_node;
+  if (want_wide) {  // A5w, optional: needs the root
+    RT_TRY(widen(h, s));
+    RT_TRY(mark(6));
+    RT_CUDA(cudaStreamSynchronize(s));
+  }
   h->wide_root = wide_root_ref(n, h->root, h->wide_leaf_max);
   if (timed) {
     for (int i = 0; i < 5; ++i) RT_CUDA(cudaEventElapsedTime(&h->times[i], ev[i], ev[i + 1]));
     RT_CUDA(cudaEventElapsedTime(&h->times[RT_STAGE_WIDE], ev[5], ev[6]));
     RT_CUDA(cudaEventElapsedTime(&h->times[RT_STAGE_TOTAL], ev[0], ev[6]));
-    for (int i = 0; i < RT_STAGE_COUNT; ++i) cudaEventDestroy(ev[i]);
     h->has_times = true;
   }
   return 0;
@@ -411,7 +421,6 @@ extern "C" int build_bvh(const float* tris, uint64_t n_tris, const rt_build_opts
   RT_TRY(scope.enter(opts ? opts->device : -1));
   int dev = 0;
   RT_CUDA(cudaGetDevice(&dev));
-  RT_TRY(tune_pool(dev));
   rt_bvh* h = new (std::nothrow) rt_bvh;
   if (!h) return fail(RT_ERR_OOM, "build_bvh: host allocation failed");
   h->n = n_tris;
@@ -608,10 +617,11 @@ int trace_reordered(const rt_bvh* h, const float4* rays, uint64_t n_rays, uint32
   return 0;
 }
 
-int trace_device(const rt_bvh* h, const float4* rays, uint64_t n_rays, uint32_t flags,
-                 float4* hits, cudaStream_t s) {
+}  // namespace
+int rt::trace_device(const rt_bvh* h, const float4* rays, uint64_t n_rays, uint32_t flags,
+                     float4* hits, cudaStream_t s) {
   unsigned long long* counter = nullptr;
-  RT_CUDA(cudaMallocAsync((void**)&counter, sizeof(unsigned long long), s));
+  RT_TRY(pool_alloc((void**)&counter, sizeof(unsigned long long), s));
   int rc;
   if ((flags & RT_TRACE_REORDER) && n_rays >= kReorderMin && h->n != 0 &&
       params().trace_variant != 0 && !(h->is_wide && params().trace_wide != 0))
@@ -622,6 +632,7 @@ int trace_device(const rt_bvh* h, const float4* rays, uint64_t n_rays, uint32_t 
   return rc;
 }
 
+namespace {
 // host rays and/or host hits: chunked, copies overlap the traversal
 int trace_staged(const rt_bvh* h, const float* rays, bool rays_dev, uint64_t n_rays, uint32_t flags,
                  float* hits, bool hits_dev) {
@@ -718,8 +729,17 @@ int trace_streamed(const rt_bvh* h, const float* rays, uint64_t n_rays, uint32_t
     while (up_shift < 20 && (n >> (up_shift + 1)) >= 6) ++up_shift;
     const uint32_t nseg = (uint32_t)((n + (1ull << seg_shift) - 1) >> seg_shift);
     float4 *d_rays = nullptr, *d_hits = nullptr;
-    RT_CUDA(cudaMallocAsync((void**)&d_rays, n * 32, p.s_in));
-    RT_CUDA(cudaMallocAsync((void**)&d_hits, n * 16, p.s_in));
+    TempPool batch(p.s_in);  // released on every return path, after the streams have drained
+    struct Drain {
+      Pipeline& p;
+      ~Drain() {
+        cudaStreamSynchronize(p.s_run);
+        cudaStreamSynchronize(p.s_out);
+        cudaStreamSynchronize(p.s_in);
+      }
+    } drain{p};
+    RT_TRY(batch.alloc((void**)&d_rays, n * 32));
+    RT_TRY(batch.alloc((void**)&d_hits, n * 16));
     RT_CUDA(cudaMemsetAsync(p.d_ctl, 0, 16 + (size_t)nseg * 4, p.s_in));
     memset(p.h_flags, 0, (size_t)nseg * 4);
     RT_CUDA(cudaEventRecord(ev_ctl, p.s_in));
@@ -775,8 +795,6 @@ int trace_streamed(const rt_bvh* h, const float* rays, uint64_t n_rays, uint32_t
         if (copy_seg(next) != cudaSuccess) rc = RT_ERR_CUDA;
     if (cudaStreamSynchronize(p.s_out) != cudaSuccess) rc = RT_ERR_CUDA;
     cudaStreamSynchronize(p.s_in);
-    cudaFreeAsync(d_rays, p.s_in);
-    cudaFreeAsync(d_hits, p.s_in);
     if (e != cudaSuccess) return fail_cuda(e, "trace_streamed", __FILE__, __LINE__);
     if (err != 0) return kStreamStalled;  // the caller runs the batch again through staged chunks
     if (rc != 0) return fail(rc, "trace_rays: streamed pipeline failed (%s)", cudaGetErrorString(cudaGetLastError()));
@@ -838,6 +856,36 @@ extern "C" int trace_rays(const rt_bvh* h, const float* rays, uint64_t n_rays, u
   if (hits_k) return trace_staged(h, rays, rays_dev, n_rays, flags, (float*)hits_k, true);
   if (rays_k) return trace_staged(h, (const float*)rays_k, true, n_rays, flags, hits, hits_dev);
   return trace_staged(h, rays, rays_dev, n_rays, flags, hits, hits_dev);
+}
+
+// Primary rays never cross PCIe: the 12-float camera goes in, the rays are generated on the
+// device (the same bytes rt_gen_primary_rays gives), traced, and only the hits come back.
+extern "C" int trace_camera(const rt_bvh* h, const float* cam, uint32_t width, uint32_t height,
+                            uint64_t first, uint64_t count, uint32_t flags, float* hits) {
+  if (!h) return fail(RT_ERR_INVALID, "trace_camera: handle is NULL");
+  if (!cam || width == 0 || height == 0) return fail(RT_ERR_INVALID, "trace_camera: bad camera or image size");
+  if (first + count > (uint64_t)width * height) return fail(RT_ERR_INVALID, "trace_camera: range beyond the image");
+  if (count == 0) return RT_OK;
+  if (!hits) return fail(RT_ERR_INVALID, "trace_camera: hits is NULL");
+  if (flags > 7u) return fail(RT_ERR_INVALID, "trace_camera: unknown flags 0x%x", flags);
+  DeviceScope scope;
+  RT_TRY(scope.enter(h->device));
+  int hd = -1;
+  const bool hits_dev = classify(hits, &hd) != 0;
+  if (hits_dev && hd != h->device)
+    return fail(RT_ERR_INVALID, "trace_camera: hits are not on the handle's device %d", h->device);
+  cudaStream_t s = 0;
+  TempPool tmp(s);
+  float4* d_rays = nullptr;
+  RT_TRY(tmp.alloc((void**)&d_rays, count * 32));
+  RT_TRY(launch_gen_primary(cam, width, height, first, count, d_rays, s));
+  if (hits_dev) {
+    RT_TRY(trace_device(h, d_rays, count, flags, reinterpret_cast<float4*>(hits), s));
+    RT_CUDA(cudaStreamSynchronize(s));
+    return RT_OK;
+  }
+  // host hits: chunks of the traversal overlap the download of the chunk before
+  return trace_staged(h, reinterpret_cast<const float*>(d_rays), true, count, flags & 3u, hits, false);
 }
 
 extern "C" int trace_rays_stats(const rt_bvh* h, const float* rays, uint64_t n_rays, uint32_t flags,
@@ -976,7 +1024,6 @@ extern "C" int bvh_alloc_empty(uint64_t n_tris, uint32_t key_bits, rt_bvh** out)
   RT_TRY(ensure_device());
   int dev = 0;
   RT_CUDA(cudaGetDevice(&dev));
-  RT_TRY(tune_pool(dev));
   rt_bvh* h = new (std::nothrow) rt_bvh;
   if (!h) return fail(RT_ERR_OOM, "bvh_alloc_empty: host allocation failed");
   h->n = n_tris;
@@ -992,6 +1039,14 @@ extern "C" int bvh_alloc_empty(uint64_t n_tris, uint32_t key_bits, rt_bvh** out)
   return RT_OK;
 }
 
+int rt::adopt_committed(rt_bvh* dst, const rt_bvh* src) {
+  if (!dst || !src || dst->n != src->n) return fail(RT_ERR_INVALID, "adopt_committed: handles differ in size");
+  dst->key_bits = src->key_bits;
+  memcpy(dst->bounds, src->bounds, sizeof(dst->bounds));
+  dst->root = src->root;
+  return 0;
+}
+
 extern "C" int bvh_commit(rt_bvh* h) {
   if (!h) return fail(RT_ERR_INVALID, "bvh_commit: handle is NULL");
   DeviceScope scope;
@@ -1002,6 +1057,33 @@ extern "C" int bvh_commit(rt_bvh* h) {
   if (n != h->n)
     return fail(RT_ERR_INVALID, "bvh_commit: header says %llu triangles, handle was sized for %llu",
                 (unsigned long long)n, (unsigned long long)h->n);
+  if (hdr.key_bits != 30 && hdr.key_bits != 63)
+    return fail(RT_ERR_INVALID, "bvh_commit: header says %u key bits", hdr.key_bits);
+  // The buffers came from a file or from another process: check everything the kernels index
+  // with before anything walks it (refit.cu validate_*), so corrupt data is RT_ERR_INVALID,
+  // not a device fault.
+  if (n != 0) {
+    cudaStream_t s = 0;
+    TempPool tmp(s);
+    uint32_t* bad = nullptr;
+    RT_TRY(tmp.alloc((void**)&bad, sizeof(uint32_t)));
+    uint32_t flag = 0;
+    RT_TRY(launch_validate(h->nodes, h->stris, n, (int)hdr.root_node, bad, s));
+    RT_CUDA(cudaMemcpyAsync(&flag, bad, 4, cudaMemcpyDeviceToHost, s));
+    RT_CUDA(cudaStreamSynchronize(s));
+    if (flag) return fail(RT_ERR_INVALID, "bvh_commit: node array, root or primitive indices are inconsistent");
+    h->root = (int)hdr.root_node;
+    {  // a tree re-committed after new data arrived: derive the parents again
+      std::lock_guard<std::mutex> lock(h->parent_mu);
+      if (h->parent) cudaFreeAsync(h->parent, s);
+      h->parent = nullptr;
+    }
+    RT_TRY(ensure_parents(h, s));
+    RT_TRY(launch_validate_depth(h->parent, n, bad, s));
+    RT_CUDA(cudaMemcpyAsync(&flag, bad, 4, cudaMemcpyDeviceToHost, s));
+    RT_CUDA(cudaStreamSynchronize(s));
+    if (flag) return fail(RT_ERR_INVALID, "bvh_commit: the tree is deeper than %d levels", kMaxDepth);
+  }
   h->key_bits = hdr.key_bits;
   for (int k = 0; k < 3; ++k) {
     h->bounds[k] = hdr.root_min[k];
@@ -1071,6 +1153,21 @@ extern "C" int bvh_load(const char* path, rt_bvh** out) {
       fread(meta, 4, 2, f) != 2) {
     fclose(f);
     return fail(RT_ERR_INVALID, "bvh_load: %s is not a BVH file", path);
+  }
+  if (n > RT_MAX_TRIS || (meta[0] != 30 && meta[0] != 63)) {
+    fclose(f);
+    return fail(RT_ERR_INVALID, "bvh_load: %s: bad triangle count or key width", path);
+  }
+  {  // the file must hold exactly header + nodes + triangles: a truncated file fails here
+    const long long want = 24 + (long long)sizeof(BvhHeader) + (long long)(n > 1 ? n - 1 : 0) * (long long)sizeof(Node) +
+                           (long long)n * (long long)sizeof(SortedTri);
+    long long have = -1;
+    if (fseek(f, 0, SEEK_END) == 0) have = ftell(f);
+    if (have != want || fseek(f, 24, SEEK_SET) != 0) {
+      fclose(f);
+      return fail(RT_ERR_INVALID, "bvh_load: %s holds %lld bytes, a BVH of %llu triangles needs %lld", path,
+                  have, (unsigned long long)n, want);
+    }
   }
   rt_bvh* h = nullptr;
   int rc = bvh_alloc_empty(n, meta[0], &h);
@@ -1243,7 +1340,38 @@ extern "C" int rt_set_param(const char* name, int64_t value) {
   else if (!strcmp(name, "trace.leaf_min")) p.trace_leaf_min = (int)value;
   else if (!strcmp(name, "trace.sh_stack")) p.trace_sh_stack = (int)value;
   else if (!strcmp(name, "build.pdl")) g_pdl = value != 0;
+  else if (!strcmp(name, "pool.keep_mb")) {
+    p.pool_keep_mb = (int)value;
+    std::lock_guard<std::mutex> lock(g_pool_mu);
+    const uint64_t thr = value > 0 ? (uint64_t)value << 20 : UINT64_MAX;
+    for (int d = 0; d < kMaxDevices; ++d)
+      if (g_pools[d]) cudaMemPoolSetAttribute(g_pools[d], cudaMemPoolAttrReleaseThreshold, (void*)&thr);
+    cudaGetLastError();
+  }
   else return fail(RT_ERR_INVALID, "rt_set_param: unknown parameter '%s'", name);
+  return RT_OK;
+}
+
+extern "C" int rt_trim(int device) {
+  RT_TRY(ensure_device());
+  int first = device, last = device;
+  if (device < 0) {
+    first = 0;
+    last = kMaxDevices - 1;
+  }
+  if (last >= kMaxDevices) return fail(RT_ERR_INVALID, "rt_trim: device ordinal %d out of range", device);
+  for (int d = first; d <= last; ++d) {
+    cudaMemPool_t pool = nullptr;
+    {
+      std::lock_guard<std::mutex> lock(g_pool_mu);
+      pool = g_pools[d];
+    }
+    if (!pool) continue;
+    DeviceScope scope;
+    RT_TRY(scope.enter(d));
+    RT_CUDA(cudaDeviceSynchronize());  // frees queued on any stream have happened
+    RT_CUDA(cudaMemPoolTrimTo(pool, 0));
+  }
   return RT_OK;
 }
 
@@ -1256,7 +1384,6 @@ extern "C" int rt_sort_pairs(void* keys, uint32_t* vals, uint64_t n, uint32_t ke
     return fail(RT_ERR_INVALID, "rt_sort_pairs: keys and vals must be device memory");
   int dev = 0;
   RT_CUDA(cudaGetDevice(&dev));
-  RT_TRY(tune_pool(dev));
   cudaStream_t s = 0;
   TempPool tmp(s);
   const size_t ksz = key_size(key_bits);

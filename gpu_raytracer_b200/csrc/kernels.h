@@ -4,6 +4,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <atomic>
+
 namespace rt {
 
 // One BVH2 node, 64 bytes: the boxes of both children plus their ids, so that
@@ -35,6 +37,9 @@ struct BvhHeader {
   uint32_t pad[6];
 };
 
+// deepest tree the traversal stacks hold: 63 key bits + 32 tie-break bits = 95 levels
+constexpr int kMaxDepth = 96;
+
 // parent word: (parent node id << 2) | (local << 1) | slot; kNoParent for the root.
 // slot 0 = left child.  local = 1 when the two children met in the shared memory
 // of one refit CTA while the tree was built (both leaf ranges inside one aligned
@@ -57,6 +62,8 @@ int launch_gen_ao(const float4* tris, const float4* rays, const float4* hits, ui
                   uint32_t spp, uint64_t seed, float radius, float4* out, cudaStream_t s);
 int launch_shade(const float4* tris, const float4* rays, const float4* hits,
                  const float4* ao_hits, uint64_t n, uint32_t spp, float* rgb, cudaStream_t s);
+// *out += number of hit records with prim >= 0 (closest hits, or occluded any-hit rays)
+int launch_count_hits(const float4* hits, uint64_t n, unsigned long long* out, cudaStream_t s);
 
 // ---- build (morton.cu, radix_sort.cu, karras.cu, refit.cu) -----------------
 // bounds_keys: 6 ordered-int keys, min.xyz then max.xyz; must be pre-set to
@@ -114,22 +121,31 @@ int launch_sort(void* keys, uint64_t n, uint32_t key_bits, const SortWorkspace& 
 // 63-bit keys with an iota payload, hybrid order (radix_sort.cu): three packed passes on the
 // top 30 bits, then ranks inside the runs of equal top bits.  ws must hold BOTH layouts
 // (rec_a, rec_b, vals for the 30-bit passes; keys_alt, vals_alt for the result), chunk_hist
-// sized for either key width; k32: n u32; long_run: one u32.  *used = false when a run was
-// too long: nothing of k64 has changed and the caller runs launch_sort on all 63 bits.
+// sized for either key width; k32: n u32; long_run: one u32, zeroed by the caller.  No host
+// synchronisation: when a run is longer than the ranking window the kernels set *long_run,
+// the result buffers hold nothing useful, and the caller (who reads the flag at its next
+// synchronisation) encodes the keys again and runs launch_sort on all 63 bits.
 int launch_sort63_hybrid(uint64_t* k64, uint64_t n, const SortWorkspace& ws, uint32_t* k32,
-                         uint32_t* long_run, void** keys_out, uint32_t** vals_out, bool* used,
-                         cudaStream_t s, bool k32_ready = false);
+                         uint32_t* long_run, void** keys_out, uint32_t** vals_out, cudaStream_t s,
+                         bool k32_ready = false);
 
 // A4 + A5 fused: topology, triangle reorder, boxes (refit.cu).  keys: the sorted Morton
 // codes; flags: n-1 u32, zeroed by the launcher.  Writes nodes (indexed by split
 // position), sorted tris, header box and root id.
 int launch_build_tree(const float4* tris, const uint32_t* sorted_idx, const void* keys,
                       uint32_t key_bits, uint64_t n, uint32_t* flags, Node* nodes,
-                      SortedTri* stris, BvhHeader* header, void* queue_buf, cudaStream_t s);
+                      SortedTri* stris, BvhHeader* header, void* queue_buf, cudaStream_t s,
+                      const uint32_t* abort_flag = nullptr);  // non-null and *abort_flag != 0: do nothing
 // parent words (2n-1 u32) from the finished nodes; needed by launch_refit_update and
 // launch_export_topology only, so the handle derives them on first use
 int launch_derive_parents(const Node* nodes, uint64_t n, int root, uint32_t* parent,
                           cudaStream_t s);
+// bvh_load / bvh_commit: *bad = 1 when the node array, the root or a primitive index is out
+// of range or inconsistent (refit.cu); launch_validate_depth needs the parent words, which
+// may only be derived once launch_validate has passed
+int launch_validate(const Node* nodes, const SortedTri* stris, uint64_t n, int root, uint32_t* bad,
+                    cudaStream_t s);
+int launch_validate_depth(const uint32_t* parent, uint64_t n, uint32_t* bad, cudaStream_t s);
 // must precede launch_build_tree on the same stream (zeroes flags and the queue head)
 int prepare_build_tree(uint64_t n, uint32_t* flags, void* queue_buf, cudaStream_t s);
 // bytes of the continuation queue launch_build_tree / launch_refit_update need (queue_buf)
@@ -201,26 +217,37 @@ int launch_trace(const Node* nodes, const SortedTri* stris, uint64_t n_tris, int
 // box = the scene bounds {min.xyz, max.xyz} (host values)
 int launch_ray_keys(const float4* rays, uint64_t n, const float* box, uint32_t* keys, cudaStream_t s);
 
-// tuning knobs (rt_set_param)
+// tuning knobs (rt_set_param).  Process-wide; every field is an atomic, so a knob may be
+// changed while other host threads trace or build (each call reads a knob once, when it
+// chooses its launch): there is no torn read, only "this call or the next one".
+struct Knob {
+  std::atomic<int> v;
+  explicit constexpr Knob(int x) : v(x) {}
+  operator int() const { return v.load(std::memory_order_relaxed); }
+  Knob& operator=(int x) {
+    v.store(x, std::memory_order_relaxed);
+    return *this;
+  }
+};
 struct Params {
-  int sort_variant = 0;
-  int sort_bits = 0;            // 0 = default digit width (sort_plan)
-  int sort_hybrid = 1;          // 63-bit builds: 1 = top-30 LSD + ranks inside runs (default), 0 = 7 passes
-  int trace_blocks_per_sm = 0;  // 0 = kernel default
-  int trace_variant = 1;        // 0 = plain while-while, 1 = dynamic fetch + voted leaf loop
-  int trace_chunk = 0, trace_refill_min = 0, trace_leaf_min = 0;  // 0 = defaults
-  int trace_sh_stack = -1;      // stack levels kept in shared memory (0, 8, 16, 24); -1 = 8 with RT_TRACE_REORDER, else 0
-  int trace_wide = 1;           // 1 = use the BVH4 of handles built with RT_BUILD_WIDE4
-  int wide_leaf_max = kWideLeafDefault;  // triangles per BVH4 leaf (1..4), read when collapsing
+  Knob sort_variant{0};
+  Knob sort_bits{0};            // 0 = default digit width (sort_plan)
+  Knob sort_hybrid{1};          // 63-bit builds: 1 = top-30 LSD + ranks inside runs (default), 0 = 7 passes
+  Knob trace_blocks_per_sm{0};  // 0 = kernel default
+  Knob trace_variant{1};        // 0 = plain while-while, 1 = dynamic fetch + voted leaf loop
+  Knob trace_chunk{0}, trace_refill_min{0}, trace_leaf_min{0};  // 0 = defaults
+  Knob trace_sh_stack{-1};      // stack levels kept in shared memory (0, 8, 16, 24); -1 = 8 with RT_TRACE_REORDER, else 0
+  Knob trace_wide{1};           // 1 = use the wide layout of handles that hold one (RT_BUILD_WIDE4 / RT_BUILD_WIDE8)
+  Knob wide_leaf_max{kWideLeafDefault};  // triangles per BVH4 leaf (1..4), read when collapsing
   // bit 0: kernels read pinned host rays in place, bit 1: store hits to pinned host in
   // place.  Measured slower than the copy engines on B200/PCIe5 (profiles/r01b_e2e_modes.md),
   // so the default stages both.
-  int zero_copy = 0;
-  int stage_chunk = 0;          // rays per staged chunk (0 = 1M)
-  int streamed = 1;             // 1 = pinned host batches go through the single-launch streamed mode
-  int num_sms = 0;              // filled at first use
+  Knob zero_copy{0};
+  Knob stage_chunk{0};          // rays per staged chunk (0 = 1M)
+  Knob streamed{1};             // 1 = pinned host batches go through the single-launch streamed mode
+  Knob pool_keep_mb{0};         // build/trace temporaries kept cached per device after a call; 0 = all
 };
 Params& params();
-int num_sms();
+int num_sms();  // of the current device (cached per device)
 
 }  // namespace rt

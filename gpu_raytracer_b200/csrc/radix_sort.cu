@@ -436,7 +436,9 @@ int clamp_variant() {
 ChunkGeom sort_geometry(uint64_t n, uint32_t key_bits) {
   const Shape& sh = kShapes[clamp_variant()];
   const uint64_t tile = (uint64_t)sh.threads * (key_bits == 30 ? sh.ipt32 : sh.ipt64);
-  const uint64_t max_ctas = (uint64_t)num_sms() * sh.ctas_per_sm;
+  uint64_t max_ctas = (uint64_t)num_sms() * sh.ctas_per_sm;
+  // chunk_offsets_kernel scans at most 32 * kOffMaxRounds chunks per bin
+  if (max_ctas > 32ull * kOffMaxRounds) max_ctas = 32ull * kOffMaxRounds;
   ChunkGeom g;
   g.n = (uint32_t)n;
   const uint64_t tiles = (n + tile - 1) / tile;
@@ -570,6 +572,7 @@ int launch_sort(void* keys, uint64_t n, uint32_t key_bits, const SortWorkspace& 
   const ChunkGeom g = make_geom(n, key_bits);
   if (ws.chunk_words < (uint64_t)g.chunks * bins)
     return fail(-2, "sort: chunk workspace too small");
+  if (g.chunks > 32u * kOffMaxRounds) return fail(-2, "sort: %u chunks exceed the offsets scan", g.chunks);
   if (!first_hist_ready)
     RT_CUDA(cudaMemsetAsync(ws.hist, 0, sort_hist_words(key_bits) * sizeof(uint32_t), s));
   for (int p = 0; p < plan.passes; ++p) {
@@ -652,12 +655,13 @@ gather_runs_kernel(const uint64_t* __restrict__ k64, const uint32_t* __restrict_
 __global__ void __launch_bounds__(kRankThreads)
 rank_runs_kernel(const uint64_t* __restrict__ k64g, const uint32_t* __restrict__ idx,
                  const uint32_t* __restrict__ k32s, uint32_t n, uint64_t* __restrict__ keys_out,
-                 uint32_t* __restrict__ vals_out) {
+                 uint32_t* __restrict__ vals_out, const uint32_t* __restrict__ long_run) {
   constexpr int kSpan = kRankThreads + 2 * (int)kMaxRun;
   constexpr int kWords = kSpan / 32;
   __shared__ uint64_t s_key[kSpan];
   __shared__ uint32_t s_head[kWords];  // bit = this slot starts a run (or lies outside the array)
   pdl_enter();
+  if (*long_run != 0u) return;  // a run longer than the window: the caller sorts all 63 bits
   const long long base = (long long)blockIdx.x * kRankThreads - (long long)kMaxRun;
   for (int t = threadIdx.x; t < kSpan; t += kRankThreads) {  // kSpan is a multiple of the CTA: whole warps
     const long long g = base + t;
@@ -709,10 +713,12 @@ rank_runs_kernel(const uint64_t* __restrict__ k64g, const uint32_t* __restrict__
 }
 
 int launch_sort63_hybrid(uint64_t* k64, uint64_t n, const SortWorkspace& ws, uint32_t* k32,
-                         uint32_t* long_run, void** keys_out, uint32_t** vals_out, bool* used,
-                         cudaStream_t s, bool k32_ready) {
-  *used = false;
-  if (n < 2 || n > ((1ull << 30) - 1)) return 0;
+                         uint32_t* long_run, void** keys_out, uint32_t** vals_out, cudaStream_t s,
+                         bool k32_ready) {
+  *keys_out = k64;
+  *vals_out = ws.vals_alt;
+  if (n > ((1ull << 30) - 1)) return fail(-5, "sort: n = %llu beyond 2^30-1", (unsigned long long)n);
+  if (n == 0) return 0;
   const unsigned grid = (unsigned)((n + 255) / 256);
   // k32_ready: the Morton kernel stored the top bits and counted their first digit; long_run
   // was zeroed by the caller before the first kernel
@@ -727,17 +733,13 @@ int launch_sort63_hybrid(uint64_t* k64, uint64_t n, const SortWorkspace& ws, uin
   RT_CUDA(launch_pdl(gather_runs_kernel, grid, 256, 0, s, (const uint64_t*)k64, (const uint32_t*)sidx,
                      (const uint32_t*)sk32, (uint32_t)n, (uint64_t*)ws.keys_alt, long_run));
   RT_LAUNCHED();
-  uint32_t flag = 0;
-  RT_CUDA(cudaMemcpyAsync(&flag, long_run, 4, cudaMemcpyDeviceToHost, s));
-  RT_CUDA(cudaStreamSynchronize(s));
-  if (flag) return 0;  // a long run: the caller sorts all 63 bits (k64 is untouched)
+  // no read-back here: rank_runs_kernel (and the caller's kernels after it) return at once
+  // when gather_runs_kernel flagged a long run; the caller reads the flag when it next
+  // synchronises and sorts all 63 bits instead
   RT_CUDA(launch_pdl(rank_runs_kernel, (unsigned)((n + kRankThreads - 1) / kRankThreads), kRankThreads,
                      0, s, (const uint64_t*)ws.keys_alt, (const uint32_t*)sidx, (const uint32_t*)sk32,
-                     (uint32_t)n, k64, ws.vals_alt));
+                     (uint32_t)n, k64, ws.vals_alt, (const uint32_t*)long_run));
   RT_LAUNCHED();
-  *keys_out = k64;
-  *vals_out = ws.vals_alt;
-  *used = true;
   return 0;
 }
 

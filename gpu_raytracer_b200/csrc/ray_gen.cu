@@ -136,6 +136,17 @@ shade_kernel(const float4* __restrict__ tris, const float4* __restrict__ rays,
   }
 }
 
+// hits with a primitive (closest hit) or the any-hit marker
+__global__ void __launch_bounds__(256)
+count_hits_kernel(const float4* __restrict__ hits, uint64_t n, unsigned long long* __restrict__ out) {
+  uint32_t c = 0;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (uint64_t)gridDim.x * blockDim.x)
+    c += (__float_as_int(ld_stream(hits + i).w) >= 0) ? 1u : 0u;
+  c = __reduce_add_sync(0xFFFFFFFFu, c);
+  if ((threadIdx.x & 31) == 0 && c) atomicAdd(out, (unsigned long long)c);
+}
+
 inline unsigned grid_for(uint64_t count) {
   uint64_t blocks = (count + 255) / 256;
   uint64_t cap = (uint64_t)num_sms() * 16;
@@ -171,6 +182,13 @@ int launch_gen_ao(const float4* tris, const float4* rays, const float4* hits, ui
   if (n == 0 || spp == 0) return 0;
   ao_kernel<<<grid_for(n), 256, 0, s>>>(tris, rays, hits, n, spp, stream_key(seed, kStreamAO),
                                         radius, out);
+  RT_LAUNCHED();
+  return 0;
+}
+
+int launch_count_hits(const float4* hits, uint64_t n, unsigned long long* out, cudaStream_t s) {
+  if (n == 0) return 0;
+  count_hits_kernel<<<grid_for(n), 256, 0, s>>>(hits, n, out);
   RT_LAUNCHED();
   return 0;
 }

@@ -188,8 +188,9 @@ __global__ void __launch_bounds__(256)
 build_top_kernel(const Continuation* __restrict__ queue, const uint32_t* __restrict__ queue_count,
                  uint32_t capacity, const KeyT* __restrict__ keys, uint32_t n,
                  uint32_t* __restrict__ flags, Node* __restrict__ nodes,
-                 BvhHeader* __restrict__ header) {
+                 BvhHeader* __restrict__ header, const uint32_t* __restrict__ abort_flag) {
   pdl_enter();
+  if (abort_flag != nullptr && *abort_flag != 0u) return;
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   const uint32_t count = min(*queue_count, capacity);
   if (i >= count) return;
@@ -225,10 +226,11 @@ build_walk_kernel(const float4* __restrict__ tris, const uint32_t* __restrict__ 
                   Node* __restrict__ nodes,
                   SortedTri* __restrict__ stris, BvhHeader* __restrict__ header,
                   Continuation* __restrict__ queue, uint32_t* __restrict__ queue_count,
-                  uint32_t capacity) {
+                  uint32_t capacity, const uint32_t* __restrict__ abort_flag) {
   extern __shared__ __align__(16) unsigned char refit_smem_raw[];
   RefitSmem& sm = *reinterpret_cast<RefitSmem*>(refit_smem_raw);
   pdl_enter();
+  if (abort_flag != nullptr && *abort_flag != 0u) return;  // the sort gave up (hybrid order, long run)
   const uint32_t tid = threadIdx.x;
   const uint32_t base = blockIdx.x * kRefitLeaves;
   const uint32_t j = base + tid;
@@ -430,6 +432,66 @@ derive_parents_kernel(const Node* __restrict__ nodes, uint32_t n, int root,
   parent[node_slot_of(__float_as_int(lo1.w), n)] = (g << 2) | local | 1u;
 }
 
+// ---- validation of a BVH that did not come from build_bvh (bvh_load, bvh_commit) --------
+// Everything traversal, refit_bvh and the accessors index with is checked, so a truncated
+// or corrupt file fails with RT_ERR_INVALID instead of faulting the GPU: child ids and leaf
+// positions in range, every node's leaf range [L, R] around its split position, each child's
+// own range equal to its half of the parent's (ranges nest strictly, so the nodes under the
+// root form a finite tree), the root covering [0, n-1], primitive indices below n.
+__global__ void __launch_bounds__(256)
+validate_nodes_kernel(const Node* __restrict__ nodes, const SortedTri* __restrict__ stris, uint32_t n,
+                      int root, uint32_t* __restrict__ bad) {
+  const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+  bool ok = true;
+  if (g < n) ok = __float_as_uint(stris[g].v0p.w) < n;
+  if (g == 0) {
+    if (n == 1) {
+      ok = ok && root == ~0;
+    } else {
+      ok = ok && root >= 0 && (uint32_t)root < n - 1u;
+      if (ok) ok = __float_as_uint(nodes[root].hi0.w) == 0u && __float_as_uint(nodes[root].hi1.w) == n - 1u;
+    }
+  }
+  if (g + 1u < n) {
+    const float4* np = reinterpret_cast<const float4*>(nodes + g);
+    const float4 lo0 = np[0], hi0 = np[1], lo1 = np[2], hi1 = np[3];
+    const uint32_t L = __float_as_uint(hi0.w), R = __float_as_uint(hi1.w);
+    const int c0 = __float_as_int(lo0.w), c1 = __float_as_int(lo1.w);
+    ok = ok && L <= g && g < R && R < n;
+    if (ok) {
+      if (c0 < 0) {
+        ok = (uint32_t)(~c0) == g && L == g;
+      } else {
+        ok = (uint32_t)c0 >= L && (uint32_t)c0 < g;
+        if (ok) ok = __float_as_uint(nodes[c0].hi0.w) == L && __float_as_uint(nodes[c0].hi1.w) == g;
+      }
+    }
+    if (ok) {
+      if (c1 < 0) {
+        ok = (uint32_t)(~c1) == g + 1u && R == g + 1u;
+      } else {
+        ok = (uint32_t)c1 > g && (uint32_t)c1 < R;
+        if (ok) ok = __float_as_uint(nodes[c1].hi0.w) == g + 1u && __float_as_uint(nodes[c1].hi1.w) == R;
+      }
+    }
+  }
+  if (!ok) *bad = 1u;
+}
+// depth: the traversal stacks hold kMaxDepth entries; a tree the build made is at most 95
+// deep (63 key bits + 32 tie-break bits), a file may claim anything
+__global__ void __launch_bounds__(256)
+validate_depth_kernel(const uint32_t* __restrict__ parent, uint32_t n, uint32_t* __restrict__ bad) {
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n) return;
+  uint32_t pw = parent[(n - 1u) + j];
+  int depth = 0;
+  while (pw != kNoParent && depth <= kMaxDepth) {
+    pw = parent[pw >> 2];
+    ++depth;
+  }
+  if (pw != kNoParent) *bad = 1u;
+}
+
 // canonical arrays from the traversal layout (parity accessors T3/T4).  Nodes are
 // stored by split position g; the Karras index of the child in slot s of node g
 // is g + s, the root is Karras node 0, leaves keep n-1+j.
@@ -508,7 +570,8 @@ size_t refit_queue_bytes(uint64_t n) {
 template <typename KeyT>
 static int build_tree_impl(const float4* tris, const uint32_t* sorted_idx, const KeyT* keys,
                            uint64_t n, uint32_t* flags, Node* nodes, SortedTri* stris,
-                           BvhHeader* header, void* queue_buf, cudaStream_t s) {
+                           BvhHeader* header, void* queue_buf, cudaStream_t s,
+                           const uint32_t* abort_flag) {
   const unsigned blocks = (unsigned)((n + kRefitLeaves - 1) / kRefitLeaves);
   const uint32_t capacity = queue_capacity(n);
   uint32_t* queue_count;
@@ -518,11 +581,11 @@ static int build_tree_impl(const float4* tris, const uint32_t* sorted_idx, const
   RT_CUDA(cudaFuncSetAttribute(build_walk_kernel<KeyT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                (int)smem));
   RT_CUDA(launch_pdl(build_walk_kernel<KeyT>, blocks, kRefitLeaves, smem, s, tris, sorted_idx, keys,
-                     (uint32_t)n, flags, nodes, stris, header, queue, queue_count, capacity));
+                     (uint32_t)n, flags, nodes, stris, header, queue, queue_count, capacity, abort_flag));
   RT_LAUNCHED();
   RT_CUDA(launch_pdl(build_top_kernel<KeyT>, (capacity + 255) / 256, 256, 0, s,
                      (const Continuation*)queue, (const uint32_t*)queue_count, capacity, keys,
-                     (uint32_t)n, flags, nodes, header));
+                     (uint32_t)n, flags, nodes, header, abort_flag));
   RT_LAUNCHED();
   return 0;
 }
@@ -542,19 +605,35 @@ int prepare_build_tree(uint64_t n, uint32_t* flags, void* queue_buf, cudaStream_
 
 int launch_build_tree(const float4* tris, const uint32_t* sorted_idx, const void* keys,
                       uint32_t key_bits, uint64_t n, uint32_t* flags, Node* nodes,
-                      SortedTri* stris, BvhHeader* header, void* queue_buf, cudaStream_t s) {
+                      SortedTri* stris, BvhHeader* header, void* queue_buf, cudaStream_t s,
+                      const uint32_t* abort_flag) {
   if (n == 0) return 0;
   if (key_bits == 30)
     return build_tree_impl<uint32_t>(tris, sorted_idx, (const uint32_t*)keys, n, flags, nodes,
-                                     stris, header, queue_buf, s);
+                                     stris, header, queue_buf, s, abort_flag);
   return build_tree_impl<uint64_t>(tris, sorted_idx, (const uint64_t*)keys, n, flags, nodes, stris,
-                                   header, queue_buf, s);
+                                   header, queue_buf, s, abort_flag);
 }
 
 int launch_derive_parents(const Node* nodes, uint64_t n, int root, uint32_t* parent,
                           cudaStream_t s) {
   if (n == 0) return 0;
   derive_parents_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(nodes, (uint32_t)n, root, parent);
+  RT_LAUNCHED();
+  return 0;
+}
+
+int launch_validate(const Node* nodes, const SortedTri* stris, uint64_t n, int root, uint32_t* bad,
+                    cudaStream_t s) {
+  RT_CUDA(cudaMemsetAsync(bad, 0, sizeof(uint32_t), s));
+  if (n == 0) return 0;
+  validate_nodes_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(nodes, stris, (uint32_t)n, root, bad);
+  RT_LAUNCHED();
+  return 0;
+}
+int launch_validate_depth(const uint32_t* parent, uint64_t n, uint32_t* bad, cudaStream_t s) {
+  if (n == 0) return 0;
+  validate_depth_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(parent, (uint32_t)n, bad);
   RT_LAUNCHED();
   return 0;
 }

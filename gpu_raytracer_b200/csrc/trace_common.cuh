@@ -7,7 +7,7 @@
 
 namespace rt {
 
-constexpr int kStack = 96;  // >= 63 key bits + 32 tie-break bits of tree depth
+constexpr int kStack = kMaxDepth;  // >= 63 key bits + 32 tie-break bits of tree depth
 constexpr int kEmpty = (int)0x80000000;
 constexpr float kSlabPad = 1.0000004f;
 constexpr int kTraceThreads = 256;
@@ -30,11 +30,16 @@ __device__ __forceinline__ F8 ldg256(const void* p) {
 struct RayState {
   float ox, oy, oz, tmin;
   float dx, dy, dz;
-  float ix, iy, iz;
+  float ix, iy, iz;  // 1/d; NaN for a direction component that is exactly +-0 (see slab)
   float best_t, bu, bv;
   int best_prim;
 };
 
+// Slab test.  A direction component that is exactly +-0 has ix = NaN: both of its plane
+// distances are then NaN and the NaN-ignoring min/max drop the axis from tnear and tfar,
+// i.e. the axis allows every t, which is what a ray parallel to the slab does when its
+// origin lies between the planes (faces included).  Whether it does is the separate
+// test on_slabs(), run only for rays that have such a component (RayFlags::kZeroDir).
 __device__ __forceinline__ bool slab(const float4 lo, const float4 hi, const RayState& r,
                                      float& tn) {
   const float t0x = (lo.x - r.ox) * r.ix, t1x = (hi.x - r.ox) * r.ix;
@@ -44,6 +49,18 @@ __device__ __forceinline__ bool slab(const float4 lo, const float4 hi, const Ray
   float tf = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fminf(fmaxf(t0z, t1z), r.best_t));
   tf = tf * kSlabPad;
   return tn <= tf;
+}
+// rays with a zero direction component: the origin must lie inside the closed slab of every
+// such axis, lo <= o <= hi (one comparison pair per axis, no rounding involved)
+__device__ __forceinline__ bool on_slabs(float lx, float ly, float lz, float hx, float hy, float hz,
+                                         const RayState& r) {
+  const bool okx = (r.ix == r.ix) || (lx <= r.ox && r.ox <= hx);
+  const bool oky = (r.iy == r.iy) || (ly <= r.oy && r.oy <= hy);
+  const bool okz = (r.iz == r.iz) || (lz <= r.oz && r.oz <= hz);
+  return okx && oky && okz;
+}
+__device__ __forceinline__ bool on_slabs(const float4 lo, const float4 hi, const RayState& r) {
+  return on_slabs(lo.x, lo.y, lo.z, hi.x, hi.y, hi.z, r);
 }
 
 // acceptance rule (A6): closest t in (tmin, best]; on equal t the smaller primitive wins
@@ -144,17 +161,23 @@ __device__ __forceinline__ bool intersect_wt(const SortedTri* __restrict__ stris
   return accept_hit(T * inv, V * inv, W * inv, __float_as_int(v0.w), r);
 }
 
-// fills the ray state from the two float4 of a ray record
-__device__ __forceinline__ void load_ray(RayState& r, const float4 ro, const float4 rd) {
+// 1/d of one direction component; NaN marks a component that is exactly +-0 (slab())
+// otherwise 1/d clamped to +-FLT_MAX, so that a denormal component gives 0 * FLT_MAX = 0, not
+// 0 * inf = NaN, for an origin on a box face
+__device__ __forceinline__ float inv_dir(float d) {
+  const float fmx = 3.402823466e+38f;
+  return d == 0.0f ? __int_as_float(0x7FC00000) : fminf(fmaxf(1.0f / d, -fmx), fmx);
+}
+// fills the ray state from the two float4 of a ray record; returns true when a direction
+// component is exactly zero (the caller then runs on_slabs() next to every slab())
+__device__ __forceinline__ bool load_ray(RayState& r, const float4 ro, const float4 rd) {
   r.ox = ro.x; r.oy = ro.y; r.oz = ro.z; r.tmin = ro.w;
   r.dx = rd.x; r.dy = rd.y; r.dz = rd.z;
-  // 1/d clamped to +-FLT_MAX: 0 * FLT_MAX = 0 instead of 0 * inf = NaN when
-  // the origin lies on a box face and the direction component is zero
-  const float fmx = 3.402823466e+38f;
-  r.ix = fminf(fmaxf(1.0f / rd.x, -fmx), fmx);
-  r.iy = fminf(fmaxf(1.0f / rd.y, -fmx), fmx);
-  r.iz = fminf(fmaxf(1.0f / rd.z, -fmx), fmx);
+  r.ix = inv_dir(rd.x);
+  r.iy = inv_dir(rd.y);
+  r.iz = inv_dir(rd.z);
   r.best_t = rd.w; r.bu = 0.0f; r.bv = 0.0f; r.best_prim = -1;
+  return rd.x == 0.0f || rd.y == 0.0f || rd.z == 0.0f;
 }
 
 __device__ __forceinline__ float4 hit_record(const RayState& r, bool any) {

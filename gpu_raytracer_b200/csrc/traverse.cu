@@ -25,7 +25,8 @@ namespace {
 template <bool ANY, bool STATS, bool WT>
 __device__ __forceinline__ void trace_one(const Node* __restrict__ nodes,
                                           const SortedTri* __restrict__ stris, int root,
-                                          RayState& r, uint32_t& n_nodes, uint32_t& n_tests) {
+                                          RayState& r, const bool zero_dir, uint32_t& n_nodes,
+                                          uint32_t& n_tests) {
   WtRay wr;
   if (WT) wr = wt_setup(r);
   int stack[kStack];
@@ -38,8 +39,12 @@ __device__ __forceinline__ void trace_one(const Node* __restrict__ nodes,
       const F8 c0h = ldg256(nodes + node), c1h = ldg256(&nodes[node].lo1);
       const float4 lo0 = c0h.a, hi0 = c0h.b, lo1 = c1h.a, hi1 = c1h.b;
       float tn0, tn1;
-      const bool h0 = slab(lo0, hi0, r, tn0);
-      const bool h1 = slab(lo1, hi1, r, tn1);
+      bool h0 = slab(lo0, hi0, r, tn0);
+      bool h1 = slab(lo1, hi1, r, tn1);
+      if (zero_dir) {  // rare: a direction component is exactly zero
+        h0 = h0 && on_slabs(lo0, hi0, r);
+        h1 = h1 && on_slabs(lo1, hi1, r);
+      }
       const int c0 = __float_as_int(lo0.w), c1 = __float_as_int(lo1.w);
       if (h0 && h1) {
         const bool swap = tn1 < tn0;
@@ -84,16 +89,8 @@ trace_kernel(const Node* __restrict__ nodes, const SortedTri* __restrict__ stris
     if (i < n_rays) {
       const float4 ro = ld_stream(rays + 2 * i), rd = ld_stream(rays + 2 * i + 1);
       RayState r;
-      r.ox = ro.x; r.oy = ro.y; r.oz = ro.z; r.tmin = ro.w;
-      r.dx = rd.x; r.dy = rd.y; r.dz = rd.z;
-      // 1/d clamped to +-FLT_MAX: 0 * FLT_MAX = 0 instead of 0 * inf = NaN when
-      // the origin lies on a box face and the direction component is zero
-      const float fmx = 3.402823466e+38f;
-      r.ix = fminf(fmaxf(1.0f / rd.x, -fmx), fmx);
-      r.iy = fminf(fmaxf(1.0f / rd.y, -fmx), fmx);
-      r.iz = fminf(fmaxf(1.0f / rd.z, -fmx), fmx);
-      r.best_t = rd.w; r.bu = 0.0f; r.bv = 0.0f; r.best_prim = -1;
-      if (n_tris != 0) trace_one<ANY, STATS, WT>(nodes, stris, root, r, n_nodes, n_tests);
+      const bool zero_dir = load_ray(r, ro, rd);
+      if (n_tris != 0) trace_one<ANY, STATS, WT>(nodes, stris, root, r, zero_dir, n_nodes, n_tests);
       float4 h;
       if (r.best_prim < 0) h = make_float4(inf, 0.0f, 0.0f, __int_as_float(-1));
       else if (ANY) h = make_float4(0.0f, 0.0f, 0.0f, __int_as_float(0x7FFFFFFF));
@@ -184,6 +181,7 @@ trace_kernel_dyn(const Node* __restrict__ nodes, const SortedTri* __restrict__ s
   };
   int node = kEmpty;
   bool has_ray = false;
+  bool zero_dir = false;  // the lane's ray has a direction component that is exactly zero
   unsigned long long my_ray = 0;
   RayState r;
   r.best_prim = -1;
@@ -295,13 +293,7 @@ trace_kernel_dyn(const Node* __restrict__ nodes, const SortedTri* __restrict__ s
         if (!PIPE && perm) my_ray = perm[my_ray];  // RT_TRACE_REORDER: position in key order -> ray
         const float4 ro = PIPE ? ld_cg_f4(rays + 2 * my_ray) : ld_stream(rays + 2 * my_ray);
         const float4 rd = PIPE ? ld_cg_f4(rays + 2 * my_ray + 1) : ld_stream(rays + 2 * my_ray + 1);
-        r.ox = ro.x; r.oy = ro.y; r.oz = ro.z; r.tmin = ro.w;
-        r.dx = rd.x; r.dy = rd.y; r.dz = rd.z;
-        const float fmx = 3.402823466e+38f;
-        r.ix = fminf(fmaxf(1.0f / rd.x, -fmx), fmx);
-        r.iy = fminf(fmaxf(1.0f / rd.y, -fmx), fmx);
-        r.iz = fminf(fmaxf(1.0f / rd.z, -fmx), fmx);
-        r.best_t = rd.w; r.bu = 0.0f; r.bv = 0.0f; r.best_prim = -1;
+        zero_dir = load_ray(r, ro, rd);
         if (WT) wr = wt_setup(r);
         has_ray = true;
         sp = 0;
@@ -328,8 +320,12 @@ trace_kernel_dyn(const Node* __restrict__ nodes, const SortedTri* __restrict__ s
         const F8 c0h = ldg256(nodes + node), c1h = ldg256(&nodes[node].lo1);
         const float4 lo0 = c0h.a, hi0 = c0h.b, lo1 = c1h.a, hi1 = c1h.b;
         float tn0, tn1;
-        const bool h0 = slab(lo0, hi0, r, tn0);
-        const bool h1 = slab(lo1, hi1, r, tn1);
+        bool h0 = slab(lo0, hi0, r, tn0);
+        bool h1 = slab(lo1, hi1, r, tn1);
+        if (zero_dir) {  // rare: a direction component is exactly zero
+          h0 = h0 && on_slabs(lo0, hi0, r);
+          h1 = h1 && on_slabs(lo1, hi1, r);
+        }
         const int c0 = __float_as_int(lo0.w), c1 = __float_as_int(lo1.w);
         if (h0 && h1) {
           const bool swap = tn1 < tn0;
@@ -487,8 +483,13 @@ int launch_trace(const Node* nodes, const SortedTri* stris, uint64_t n_tris, int
     const int refill_min = p.trace_refill_min > 0 ? p.trace_refill_min : (any ? 16 : 8);
     const int leaf_min = p.trace_leaf_min > 0 ? p.trace_leaf_min : 8;
     if (pipe) {
-      // 32-ray chunks: when a piece arrives every resident warp gets a share of it
+      // 32-ray chunks: when a piece arrives every resident warp gets a share of it.  The
+      // segment accounting needs chunks that never straddle a segment: a power of two
+      // not above the segment size (a caller-set "trace.chunk" is rounded down to one)
       if (p.trace_chunk <= 0) chunk = 32;
+      int pow2 = 1;
+      while (pow2 * 2 <= chunk && pow2 * 2 <= (1 << pipe->seg_shift)) pow2 *= 2;
+      chunk = pow2;
 #define RT_TRACE_PIPE(A, W)                                                          \
   trace_kernel_dyn<A, false, W, true, 0><<<(unsigned)blocks, kTraceThreads, 0, s>>>( \
       nodes, stris, (uint32_t)n_tris, root, rays, n_rays, hits, ray_counter, stats, chunk, refill_min, leaf_min, *pipe, nullptr)

@@ -3,13 +3,23 @@ from __future__ import annotations
 
 import numpy as np
 
+# 8-bit code of a linear value c in [0, 1] with display gamma 2.2: round(c^(1/2.2) * 255).
+# Written as a search in 255 thresholds, t_v = ((v - 0.5) / 255)^2.2, so that the code of a
+# float32 input does not depend on the platform's powf: code = number of thresholds <= c.
+_THRESHOLDS = ((np.arange(1, 256, dtype=np.float64) - 0.5) / 255.0) ** 2.2
+
+
+def quantize(rgb) -> np.ndarray:
+    """uint8 codes of linear float values (any shape); NaN and negatives give 0."""
+    a = np.nan_to_num(np.asarray(rgb, dtype=np.float32), nan=0.0).astype(np.float64)
+    return np.searchsorted(_THRESHOLDS, np.clip(a, 0.0, 1.0), side="right").astype(np.uint8)
+
 
 def write_ppm(path: str, rgb, width: int, height: int) -> None:
     """rgb: [height*width, 3] floats in [0, 1] (numpy or torch, any device)."""
     if hasattr(rgb, "detach"):
         rgb = rgb.detach().cpu().numpy()
-    a = np.clip(np.asarray(rgb, dtype=np.float32).reshape(height, width, 3), 0.0, 1.0)
-    a = (a ** (1.0 / 2.2) * 255.0 + 0.5).astype(np.uint8)
+    a = quantize(np.asarray(rgb, dtype=np.float32).reshape(height, width, 3))
     with open(path, "wb") as f:
         f.write(f"P6\n{width} {height}\n255\n".encode())
         f.write(a.tobytes())

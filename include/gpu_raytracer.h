@@ -138,6 +138,14 @@ RT_API const char* bvh_last_error(void);
 RT_API int trace_rays_async(const rt_bvh* h, const float* rays, uint64_t n_rays, uint32_t flags,
                      float* hits, void* stream);
 
+/* Primary rays [first, first+count) of a width x height pinhole image (cam: host, 12 floats as
+ * for rt_gen_primary_rays) are generated on the device and traced; only the hits cross the
+ * bus.  hits: [host|device] count x 4 floats.  Same bytes as rt_gen_primary_rays followed by
+ * trace_rays; what it saves is the 32 B/ray upload (rays are "generated
+ * on device from a seed, never copied from host at scale"). */
+RT_API int trace_camera(const rt_bvh* h, const float* cam, uint32_t width, uint32_t height,
+                        uint64_t first, uint64_t count, uint32_t flags, float* hits);
+
 /* Like trace_rays on device buffers, and also counts the work done: counters[0]
  * = internal nodes fetched (64 B each), counters[1] = triangles tested (48 B
  * each); these give the algorithmic bytes per ray of SURVEY.md §8(d).  Slower
@@ -184,8 +192,44 @@ RT_API int bvh_device_buffers(const rt_bvh* h, void** ptrs, uint64_t* bytes);
 /* Allocates a handle with uninitialised buffers of the right size for n_tris,
  * to be filled through bvh_device_buffers (receiver side of the broadcast). */
 RT_API int bvh_alloc_empty(uint64_t n_tris, uint32_t key_bits, rt_bvh** out);
-/* Re-reads the header buffer after it was filled by a broadcast. */
+/* Re-reads the header buffer after it was filled by a broadcast, and validates what arrived
+ * (child ids, leaf ranges, root, primitive indices, depth): RT_ERR_INVALID for buffers that
+ * do not hold a tree the traversal can walk. */
 RT_API int bvh_commit(rt_bvh* h);
+
+/* Single-process multi-GPU (SURVEY.md §8b "Multi-GPU entry takes a device list", §8e): one
+ * host thread per device inside the library, no collective on the data path.
+ *
+ * rt_shard_range: [first, first+count) of rank's contiguous share of n rays; shares are cut
+ * at multiples of 32 rays, tile [0, n) exactly and differ by less than two granules.
+ *
+ * build_bvh_multi: one ordinary handle per entry of devices[] (out: n_devices pointers, all
+ * NULL on failure).  RT_MULTI_REDUNDANT: every device runs build_bvh on tris.
+ * RT_MULTI_BROADCAST: devices[0] builds, the others receive nodes + reordered triangles +
+ * header by cudaMemcpyPeerAsync (NVLink where the devices are peers).  tris: host, or device
+ * memory of any one device (peers get a temporary copy).  opts->device and opts->stream are
+ * ignored.  The same device may appear twice (two shards on one GPU).
+ *
+ * trace_rays_sharded: rays and hits are HOST buffers holding the whole batch; handle i
+ * traces share i (rt_shard_range(n_rays, i, n_devices)) through trace_rays, all devices at
+ * once.  Byte-identical to one trace_rays call on the whole batch.
+ *
+ * trace_random_sharded: config 5: rays first..first+n_rays of the
+ * rt_gen_random_rays sequence (box, seed) are generated on the devices, batch rays at a time
+ * (0 = 32M), share i on handle i, and traced with flags (RT_TRACE_REORDER allowed).  hits:
+ * host buffer for all n_rays hits, or NULL to keep them on the devices' scratch only;
+ * n_hit[i]: rays of share i that hit; trace_ms[i]: device time of share i's traversal
+ * (CUDA events, ray generation excluded).  n_hit and trace_ms may be NULL. */
+#define RT_MULTI_REDUNDANT 0
+#define RT_MULTI_BROADCAST 1
+RT_API int rt_shard_range(uint64_t n, int rank, int world, uint64_t* first, uint64_t* count);
+RT_API int build_bvh_multi(const float* tris, uint64_t n_tris, const rt_build_opts* opts,
+                           const int* devices, int n_devices, int strategy, rt_bvh** out);
+RT_API int trace_rays_sharded(rt_bvh* const* handles, int n_devices, const float* rays, uint64_t n_rays,
+                              uint32_t flags, float* hits);
+RT_API int trace_random_sharded(rt_bvh* const* handles, int n_devices, const float* box, uint64_t seed,
+                                uint64_t first, uint64_t n_rays, uint32_t flags, uint64_t batch,
+                                float* hits, uint64_t* n_hit, float* trace_ms);
 
 /* ---- scene input and BVH files --------------------- */
 
@@ -200,7 +244,9 @@ RT_API int rt_load_tris(const char* path, float** tris_out, uint64_t* n_out);
 RT_API void rt_free_host(void* p);
 /* A built BVH as a file (header, node array, reordered triangles) and back, on the
  * current device; a loaded handle traces exactly like the one that was saved.  The
- * optional BVH4 is not stored: call bvh_widen after bvh_load. */
+ * optional BVH4 is not stored: call bvh_widen after bvh_load.  bvh_load checks the file's
+ * length and validates the tree like bvh_commit: a truncated or corrupt file is
+ * RT_ERR_INVALID, never a device fault. */
 RT_API int bvh_save(const rt_bvh* h, const char* path);
 RT_API int bvh_load(const char* path, rt_bvh** out);
 
@@ -232,7 +278,14 @@ RT_API int rt_shade(const float* tris, const float* rays, const float* hits, con
 RT_API int rt_device_count(void);
 /* number of CUDA kernels this library has launched in this process */
 RT_API uint64_t rt_kernel_launches(void);
-/* tuning knobs for experiments (process-wide): "sort.variant", "sort.bits",
+/* Gives the memory the library keeps cached in its own stream-ordered pool (build and trace
+ * temporaries, freed handles) back to the driver; device -1 = every device used so far.
+ * Live handles are not touched.  Synchronises the device. */
+RT_API int rt_trim(int device);
+/* tuning knobs (process-wide, atomic: a knob may be changed while other host threads build
+ * or trace; a call reads each knob once, so the change applies to that call or the next):
+ * "pool.keep_mb" (memory the pool keeps cached per device between calls; 0, the default,
+ * keeps everything, which makes repeated builds allocation-free), "sort.variant", "sort.bits",
  * "trace.variant", "trace.blocks_per_sm", "trace.chunk", "trace.refill_min", "trace.leaf_min",
  * "trace.wide", "wide.leaf_max", "trace.streamed" (0 = always stage host batches),
  * "trace.stage_chunk", "trace.zero_copy", "trace.sh_stack" (0 | 8 | 16 | 24 stack levels in

@@ -64,8 +64,11 @@ def lib() -> C.CDLL:
         L.orc_gen_primary_rays.argtypes = [vp, u32, u32, u64, u64, vp]
         L.orc_gen_random_rays.argtypes = [vp, u64, u64, u64, vp]
         L.orc_gen_ao_rays.argtypes = [vp, vp, vp, u64, u32, u64, C.c_float, vp]
+        L.orc_shade.argtypes = [vp, vp, vp, vp, u64, u32, vp]
         L.orc_build.argtypes = [vp, u64, u32]
         L.orc_build.restype = vp
+        L.orc_build_borrow.argtypes = [vp, u64, u32]
+        L.orc_build_borrow.restype = vp
         L.orc_free.argtypes = [vp]
         L.orc_read.argtypes = [vp] * 8
         L.orc_build_times.argtypes = [vp, vp]
@@ -138,31 +141,57 @@ def gen_ao_rays(tris: np.ndarray, rays: np.ndarray, hits: np.ndarray, spp: int, 
     return out
 
 
+def shade(tris: np.ndarray, rays: np.ndarray, hits: np.ndarray, ao_hits=None, spp: int = 0) -> np.ndarray:
+    """§8(f).1: grey = |n.d| * (1 - occluded/spp), float32 [n, 3]; tris in original order."""
+    tris = np.ascontiguousarray(tris, dtype=np.float32)
+    rays = np.ascontiguousarray(rays, dtype=np.float32).reshape(-1, 8)
+    hits = np.ascontiguousarray(hits, dtype=np.float32).reshape(-1, 4)
+    n = rays.shape[0]
+    out = np.empty((n, 3), dtype=np.float32)
+    if ao_hits is not None and spp:
+        ao_hits = np.ascontiguousarray(ao_hits, dtype=np.float32).reshape(-1, 4)
+        assert ao_hits.shape[0] == n * spp
+    lib().orc_shade(_p(tris), _p(rays), _p(hits), _p(ao_hits) if ao_hits is not None and spp else None,
+                    n, spp if ao_hits is not None else 0, _p(out))
+    return out
+
+
 class OracleBvh:
     """Result of the oracle's build: canonical arrays."""
 
-    def __init__(self, tris: np.ndarray, key_bits: int = 30):
+    def __init__(self, tris: np.ndarray, key_bits: int = 30, lazy: bool = False):
+        """lazy=True (the 100M-triangle test): the oracle borrows ``tris`` instead of copying
+        it, and the result arrays are fetched one at a time with ``read(name)``."""
         tris = np.ascontiguousarray(tris, dtype=np.float32).reshape(-1, 12)
         self.n = int(tris.shape[0])
         self.key_bits = key_bits
         self._tris = tris
-        self._h = lib().orc_build(_p(tris), self.n, key_bits)
+        self._h = (lib().orc_build_borrow if lazy else lib().orc_build)(_p(tris), self.n, key_bits)
         if not self._h:
             raise ValueError("orc_build failed")
-        n = self.n
-        nodes = max(2 * n - 1, 0)
-        self.keys = np.empty(n, dtype=np.uint64)
-        self.idx = np.empty(n, dtype=np.uint32)
-        self.left = np.empty(max(n - 1, 0), dtype=np.uint32)
-        self.right = np.empty(max(n - 1, 0), dtype=np.uint32)
-        self.parent = np.empty(nodes, dtype=np.uint32)
-        self.boxes = np.empty((nodes, 6), dtype=np.float32)
-        self.bounds = np.zeros(6, dtype=np.float32)
-        lib().orc_read(self._h, _p(self.keys), _p(self.idx), _p(self.left), _p(self.right),
-                       _p(self.parent), _p(self.boxes), _p(self.bounds))
         t = np.zeros(4, dtype=np.float64)
         lib().orc_build_times(self._h, _p(t))
         self.times = dict(morton=t[0], sort=t[1], topology=t[2], refit=t[3], total=float(t.sum()))
+        if lazy:
+            return
+        for name in self._ARRAYS:
+            setattr(self, name, self.read(name))
+
+    _ARRAYS = ("keys", "idx", "left", "right", "parent", "boxes", "bounds")
+
+    def read(self, name: str) -> np.ndarray:
+        """One result array of the build (a fresh numpy copy)."""
+        n = self.n
+        nodes = max(2 * n - 1, 0)
+        shape, dtype = {"keys": ((n,), np.uint64), "idx": ((n,), np.uint32),
+                        "left": ((max(n - 1, 0),), np.uint32), "right": ((max(n - 1, 0),), np.uint32),
+                        "parent": ((nodes,), np.uint32), "boxes": ((nodes, 6), np.float32),
+                        "bounds": ((6,), np.float32)}[name]
+        out = np.zeros(shape, dtype=dtype)
+        args = [None] * 7
+        args[self._ARRAYS.index(name)] = _p(out)
+        lib().orc_read(self._h, *args)
+        return out
 
     def trace(self, rays: np.ndarray, flags: int = TRACE_CLOSEST, counters: bool = False):
         rays = np.ascontiguousarray(rays, dtype=np.float32).reshape(-1, 8)

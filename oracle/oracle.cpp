@@ -355,7 +355,8 @@ struct Bvh {
   uint64_t n = 0;
   uint32_t key_bits = 30;  // 30 or 63
   float smin[3] = {0, 0, 0}, smax[3] = {0, 0, 0};
-  std::vector<float> tris;       // copy of the input, 12 floats per triangle
+  std::vector<float> tris;       // copy of the input, 12 floats per triangle (empty when borrowed)
+  const float* T = nullptr;      // the triangles: tris.data(), or the caller's array (orc_build_borrow)
   std::vector<uint64_t> keys;    // sorted Morton codes
   std::vector<uint32_t> idx;     // sorted primitive indices
   std::vector<uint32_t> left, right;  // per internal node, canonical ids
@@ -385,7 +386,7 @@ inline int delta(const Bvh& b, int64_t i, int64_t j) {
 
 void build(Bvh& b) {
   const uint64_t n = b.n;
-  const float* T = b.tris.data();
+  const float* T = b.T;
   double t0 = now_s();
   // A1: scene bounds over all vertices
   if (n) {
@@ -584,6 +585,11 @@ inline bool accept(float t, int32_t prim, float tmin, float best_t, int32_t best
 
 const float kSlabPad = 1.0000004f;  // 1 + 3 ulp: keeps the slab test conservative
 
+// idir[k] is NaN for a direction component that is exactly +-0: both plane distances of
+// that axis are then NaN and the NaN-ignoring min/max leave the axis out of tnear/tfar (a
+// ray parallel to a slab is inside it for every t or for none); which of the two is the
+// closed-interval test lo <= o <= hi below.  (A clamped 1/d, as the first version had it,
+// gives 0 * FLT_MAX = 0 for an origin ON a face and culled nodes the ray does enter.)
 inline bool slab(const float* bx, const Ray& r, const float idir[3], float best_t, float& tn) {
   float t0x = (bx[0] - r.o[0]) * idir[0], t1x = (bx[3] - r.o[0]) * idir[0];
   float t0y = (bx[1] - r.o[1]) * idir[1], t1y = (bx[4] - r.o[1]) * idir[1];
@@ -591,7 +597,18 @@ inline bool slab(const float* bx, const Ray& r, const float idir[3], float best_
   tn = nmax(nmax(nmin(t0x, t1x), nmin(t0y, t1y)), nmax(nmin(t0z, t1z), r.tmin));
   float tf = nmin(nmin(nmax(t0x, t1x), nmax(t0y, t1y)), nmin(nmax(t0z, t1z), best_t));
   tf = tf * kSlabPad;
-  return tn <= tf;
+  if (!(tn <= tf)) return false;
+  for (int k = 0; k < 3; ++k)
+    if (idir[k] != idir[k] && !(bx[k] <= r.o[k] && r.o[k] <= bx[3 + k])) return false;
+  return true;
+}
+
+// 1/d: NaN for an exact zero, else clamped to +-FLT_MAX (a denormal component then gives
+// 0 * FLT_MAX = 0, not 0 * inf = NaN, for an origin on a box face)
+inline float inv_dir(float d) {
+  const float fmx = std::numeric_limits<float>::max();
+  if (d == 0.0f) return std::numeric_limits<float>::quiet_NaN();
+  return nmin(nmax(1.0f / d, -fmx), fmx);
 }
 
 enum { TRACE_CLOSEST = 0, TRACE_ANY = 1, TRACE_WATERTIGHT = 2 };
@@ -606,11 +623,7 @@ Hit trace_one(const Bvh& b, const Ray& r, uint32_t flags, uint64_t& nodes, uint6
   float best_t = r.tmax;
   int32_t best_prim = -1;
   float bu = 0, bv = 0;
-  // 1/d clamped to +-FLT_MAX: a zero direction component then gives 0 * FLT_MAX
-  // = 0 (not 0 * inf = NaN) for a ray origin lying on a box face
-  const float fmx = std::numeric_limits<float>::max();
-  const float idir[3] = {nmin(nmax(1.0f / r.d[0], -fmx), fmx), nmin(nmax(1.0f / r.d[1], -fmx), fmx),
-                         nmin(nmax(1.0f / r.d[2], -fmx), fmx)};
+  const float idir[3] = {inv_dir(r.d[0]), inv_dir(r.d[1]), inv_dir(r.d[2])};
   const uint32_t leaf0 = (uint32_t)(n - 1);
   uint32_t stack[128];
   int sp = 0;
@@ -624,7 +637,7 @@ Hit trace_one(const Bvh& b, const Ray& r, uint32_t flags, uint64_t& nodes, uint6
       uint32_t prim = b.idx[node - leaf0];
       float t, u, v;
       ++tests;
-      const float* tp = &b.tris[(uint64_t)prim * 12];
+      const float* tp = b.T + (uint64_t)prim * 12;
       if ((wt ? tri_test_wt(tp, r, wr, t, u, v) : tri_test(tp, r, t, u, v)) &&
           accept(t, (int32_t)prim, r.tmin, best_t, best_prim)) {
         best_t = t; best_prim = (int32_t)prim; bu = u; bv = v;
@@ -784,12 +797,59 @@ ORC_API void orc_gen_ao_rays(const float* tris, const float* rays, const float* 
   }
 }
 
+// §8(f).1 shading: grey = |n.d| * (1 - occluded/spp) with the geometric normal of the hit
+// triangle (ORIGINAL triangle order), misses black; ao_hits may be NULL (spp = 0).  Same
+// operation order as the product's shade kernel, so the comparison is bit for bit.
+ORC_API void orc_shade(const float* tris, const float* rays, const float* hits, const float* ao_hits,
+                       uint64_t n, uint32_t spp, float* rgb) {
+#pragma omp parallel for schedule(static)
+  for (int64_t i = 0; i < (int64_t)n; ++i) {
+    const float* r = rays + (uint64_t)i * 8;
+    int32_t prim;
+    std::memcpy(&prim, hits + (uint64_t)i * 4 + 3, 4);
+    float c = 0.0f;
+    if (prim >= 0) {
+      const float* p = tris + (uint64_t)prim * 12;
+      float e1[3] = {p[4] - p[0], p[5] - p[1], p[6] - p[2]};
+      float e2[3] = {p[8] - p[0], p[9] - p[1], p[10] - p[2]};
+      float nrm[3] = {fmaf(e1[1], e2[2], -(e1[2] * e2[1])), fmaf(e1[2], e2[0], -(e1[0] * e2[2])),
+                      fmaf(e1[0], e2[1], -(e1[1] * e2[0]))};
+      normalize3(nrm);
+      float dn = fmaf(nrm[0], r[4], fmaf(nrm[1], r[5], nrm[2] * r[6]));
+      if (dn > 0.0f) { nrm[0] = -nrm[0]; nrm[1] = -nrm[1]; nrm[2] = -nrm[2]; }
+      c = std::fabs(fmaf(nrm[0], r[4], fmaf(nrm[1], r[5], nrm[2] * r[6])));
+      if (ao_hits && spp > 0) {
+        uint32_t occ = 0;
+        for (uint32_t s = 0; s < spp; ++s) {
+          int32_t ap;
+          std::memcpy(&ap, ao_hits + ((uint64_t)i * spp + s) * 4 + 3, 4);
+          occ += ap >= 0 ? 1u : 0u;
+        }
+        c = c * (1.0f - (float)occ / (float)spp);
+      }
+    }
+    rgb[3 * i + 0] = c; rgb[3 * i + 1] = c; rgb[3 * i + 2] = c;
+  }
+}
+
 ORC_API void* orc_build(const float* tris, uint64_t n, uint32_t key_bits) {
   if (key_bits != 30 && key_bits != 63) return nullptr;
   Bvh* b = new Bvh;
   b->n = n;
   b->key_bits = key_bits;
   b->tris.assign(tris, tris + n * 12);
+  b->T = b->tris.data();
+  build(*b);
+  return b;
+}
+// the same build without the copy of the triangles: the caller keeps `tris` alive until
+// orc_free (the 100M-triangle parity test: 4.8 GB less)
+ORC_API void* orc_build_borrow(const float* tris, uint64_t n, uint32_t key_bits) {
+  if (key_bits != 30 && key_bits != 63) return nullptr;
+  Bvh* b = new Bvh;
+  b->n = n;
+  b->key_bits = key_bits;
+  b->T = tris;
   build(*b);
   return b;
 }

@@ -6,6 +6,7 @@ oracle or to the kernels that alters any byte fails tests/test_golden.py.  They
 travel to the GPU box, where the CUDA path is compared with them directly.
 
     python tests/golden/make_golden.py        # rewrites the fixtures
+    python tests/golden/make_golden.py frame  # only cornell_96_frame.json (§8f.1 image)
 """
 import hashlib
 import os
@@ -39,7 +40,43 @@ def build_fixture(name, tris, key_bits, rays, extra=None):
     print(name, b.n, "tris", rays.shape[0], "rays", int((O.hit_prims(hits) >= 0).sum()), "hits")
 
 
+def cornell_frame(width=96, height=96, spp=4, seed=2):
+    """§8(f).1: Cornell box, primary rays -> AO rays -> any-hit -> shade, all by the oracle.
+    Returns (rgb float32 [w*h, 3], radius)."""
+    cam = camera.cornell_camera(width, height)
+    tris = O.gen_scene(O.SCENE_CORNELL)
+    b = O.OracleBvh(tris)
+    rays = O.gen_primary_rays(cam, width, height)
+    hits = b.trace(rays)
+    radius = np.float32(0.05) * np.float32(np.linalg.norm(b.bounds[3:] - b.bounds[:3]))
+    ao = O.gen_ao_rays(tris, rays, hits, spp, seed, float(radius))
+    occ = b.trace(ao, O.TRACE_ANY)
+    return O.shade(tris, rays, hits, occ, spp), float(radius)
+
+
+def frame_fixture():
+    import json
+    import tempfile
+    from gpu_raytracer_b200 import image
+    rgb, radius = cornell_frame()
+    with tempfile.TemporaryDirectory() as d:
+        path = os.path.join(d, "f.ppm")
+        image.write_ppm(path, rgb, 96, 96)
+        ppm = open(path, "rb").read()
+    out = {"width": 96, "height": 96, "spp": 4, "seed": 2, "radius": radius,
+           "rgb_sha256": hashlib.sha256(rgb.tobytes()).hexdigest(),
+           "ppm_bytes": len(ppm), "ppm_sha256": hashlib.sha256(ppm).hexdigest(),
+           "mean": float(rgb.mean())}
+    with open(os.path.join(HERE, "cornell_96_frame.json"), "w") as f:
+        json.dump(out, f, indent=1)
+    print("cornell_96_frame", out)
+
+
 def main():
+    if sys.argv[1:] == ["frame"]:
+        frame_fixture()
+        return
+    frame_fixture()
     # config 1, reduced image: Cornell box, 96 x 96 primary rays
     cam = camera.cornell_camera(96, 96)
     tris = O.gen_scene(O.SCENE_CORNELL)
