@@ -30,37 +30,48 @@ __device__ __forceinline__ F8 ldg256(const void* p) {
 struct RayState {
   float ox, oy, oz, tmin;
   float dx, dy, dz;
-  float ix, iy, iz;  // 1/d; NaN for a direction component that is exactly +-0 (see slab)
+  float ix, iy, iz;  // 1/d clamped to +-FLT_MAX; +inf for a component that is exactly +-0
   float best_t, bu, bv;
   int best_prim;
 };
 
-// Slab test.  A direction component that is exactly +-0 has ix = NaN: both of its plane
-// distances are then NaN and the NaN-ignoring min/max drop the axis from tnear and tfar,
-// i.e. the axis allows every t, which is what a ray parallel to the slab does when its
-// origin lies between the planes (faces included).  Whether it does is the separate
-// test on_slabs(), run only for rays that have such a component (RayFlags::kZeroDir).
-__device__ __forceinline__ bool slab(const float4 lo, const float4 hi, const RayState& r,
-                                     float& tn) {
-  const float t0x = (lo.x - r.ox) * r.ix, t1x = (hi.x - r.ox) * r.ix;
-  const float t0y = (lo.y - r.oy) * r.iy, t1y = (hi.y - r.oy) * r.iy;
-  const float t0z = (lo.z - r.oz) * r.iz, t1z = (hi.z - r.oz) * r.iz;
-  tn = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), r.tmin));
-  float tf = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fminf(fmaxf(t0z, t1z), r.best_t));
+// min / max that PROPAGATE a NaN operand (min.NaN.f32 / max.NaN.f32: FMNMX.NAN), where
+// fminf / fmaxf return the other operand
+__device__ __forceinline__ float min_nan(float a, float b) {
+  float r;
+  asm("min.NaN.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b));
+  return r;
+}
+__device__ __forceinline__ float max_nan(float a, float b) {
+  float r;
+  asm("max.NaN.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b));
+  return r;
+}
+
+// Slab test.  The two plane distances of an axis are combined with NaN-PROPAGATING min/max,
+// the three axes (and tmin / best_t) with NaN-IGNORING ones.  A direction component that is
+// exactly +-0 has ix = +inf, so its plane distances are -inf, +inf or, for an origin exactly ON
+// the plane, 0 * inf = NaN:
+//   origin strictly between the planes  (-inf, +inf): the axis allows every t
+//   origin on a plane                   a NaN: the axis drops out of tnear and tfar, i.e. it
+//                                       allows every t as well (the slab is closed)
+//   origin outside                      (-inf, -inf) or (+inf, +inf): tfar = -inf or tnear = +inf
+// which is the exact answer for a ray parallel to the slab, at the instruction count of the
+// plain test and with no per-ray flag.  (The first version clamped 1/0 to FLT_MAX: the
+// on-plane distance became 0 * FLT_MAX = 0 and the node was culled.)  Non-zero components
+// never produce a NaN: ix is clamped to +-FLT_MAX and the inputs are finite.
+__device__ __forceinline__ bool slab(float lx, float ly, float lz, float hx, float hy, float hz,
+                                     const RayState& r, float& tn) {
+  const float t0x = (lx - r.ox) * r.ix, t1x = (hx - r.ox) * r.ix;
+  const float t0y = (ly - r.oy) * r.iy, t1y = (hy - r.oy) * r.iy;
+  const float t0z = (lz - r.oz) * r.iz, t1z = (hz - r.oz) * r.iz;
+  tn = fmaxf(fmaxf(min_nan(t0x, t1x), min_nan(t0y, t1y)), fmaxf(min_nan(t0z, t1z), r.tmin));
+  float tf = fminf(fminf(max_nan(t0x, t1x), max_nan(t0y, t1y)), fminf(max_nan(t0z, t1z), r.best_t));
   tf = tf * kSlabPad;
   return tn <= tf;
 }
-// rays with a zero direction component: the origin must lie inside the closed slab of every
-// such axis, lo <= o <= hi (one comparison pair per axis, no rounding involved)
-__device__ __forceinline__ bool on_slabs(float lx, float ly, float lz, float hx, float hy, float hz,
-                                         const RayState& r) {
-  const bool okx = (r.ix == r.ix) || (lx <= r.ox && r.ox <= hx);
-  const bool oky = (r.iy == r.iy) || (ly <= r.oy && r.oy <= hy);
-  const bool okz = (r.iz == r.iz) || (lz <= r.oz && r.oz <= hz);
-  return okx && oky && okz;
-}
-__device__ __forceinline__ bool on_slabs(const float4 lo, const float4 hi, const RayState& r) {
-  return on_slabs(lo.x, lo.y, lo.z, hi.x, hi.y, hi.z, r);
+__device__ __forceinline__ bool slab(const float4 lo, const float4 hi, const RayState& r, float& tn) {
+  return slab(lo.x, lo.y, lo.z, hi.x, hi.y, hi.z, r, tn);
 }
 
 // acceptance rule (A6): closest t in (tmin, best]; on equal t the smaller primitive wins
@@ -161,23 +172,21 @@ __device__ __forceinline__ bool intersect_wt(const SortedTri* __restrict__ stris
   return accept_hit(T * inv, V * inv, W * inv, __float_as_int(v0.w), r);
 }
 
-// 1/d of one direction component; NaN marks a component that is exactly +-0 (slab())
-// otherwise 1/d clamped to +-FLT_MAX, so that a denormal component gives 0 * FLT_MAX = 0, not
-// 0 * inf = NaN, for an origin on a box face
+// 1/d of one direction component, clamped to +-FLT_MAX so that a denormal component gives
+// 0 * FLT_MAX = 0, not 0 * inf = NaN, for an origin on a box face; +inf for a component that is
+// exactly +-0, which slab() treats as a ray parallel to the slab
 __device__ __forceinline__ float inv_dir(float d) {
   const float fmx = 3.402823466e+38f;
-  return d == 0.0f ? __int_as_float(0x7FC00000) : fminf(fmaxf(1.0f / d, -fmx), fmx);
+  return d == 0.0f ? __int_as_float(0x7F800000) : fminf(fmaxf(1.0f / d, -fmx), fmx);
 }
-// fills the ray state from the two float4 of a ray record; returns true when a direction
-// component is exactly zero (the caller then runs on_slabs() next to every slab())
-__device__ __forceinline__ bool load_ray(RayState& r, const float4 ro, const float4 rd) {
+// fills the ray state from the two float4 of a ray record
+__device__ __forceinline__ void load_ray(RayState& r, const float4 ro, const float4 rd) {
   r.ox = ro.x; r.oy = ro.y; r.oz = ro.z; r.tmin = ro.w;
   r.dx = rd.x; r.dy = rd.y; r.dz = rd.z;
   r.ix = inv_dir(rd.x);
   r.iy = inv_dir(rd.y);
   r.iz = inv_dir(rd.z);
   r.best_t = rd.w; r.bu = 0.0f; r.bv = 0.0f; r.best_prim = -1;
-  return rd.x == 0.0f || rd.y == 0.0f || rd.z == 0.0f;
 }
 
 __device__ __forceinline__ float4 hit_record(const RayState& r, bool any) {

@@ -25,8 +25,7 @@ namespace {
 template <bool ANY, bool STATS, bool WT>
 __device__ __forceinline__ void trace_one(const Node* __restrict__ nodes,
                                           const SortedTri* __restrict__ stris, int root,
-                                          RayState& r, const bool zero_dir, uint32_t& n_nodes,
-                                          uint32_t& n_tests) {
+                                          RayState& r, uint32_t& n_nodes, uint32_t& n_tests) {
   WtRay wr;
   if (WT) wr = wt_setup(r);
   int stack[kStack];
@@ -39,12 +38,8 @@ __device__ __forceinline__ void trace_one(const Node* __restrict__ nodes,
       const F8 c0h = ldg256(nodes + node), c1h = ldg256(&nodes[node].lo1);
       const float4 lo0 = c0h.a, hi0 = c0h.b, lo1 = c1h.a, hi1 = c1h.b;
       float tn0, tn1;
-      bool h0 = slab(lo0, hi0, r, tn0);
-      bool h1 = slab(lo1, hi1, r, tn1);
-      if (zero_dir) {  // rare: a direction component is exactly zero
-        h0 = h0 && on_slabs(lo0, hi0, r);
-        h1 = h1 && on_slabs(lo1, hi1, r);
-      }
+      const bool h0 = slab(lo0, hi0, r, tn0);
+      const bool h1 = slab(lo1, hi1, r, tn1);
       const int c0 = __float_as_int(lo0.w), c1 = __float_as_int(lo1.w);
       if (h0 && h1) {
         const bool swap = tn1 < tn0;
@@ -89,8 +84,8 @@ trace_kernel(const Node* __restrict__ nodes, const SortedTri* __restrict__ stris
     if (i < n_rays) {
       const float4 ro = ld_stream(rays + 2 * i), rd = ld_stream(rays + 2 * i + 1);
       RayState r;
-      const bool zero_dir = load_ray(r, ro, rd);
-      if (n_tris != 0) trace_one<ANY, STATS, WT>(nodes, stris, root, r, zero_dir, n_nodes, n_tests);
+      load_ray(r, ro, rd);
+      if (n_tris != 0) trace_one<ANY, STATS, WT>(nodes, stris, root, r, n_nodes, n_tests);
       float4 h;
       if (r.best_prim < 0) h = make_float4(inf, 0.0f, 0.0f, __int_as_float(-1));
       else if (ANY) h = make_float4(0.0f, 0.0f, 0.0f, __int_as_float(0x7FFFFFFF));
@@ -181,7 +176,6 @@ trace_kernel_dyn(const Node* __restrict__ nodes, const SortedTri* __restrict__ s
   };
   int node = kEmpty;
   bool has_ray = false;
-  bool zero_dir = false;  // the lane's ray has a direction component that is exactly zero
   unsigned long long my_ray = 0;
   RayState r;
   r.best_prim = -1;
@@ -293,7 +287,7 @@ trace_kernel_dyn(const Node* __restrict__ nodes, const SortedTri* __restrict__ s
         if (!PIPE && perm) my_ray = perm[my_ray];  // RT_TRACE_REORDER: position in key order -> ray
         const float4 ro = PIPE ? ld_cg_f4(rays + 2 * my_ray) : ld_stream(rays + 2 * my_ray);
         const float4 rd = PIPE ? ld_cg_f4(rays + 2 * my_ray + 1) : ld_stream(rays + 2 * my_ray + 1);
-        zero_dir = load_ray(r, ro, rd);
+        load_ray(r, ro, rd);
         if (WT) wr = wt_setup(r);
         has_ray = true;
         sp = 0;
@@ -320,12 +314,8 @@ trace_kernel_dyn(const Node* __restrict__ nodes, const SortedTri* __restrict__ s
         const F8 c0h = ldg256(nodes + node), c1h = ldg256(&nodes[node].lo1);
         const float4 lo0 = c0h.a, hi0 = c0h.b, lo1 = c1h.a, hi1 = c1h.b;
         float tn0, tn1;
-        bool h0 = slab(lo0, hi0, r, tn0);
-        bool h1 = slab(lo1, hi1, r, tn1);
-        if (zero_dir) {  // rare: a direction component is exactly zero
-          h0 = h0 && on_slabs(lo0, hi0, r);
-          h1 = h1 && on_slabs(lo1, hi1, r);
-        }
+        const bool h0 = slab(lo0, hi0, r, tn0);
+        const bool h1 = slab(lo1, hi1, r, tn1);
         const int c0 = __float_as_int(lo0.w), c1 = __float_as_int(lo1.w);
         if (h0 && h1) {
           const bool swap = tn1 < tn0;

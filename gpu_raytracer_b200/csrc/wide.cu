@@ -136,18 +136,6 @@ collapse4_kernel(const Node* __restrict__ nodes, uint32_t n, uint32_t leaf_max,
 // ---- traversal ----------------------------------------------------------------------
 constexpr int kWideStack = 3 * 95 + 3;
 
-// same arithmetic as slab() of trace_common.cuh, on scalars
-__device__ __forceinline__ bool slab1(float lx, float ly, float lz, float hx, float hy, float hz,
-                                      const RayState& r, float& tn) {
-  const float t0x = (lx - r.ox) * r.ix, t1x = (hx - r.ox) * r.ix;
-  const float t0y = (ly - r.oy) * r.iy, t1y = (hy - r.oy) * r.iy;
-  const float t0z = (lz - r.oz) * r.iz, t1z = (hz - r.oz) * r.iz;
-  tn = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), r.tmin));
-  float tf = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fminf(fmaxf(t0z, t1z), r.best_t));
-  tf = tf * kSlabPad;
-  return tn <= tf;
-}
-
 __device__ __forceinline__ void cswap(uint32_t& a, uint32_t& b) {
   const uint32_t lo = min(a, b), hi = max(a, b);
   a = lo;
@@ -171,7 +159,6 @@ trace_wide_kernel(const Node4* __restrict__ wide, const SortedTri* __restrict__ 
   int sp = 0;
   uint32_t cur = kWideEmpty;
   bool has_ray = false;
-  bool zero_dir = false;
   unsigned long long my_ray = 0;
   RayState r;
   r.best_prim = -1;
@@ -199,7 +186,7 @@ trace_wide_kernel(const Node4* __restrict__ wide, const SortedTri* __restrict__ 
       const uint32_t slot = __popc(idle & lt_mask);
       if (!has_ray && slot < avail) {
         my_ray = chunk_next + slot;
-        zero_dir = load_ray(r, ld_stream(rays + 2 * my_ray), ld_stream(rays + 2 * my_ray + 1));
+        load_ray(r, ld_stream(rays + 2 * my_ray), ld_stream(rays + 2 * my_ray + 1));
         if (WT) wr = wt_setup(r);
         has_ray = true;
         sp = 0;
@@ -227,16 +214,10 @@ trace_wide_kernel(const Node4* __restrict__ wide, const SortedTri* __restrict__ 
         const float4 lox = q0.a, loy = q0.b, loz = q1.a, hix = q1.b, hiy = q2.a, hiz = q2.b;
         const uint4 ref = __ldg(reinterpret_cast<const uint4*>(np) + 6);
         float t0, t1, t2, t3;
-        bool h0 = slab1(lox.x, loy.x, loz.x, hix.x, hiy.x, hiz.x, r, t0) && ref.x != kWideEmpty;
-        bool h1 = slab1(lox.y, loy.y, loz.y, hix.y, hiy.y, hiz.y, r, t1) && ref.y != kWideEmpty;
-        bool h2 = slab1(lox.z, loy.z, loz.z, hix.z, hiy.z, hiz.z, r, t2) && ref.z != kWideEmpty;
-        bool h3 = slab1(lox.w, loy.w, loz.w, hix.w, hiy.w, hiz.w, r, t3) && ref.w != kWideEmpty;
-        if (zero_dir) {  // rare: a direction component is exactly zero (trace_common.cuh)
-          h0 = h0 && on_slabs(lox.x, loy.x, loz.x, hix.x, hiy.x, hiz.x, r);
-          h1 = h1 && on_slabs(lox.y, loy.y, loz.y, hix.y, hiy.y, hiz.y, r);
-          h2 = h2 && on_slabs(lox.z, loy.z, loz.z, hix.z, hiy.z, hiz.z, r);
-          h3 = h3 && on_slabs(lox.w, loy.w, loz.w, hix.w, hiy.w, hiz.w, r);
-        }
+        const bool h0 = slab(lox.x, loy.x, loz.x, hix.x, hiy.x, hiz.x, r, t0) && ref.x != kWideEmpty;
+        const bool h1 = slab(lox.y, loy.y, loz.y, hix.y, hiy.y, hiz.y, r, t1) && ref.y != kWideEmpty;
+        const bool h2 = slab(lox.z, loy.z, loz.z, hix.z, hiy.z, hiz.z, r, t2) && ref.z != kWideEmpty;
+        const bool h3 = slab(lox.w, loy.w, loz.w, hix.w, hiy.w, hiz.w, r, t3) && ref.w != kWideEmpty;
         // (entry distance | slot) keys; a miss sorts last
         uint32_t k0 = h0 ? ((__float_as_uint(t0) & ~3u) | 0u) : 0xFFFFFFFFu;
         uint32_t k1 = h1 ? ((__float_as_uint(t1) & ~3u) | 1u) : 0xFFFFFFFFu;

@@ -585,29 +585,31 @@ inline bool accept(float t, int32_t prim, float tmin, float best_t, int32_t best
 
 const float kSlabPad = 1.0000004f;  // 1 + 3 ulp: keeps the slab test conservative
 
-// idir[k] is NaN for a direction component that is exactly +-0: both plane distances of
-// that axis are then NaN and the NaN-ignoring min/max leave the axis out of tnear/tfar (a
-// ray parallel to a slab is inside it for every t or for none); which of the two is the
-// closed-interval test lo <= o <= hi below.  (A clamped 1/d, as the first version had it,
-// gives 0 * FLT_MAX = 0 for an origin ON a face and culled nodes the ray does enter.)
+// The two plane distances of an axis are combined with NaN-PROPAGATING min/max (pmin/pmax),
+// the axes and tmin / best_t with NaN-ignoring ones (nmin/nmax).  idir[k] is +inf for a
+// direction component that is exactly +-0: its plane distances are then -inf / +inf, or 0 * inf
+// = NaN for an origin exactly on the plane, and a NaN drops the axis from tnear and tfar.  So a
+// ray parallel to a slab passes when its origin lies in the CLOSED slab and fails otherwise
+// ((-inf,-inf) -> tfar = -inf, (+inf,+inf) -> tnear = +inf).  (A clamped 1/0 = FLT_MAX, as the
+// first version had it, gives 0 * FLT_MAX = 0 for an origin ON a face and culled nodes the ray
+// does enter.)
+inline float pmin(float a, float b) { return (a != a || b != b) ? std::numeric_limits<float>::quiet_NaN() : (a < b ? a : b); }
+inline float pmax(float a, float b) { return (a != a || b != b) ? std::numeric_limits<float>::quiet_NaN() : (a > b ? a : b); }
 inline bool slab(const float* bx, const Ray& r, const float idir[3], float best_t, float& tn) {
   float t0x = (bx[0] - r.o[0]) * idir[0], t1x = (bx[3] - r.o[0]) * idir[0];
   float t0y = (bx[1] - r.o[1]) * idir[1], t1y = (bx[4] - r.o[1]) * idir[1];
   float t0z = (bx[2] - r.o[2]) * idir[2], t1z = (bx[5] - r.o[2]) * idir[2];
-  tn = nmax(nmax(nmin(t0x, t1x), nmin(t0y, t1y)), nmax(nmin(t0z, t1z), r.tmin));
-  float tf = nmin(nmin(nmax(t0x, t1x), nmax(t0y, t1y)), nmin(nmax(t0z, t1z), best_t));
+  tn = nmax(nmax(pmin(t0x, t1x), pmin(t0y, t1y)), nmax(pmin(t0z, t1z), r.tmin));
+  float tf = nmin(nmin(pmax(t0x, t1x), pmax(t0y, t1y)), nmin(pmax(t0z, t1z), best_t));
   tf = tf * kSlabPad;
-  if (!(tn <= tf)) return false;
-  for (int k = 0; k < 3; ++k)
-    if (idir[k] != idir[k] && !(bx[k] <= r.o[k] && r.o[k] <= bx[3 + k])) return false;
-  return true;
+  return tn <= tf;
 }
 
-// 1/d: NaN for an exact zero, else clamped to +-FLT_MAX (a denormal component then gives
-// 0 * FLT_MAX = 0, not 0 * inf = NaN, for an origin on a box face)
+// 1/d clamped to +-FLT_MAX (a denormal component then gives 0 * FLT_MAX = 0, not 0 * inf = NaN,
+// for an origin on a box face); +inf for a component that is exactly +-0
 inline float inv_dir(float d) {
   const float fmx = std::numeric_limits<float>::max();
-  if (d == 0.0f) return std::numeric_limits<float>::quiet_NaN();
+  if (d == 0.0f) return std::numeric_limits<float>::infinity();
   return nmin(nmax(1.0f / d, -fmx), fmx);
 }
 
