@@ -119,6 +119,10 @@ def shade(tris, rays, hits, ao_hits=None, spp: int = 0):
 WIDE_NODE_DTYPE = np.dtype([("lo", np.float32, (3, 4)), ("hi", np.float32, (3, 4)),
                             ("ref", np.uint32, 4), ("n_children", np.uint32), ("pad", np.uint32, 3)])
 WIDE_LEAF_BIT, WIDE_EMPTY, WIDE_FIRST_MASK = 0x80000000, 0x7FFFFFFF, (1 << 29) - 1
+# one node of bvh_read_wide8 (80 bytes)
+WIDE8_NODE_DTYPE = np.dtype([("p", np.float32, 3), ("e", np.uint8, 3), ("imask", np.uint8),
+                             ("child_base", np.uint32), ("tri_base", np.uint32), ("meta", np.uint8, 8),
+                             ("qlo", np.uint8, (3, 8)), ("qhi", np.uint8, (3, 8))])
 
 
 # ---------------------------------------------------------------------------
@@ -164,12 +168,12 @@ class Bvh:
     # -- build_bvh -----------------------------------------------------------
     @classmethod
     def build(cls, tris, key_bits: int = 30, keep_keys: bool = False, timings: bool = False,
-              device: int = -1, stream: int = 0, wide: bool = False) -> "Bvh":
+              device: int = -1, stream: int = 0, wide: bool = False, wide8: bool = False) -> "Bvh":
         n = _rows(tris, 12)
         opts = L.BuildOpts(key_bits=key_bits,
                            flags=(L.RT_BUILD_KEEP_KEYS if keep_keys else 0) |
                                  (L.RT_BUILD_TIMINGS if timings else 0) |
-                                 (L.RT_BUILD_WIDE4 if wide else 0),
+                                 (L.RT_BUILD_WIDE4 if wide else 0) | (L.RT_BUILD_WIDE8 if wide8 else 0),
                            device=device, reserved=0, stream=stream or None)
         h = C.c_void_p()
         L.check(L.lib().build_bvh(_ptr(tris) if n else None, n, C.byref(opts), C.byref(h)))
@@ -233,6 +237,19 @@ class Bvh:
     def widen(self) -> None:
         """Collapse to the 4-wide layout (A5w); ``trace`` then walks it."""
         L.check(L.lib().bvh_widen(self._h))
+
+    def widen8(self) -> None:
+        """Collapse to the compressed 8-wide layout (needs keep_keys=True); ``trace`` then walks it."""
+        L.check(L.lib().bvh_widen8(self._h))
+
+    def read_wide8(self):
+        """(nodes, tris): the 8-wide layout as a structured array and the triangles in its order."""
+        cnt = C.c_uint32()
+        L.check(L.lib().bvh_read_wide8(self._h, None, None, C.byref(cnt)))
+        nodes = np.zeros(int(cnt.value), dtype=WIDE8_NODE_DTYPE)
+        tris = np.zeros((self.n_tris, 12), dtype=np.float32)
+        L.check(L.lib().bvh_read_wide8(self._h, nodes.ctypes.data, tris.ctypes.data, C.byref(cnt)))
+        return nodes, tris
 
     def read_wide(self):
         """(nodes, root_ref): the BVH4 as a structured array with n-1 slots."""

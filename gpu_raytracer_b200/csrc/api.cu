@@ -183,6 +183,8 @@ void release(rt_bvh* h) {
   if (h->parent) cudaFreeAsync(h->parent, 0);
   if (h->keys) cudaFreeAsync(h->keys, 0);
   if (h->wide) cudaFreeAsync(h->wide, 0);
+  if (h->wide8.nodes) cudaFreeAsync(h->wide8.nodes, 0);
+  if (h->wide8.tris) cudaFreeAsync(h->wide8.tris, 0);
   if (prev != h->device && prev >= 0) cudaSetDevice(prev);
   delete h;
 }
@@ -219,11 +221,45 @@ int widen(rt_bvh* h, cudaStream_t s) {
   return 0;
 }
 
+// (re)builds the compressed 8-wide layout of a finished BVH2 (A5w, wide8.cu).  Host
+// synchronisations: one per batch of levels (the queue length decides when to stop).
+int widen8(rt_bvh* h, cudaStream_t s) {
+  if (h->n <= wide8_leaf_max())
+    return fail(RT_ERR_INVALID, "wide8: the layout needs more than %u triangles", wide8_leaf_max());
+  TempPool tmp(s);
+  void* scratch = nullptr;
+  Node8* big = nullptr;
+  const uint32_t capacity = wide8_node_capacity(h->n);
+  RT_TRY(tmp.alloc(&scratch, wide8_scratch_bytes(h->n)));
+  RT_TRY(tmp.alloc((void**)&big, (size_t)capacity * sizeof(Node8)));
+  if (!h->wide8.tris) {
+    RT_TRY(pool_alloc((void**)&h->wide8.tris, h->n * sizeof(SortedTri), s));
+    h->bytes += h->n * sizeof(SortedTri);
+  }
+  h->wide8.valid = false;
+  uint32_t n_nodes = 0;
+  RT_TRY(launch_collapse8(h->nodes, h->stris, h->n, h->root, scratch, big, h->wide8.tris, &n_nodes, s));
+  // the worst-case array goes back to the pool; the handle keeps an exact copy
+  if (h->wide8.nodes) {
+    cudaFreeAsync(h->wide8.nodes, s);
+    h->bytes -= (uint64_t)h->wide8.n_nodes * sizeof(Node8);
+    h->wide8.nodes = nullptr;
+  }
+  RT_TRY(pool_alloc((void**)&h->wide8.nodes, (size_t)n_nodes * sizeof(Node8), s));
+  RT_CUDA(cudaMemcpyAsync(h->wide8.nodes, big, (size_t)n_nodes * sizeof(Node8), cudaMemcpyDeviceToDevice, s));
+  h->bytes += (uint64_t)n_nodes * sizeof(Node8);
+  h->wide8.n_nodes = n_nodes;
+  h->wide8.valid = true;
+  return 0;
+}
+
 }  // namespace
 // traversal of whichever layout the handle holds
 int rt::launch_trace_h(const rt_bvh* h, const float4* rays, uint64_t n_rays, uint32_t flags,
                        float4* hits, unsigned long long* counter, cudaStream_t s,
                        unsigned long long* stats) {
+  if (h->wide8.valid && params().trace_wide != 0)
+    return launch_trace_wide8(h->wide8.nodes, h->wide8.tris, rays, n_rays, flags, hits, counter, s, stats);
   if (h->is_wide && params().trace_wide != 0)
     return launch_trace_wide(h->wide, h->stris, h->n, h->wide_root, rays, n_rays, flags, hits,
                              counter, s, stats);
@@ -356,7 +392,7 @@ int build_impl(rt_bvh* h, const float* tris_in, uint32_t flags, cudaStream_t s) 
   RT_TRY(launch_build_tree(tris, svals, skeys, h->key_bits, n, (uint32_t*)flags_buf, h->nodes,
                            h->stris, h->header, queue_buf, s, hybrid ? long_run : nullptr));
   RT_TRY(mark(5));
-  const bool want_wide = (flags & RT_BUILD_WIDE4) != 0;
+  const bool want_wide = (flags & (RT_BUILD_WIDE4 | RT_BUILD_WIDE8)) != 0;
   if (!want_wide) RT_TRY(mark(6));
   uint32_t long_flag = 0;
   if (hybrid) RT_CUDA(cudaMemcpyAsync(&long_flag, long_run, 4, cudaMemcpyDeviceToHost, s));
@@ -389,7 +425,8 @@ int build_impl(rt_bvh* h, const float* tris_in, uint32_t flags, cudaStream_t s) 
   }
   h->root = (int)hdr.root_node;
   if (want_wide) {  // A5w, optional: needs the root
-    RT_TRY(widen(h, s));
+    if (flags & RT_BUILD_WIDE4) RT_TRY(widen(h, s));
+    if ((flags & RT_BUILD_WIDE8) && n > wide8_leaf_max()) RT_TRY(widen8(h, s));
     RT_TRY(mark(6));
     RT_CUDA(cudaStreamSynchronize(s));
   }
@@ -477,6 +514,10 @@ extern "C" int refit_bvh(rt_bvh* h, const float* tris_in) {
     RT_TRY(widen(h, s));
     RT_CUDA(cudaStreamSynchronize(s));
   }
+  if (h->wide8.valid) {  // and the 8-wide layout
+    RT_TRY(widen8(h, s));
+    RT_CUDA(cudaStreamSynchronize(s));
+  }
   return RT_OK;
 }
 
@@ -499,6 +540,27 @@ extern "C" int bvh_read_wide(const rt_bvh* h, void* nodes4, uint32_t* root_ref) 
     RT_TRY(scope.enter(h->device));
     RT_CUDA(cudaMemcpy(nodes4, h->wide, (h->n - 1) * sizeof(Node4), cudaMemcpyDeviceToHost));
   }
+  return RT_OK;
+}
+
+extern "C" int bvh_widen8(rt_bvh* h) {
+  if (!h) return fail(RT_ERR_INVALID, "bvh_widen8: handle is NULL");
+  DeviceScope scope;
+  RT_TRY(scope.enter(h->device));
+  cudaStream_t s = 0;
+  RT_TRY(widen8(h, s));
+  RT_CUDA(cudaStreamSynchronize(s));
+  return RT_OK;
+}
+
+extern "C" int bvh_read_wide8(const rt_bvh* h, void* nodes8, float* tris8, uint32_t* n_nodes) {
+  if (!h) return fail(RT_ERR_INVALID, "bvh_read_wide8: handle is NULL");
+  if (!h->wide8.valid) return fail(RT_ERR_INVALID, "bvh_read_wide8: the handle holds no 8-wide layout");
+  if (n_nodes) *n_nodes = h->wide8.n_nodes;
+  DeviceScope scope;
+  RT_TRY(scope.enter(h->device));
+  if (nodes8) RT_CUDA(cudaMemcpy(nodes8, h->wide8.nodes, (size_t)h->wide8.n_nodes * sizeof(Node8), cudaMemcpyDeviceToHost));
+  if (tris8) RT_CUDA(cudaMemcpy(tris8, h->wide8.tris, h->n * sizeof(SortedTri), cudaMemcpyDeviceToHost));
   return RT_OK;
 }
 
@@ -611,8 +673,12 @@ int trace_reordered(const rt_bvh* h, const float4* rays, uint64_t n_rays, uint32
     uint32_t* perm = nullptr;
     RT_TRY(launch_sort(keys, n, 30, ws, /*iota_payload=*/true, &skeys, &perm, s, false,
                        /*max_passes=*/2));  // 20-bit keys
-    RT_TRY(launch_trace(h->nodes, h->stris, h->n, h->root, rays + 2 * first, n, flags & 3u,
-                        hits + first, counter, s, nullptr, nullptr, perm));
+    if (h->wide8.valid && params().trace_wide != 0)
+      RT_TRY(launch_trace_wide8(h->wide8.nodes, h->wide8.tris, rays + 2 * first, n, flags & 3u, hits + first,
+                                counter, s, nullptr, perm));
+    else
+      RT_TRY(launch_trace(h->nodes, h->stris, h->n, h->root, rays + 2 * first, n, flags & 3u,
+                          hits + first, counter, s, nullptr, nullptr, perm));
   }
   return 0;
 }
@@ -624,7 +690,7 @@ int rt::trace_device(const rt_bvh* h, const float4* rays, uint64_t n_rays, uint3
   RT_TRY(pool_alloc((void**)&counter, sizeof(unsigned long long), s));
   int rc;
   if ((flags & RT_TRACE_REORDER) && n_rays >= kReorderMin && h->n != 0 &&
-      params().trace_variant != 0 && !(h->is_wide && params().trace_wide != 0))
+      params().trace_variant != 0 && !(h->is_wide && !h->wide8.valid && params().trace_wide != 0))
     rc = trace_reordered(h, rays, n_rays, flags, hits, counter, s);
   else
     rc = launch_trace_h(h, rays, n_rays, flags & 3u, hits, counter, s);
@@ -846,7 +912,7 @@ extern "C" int trace_rays(const rt_bvh* h, const float* rays, uint64_t n_rays, u
   // kernel straight into pinned host memory (posted PCIe writes need no staging)
   // both buffers pinned on the host: one kernel launch follows the upload (see trace_streamed)
   if (!rays_dev && !hits_dev && !rays_k && !hits_k && params().streamed != 0 &&
-      params().trace_variant != 0 && !(h->is_wide && params().trace_wide != 0) &&
+      params().trace_variant != 0 && !((h->is_wide || h->wide8.valid) && params().trace_wide != 0) &&
       n_rays >= (1ull << 19) && is_pinned_host(rays) && is_pinned_host(hits))
   {
     const int rc = trace_streamed(h, rays, n_rays, flags, hits);

@@ -79,6 +79,7 @@ struct rt_bvh {
   uint32_t wide_root = 0;     // reference the BVH4 traversal starts from
   bool is_wide = false;
   uint32_t wide_leaf_max = rt::kWideLeafDefault;
+  rt::Wide8 wide8;            // only with RT_BUILD_WIDE8 / bvh_widen8: compressed 8-wide layout
   float bounds[6] = {0, 0, 0, 0, 0, 0};
   int root = 0;  // node id where traversal starts (header.root_node)
   float times[RT_STAGE_COUNT] = {0, 0, 0, 0, 0, 0, 0};

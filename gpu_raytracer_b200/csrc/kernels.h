@@ -199,6 +199,28 @@ int launch_trace_wide(const Node4* wide, const SortedTri* stris, uint64_t n_tris
                       unsigned long long* ray_counter, cudaStream_t s,
                       unsigned long long* stats = nullptr);
 
+// ---- A5w: compressed 8-wide BVH (wide8.cu) -----------------------------------------
+// 80-byte node: five 16-byte words (layout in wide8.cu and include/gpu_raytracer.h)
+struct __align__(16) Node8 {
+  uint4 w[5];
+};
+// the layout as a handle holds it
+struct Wide8 {
+  Node8* nodes = nullptr;
+  SortedTri* tris = nullptr;  // the triangles in wide-node order: a node's leaf triangles are consecutive
+  uint32_t n_nodes = 0;
+  bool valid = false;
+};
+size_t wide8_scratch_bytes(uint64_t n);
+uint32_t wide8_leaf_max();
+uint32_t wide8_node_capacity(uint64_t n);
+// out: wide8_node_capacity(n) nodes; tris8: n records; n > wide8_leaf_max().  Synchronises s.
+int launch_collapse8(const Node* nodes, const SortedTri* stris, uint64_t n, int root, void* scratch,
+                     Node8* out, SortedTri* tris8, uint32_t* n_nodes_out, cudaStream_t s);
+int launch_trace_wide8(const Node8* nodes8, const SortedTri* tris8, const float4* rays, uint64_t n_rays,
+                       uint32_t flags, float4* hits, unsigned long long* ray_counter, cudaStream_t s,
+                       unsigned long long* stats = nullptr, const uint32_t* perm = nullptr);
+
 // ---- traversal (traverse.cu) -------------------------------------------------
 // Hand-shake of the streamed mode (host-resident batches): rays arrive while the kernel runs.
 struct TracePipe {

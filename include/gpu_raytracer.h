@@ -72,6 +72,11 @@ extern "C" {
 #define RT_BUILD_WIDE4 4u     /* A5w: also collapse the tree to a 4-wide BVH; trace_rays then
                                  walks that layout (same hits, bit for bit); n <= 2^29 */
 
+#define RT_BUILD_WIDE8 8u     /* A5w: also collapse the tree to the compressed 8-wide layout (80-byte
+                                 nodes, 8-bit child boxes); trace_rays then walks that layout: same
+                                 hits, bit for bit.  More than 3 triangles; +48 n bytes (the triangles
+                                 in wide-node order) + 80 bytes per wide node.  Wins for incoherent rays */
+
 /* scene kinds for rt_gen_scene */
 #define RT_SCENE_CORNELL 0     /* config 1: 1,024 triangles, no parameters       */
 #define RT_SCENE_SOUP 1        /* config 2: p0 = triangle count                  */
@@ -182,6 +187,21 @@ RT_API int bvh_widen(rt_bvh* h);
  * subtrees with <= 4 triangles are unused (unspecified bytes).  root_ref: the
  * reference traversal starts from. */
 RT_API int bvh_read_wide(const rt_bvh* h, void* nodes4, uint32_t* root_ref);
+
+/* Compressed 8-wide layout (what RT_BUILD_WIDE8 does at build time) of any handle with more than
+ * 3 triangles, also one filled through bvh_device_buffers + bvh_commit or bvh_load. */
+RT_API int bvh_widen8(rt_bvh* h);
+/* nodes8: host, n_nodes x 80 bytes (call with nodes8 = tris8 = NULL for the count); tris8: host,
+ * n x 12 floats, the triangles in wide-node order (v0.xyz, prim, v1.xyz, 0, v2.xyz, 0).  Node:
+ *   f32 p[3]; u8 e[3]; u8 imask; u32 child_base; u32 tri_base; u8 meta[8];
+ *   u8 qlo_x[8], qlo_y[8], qlo_z[8], qhi_x[8], qhi_y[8], qhi_z[8];
+ * Slots follow octants (bit 2 / 1 / 0 = upper half of the node's box in x / y / z) as far as
+ * the children allow.  Child box =
+ * [p + qlo * 2^(e-127), p + qhi * 2^(e-127)] (contains the exact box).  meta[s]: 0 empty;
+ * 0x20 | 24 + s internal child, stored at child_base + popcount(imask & ((1 << s) - 1));
+ * ((1 << count) - 1) << 5 | offset: leaf child of count (1..3) triangles at tri_base + offset.
+ * Node 0 is the root. */
+RT_API int bvh_read_wide8(const rt_bvh* h, void* nodes8, float* tris8, uint32_t* n_nodes);
 
 /* ---- multi-GPU helpers ----------------------------------- */
 

@@ -76,6 +76,10 @@ def lib() -> C.CDLL:
         L.orc_brute.argtypes = [vp, u64, vp, u64, u32, vp]
         L.orc_collapse4.argtypes = [vp, u32, u64, vp, vp]
         L.orc_collapse4.restype = u64
+        L.orc_collapse8.argtypes = [vp, u64, vp, vp]
+        L.orc_collapse8.restype = u64
+        L.orc_canon8.argtypes = [vp, u64, vp, u64, vp, vp]
+        L.orc_canon8.restype = u64
         _lib = L
     return _lib
 
@@ -156,6 +160,18 @@ def shade(tris: np.ndarray, rays: np.ndarray, hits: np.ndarray, ao_hits=None, sp
     return out
 
 
+def canon8(nodes: np.ndarray, tris: np.ndarray):
+    """A compressed 8-wide tree (bvh_read_wide8) renumbered breadth first, the numbering
+    ``OracleBvh.collapse8`` uses.  Returns (nodes uint8 [m, 80], tris float32 [n, 12])."""
+    nodes = np.ascontiguousarray(nodes).view(np.uint8).reshape(-1, 80)
+    tris = np.ascontiguousarray(tris, dtype=np.float32).reshape(-1, 12)
+    out_n, out_t = np.zeros_like(nodes), np.zeros_like(tris)
+    m = int(lib().orc_canon8(_p(nodes), nodes.shape[0], _p(tris), tris.shape[0], _p(out_n), _p(out_t)))
+    if m != nodes.shape[0]:
+        raise ValueError(f"malformed 8-wide tree: {m} of {nodes.shape[0]} nodes reached")
+    return out_n, out_t
+
+
 class OracleBvh:
     """Result of the oracle's build: canonical arrays."""
 
@@ -210,6 +226,15 @@ class OracleBvh:
         if m:
             lib().orc_collapse4(self._h, leaf_max, m, _p(boxes), _p(desc))
         return boxes, desc
+
+    def collapse8(self):
+        """A5w: the compressed 8-wide layout: (nodes uint8 [m, 80], tris float32 [n, 12])."""
+        m = int(lib().orc_collapse8(self._h, 0, None, None))
+        nodes = np.zeros((m, 80), dtype=np.uint8)
+        tris = np.zeros((self.n, 12), dtype=np.float32)
+        if m:
+            lib().orc_collapse8(self._h, m, _p(nodes), _p(tris))
+        return nodes, tris
 
     def close(self):
         if self._h:

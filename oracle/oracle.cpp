@@ -1006,6 +1006,231 @@ ORC_API uint64_t orc_collapse4(const void* h, uint32_t leaf_max, uint64_t cap, f
   return c.count;
 }
 
+// ---------------------------------------------------------------------------
+// A5w, second wide layout: the compressed 8-wide BVH (80-byte nodes, 8-bit child boxes;
+// Ylitie, Karras & Laine 2017).  Collapse rule, top-down from the binary tree: a wide node
+// starts from the two children of its binary node and keeps replacing the child with the
+// largest half surface area ((dx*dy + dy*dz) + dz*dx, no contraction; ties to the leftmost)
+// among those holding more than 3 triangles by that child's own two children, in place, until
+// it has eight children or none is left; then, while slots are free, it opens the largest child
+// that holds 2 or 3 triangles (tighter leaf boxes at no cost in nodes).  Children of at most 3
+// triangles are leaves.
+// Slots: left to right, each child takes the free slot t maximising
+// ((t&4 ? ox : -ox) + (t&2 ? oy : -oy)) + (t&1 ? oz : -oz), o = centre of the child's box -
+// centre of the node's box (centre = 0.5f * (lo + hi)), ties to the lowest slot.  Child boxes
+// are quantised outward on a grid of 2^e cells from the node's min corner (double-precision
+// floor / ceil).  Numbering (canonical): breadth first; a node's internal children are
+// consecutive from child_base in slot order, its leaf triangles consecutive from tri_base in
+// slot order, both allocated in the order the nodes are visited.
+//   nodes: cap x 80 bytes (layout in include/gpu_raytracer.h, bvh_read_wide8)
+//   tris:  n x 12 floats: v0.xyz, prim bits, v1.xyz, 0, v2.xyz, 0 in wide-node order
+// Returns the number of wide nodes (cap = 0: count only); 0 when n <= 3.
+// ---------------------------------------------------------------------------
+namespace {
+struct Collapser8 {
+  const Bvh& b;
+  uint32_t leaf0 = 0;
+  std::vector<uint32_t> first, cnt;
+
+  void ranges() {
+    const uint64_t n = b.n, nodes = 2 * n - 1;
+    leaf0 = (uint32_t)(n - 1);
+    first.assign(nodes, 0);
+    cnt.assign(nodes, 0);
+    for (uint64_t j = 0; j < n; ++j) { first[leaf0 + j] = (uint32_t)j; cnt[leaf0 + j] = 1; }
+    std::vector<uint32_t> stack{0};
+    std::vector<uint8_t> seen(n - 1, 0);
+    while (!stack.empty()) {
+      uint32_t i = stack.back();
+      if (!seen[i]) {
+        seen[i] = 1;
+        if (b.left[i] < leaf0) stack.push_back(b.left[i]);
+        if (b.right[i] < leaf0) stack.push_back(b.right[i]);
+      } else {
+        stack.pop_back();
+        first[i] = first[b.left[i]];
+        cnt[i] = cnt[b.left[i]] + cnt[b.right[i]];
+      }
+    }
+  }
+
+  static uint32_t quant_exponent(double ext) {
+    if (!(ext > 0.0)) return 0u;
+    int e;
+    std::frexp(ext / 255.0, &e);
+    while (std::ldexp(255.0, e - 1) >= ext) --e;
+    while (std::ldexp(255.0, e) < ext) ++e;
+    if (e < -126) e = -126;
+    if (e > 127) e = 127;
+    return (uint32_t)(e + 127);
+  }
+  static uint32_t quant_lo(float v, float p, uint32_t eb) {
+    if (eb == 0u) return 0u;
+    const double cell = std::ldexp(1.0, (int)eb - 127), d = (double)v - (double)p;
+    double q = std::floor(d / cell);
+    q = std::fmin(std::fmax(q, 0.0), 255.0);
+    while (q > 0.0 && (double)p + q * cell > (double)v) q -= 1.0;
+    return (uint32_t)q;
+  }
+  static uint32_t quant_hi(float v, float p, uint32_t eb) {
+    if (eb == 0u) return 0u;
+    const double cell = std::ldexp(1.0, (int)eb - 127), d = (double)v - (double)p;
+    double q = std::ceil(d / cell);
+    q = std::fmin(std::fmax(q, 0.0), 255.0);
+    while (q < 255.0 && (double)p + q * cell < (double)v) q += 1.0;
+    return (uint32_t)q;
+  }
+
+  // breadth-first; returns the node count; writes when nodes_out != nullptr
+  uint64_t run(uint8_t* nodes_out, float* tris_out) {
+    std::vector<uint32_t> queue{0};  // canonical binary node ids; wide node index = queue position
+    uint32_t next_tri = 0;
+    for (size_t at = 0; at < queue.size(); ++at) {
+      const uint32_t node = queue[at];
+      uint32_t s[8];
+      int ns = 2;
+      s[0] = b.left[node];
+      s[1] = b.right[node];
+      while (ns < 8) {
+        int best = -1;
+        float best_area = 0.0f;
+        for (int k = 0; k < ns; ++k)
+          if (cnt[s[k]] > 3) {
+            const float a = half_area(&b.boxes[(uint64_t)s[k] * 6]);
+            if (best < 0 || a > best_area) { best = k; best_area = a; }
+          }
+        if (best < 0)  // nothing left that must be opened: spend the free slots on tighter leaves
+          for (int k = 0; k < ns; ++k)
+            if (cnt[s[k]] > 1) {
+              const float a = half_area(&b.boxes[(uint64_t)s[k] * 6]);
+              if (best < 0 || a > best_area) { best = k; best_area = a; }
+            }
+        if (best < 0) break;
+        const uint32_t x = s[best];
+        for (int k = ns; k > best + 1; --k) s[k] = s[k - 1];
+        s[best] = b.left[x];
+        s[best + 1] = b.right[x];
+        ++ns;
+      }
+      float lo[3], hi[3];
+      for (int a = 0; a < 3; ++a) { lo[a] = b.boxes[(uint64_t)s[0] * 6 + a]; hi[a] = b.boxes[(uint64_t)s[0] * 6 + 3 + a]; }
+      uint32_t n_int = 0, n_tri = 0;
+      for (int k = 0; k < ns; ++k) {
+        const float* bx = &b.boxes[(uint64_t)s[k] * 6];
+        for (int a = 0; a < 3; ++a) { lo[a] = std::fmin(lo[a], bx[a]); hi[a] = std::fmax(hi[a], bx[3 + a]); }
+        if (cnt[s[k]] > 3) ++n_int; else n_tri += cnt[s[k]];
+      }
+      uint32_t e[3];
+      for (int a = 0; a < 3; ++a) e[a] = quant_exponent((double)hi[a] - (double)lo[a]);
+      const uint32_t child_base = n_int ? (uint32_t)queue.size() : 0u;
+      const uint32_t tri_base = n_tri ? next_tri : 0u;
+      next_tri += n_tri;
+      const float c[3] = {0.5f * (lo[0] + hi[0]), 0.5f * (lo[1] + hi[1]), 0.5f * (lo[2] + hi[2])};
+      uint32_t used = 0, imask = 0, slot_of[8];
+      for (int k = 0; k < ns; ++k) {
+        const float* bx = &b.boxes[(uint64_t)s[k] * 6];
+        const float ox = 0.5f * (bx[0] + bx[3]) - c[0], oy = 0.5f * (bx[1] + bx[4]) - c[1],
+                    oz = 0.5f * (bx[2] + bx[5]) - c[2];
+        int pick = -1;
+        float pick_cost = 0.0f;
+        for (int t = 0; t < 8; ++t)
+          if (!((used >> t) & 1u)) {
+            const float cost = (((t & 4) ? ox : -ox) + ((t & 2) ? oy : -oy)) + ((t & 1) ? oz : -oz);
+            if (pick < 0 || cost > pick_cost) { pick = t; pick_cost = cost; }
+          }
+        used |= 1u << pick;
+        slot_of[k] = (uint32_t)pick;
+        if (cnt[s[k]] > 3) imask |= 1u << pick;
+      }
+      // internal children enter the queue in slot order
+      uint32_t by_slot[8];
+      for (int t = 0; t < 8; ++t) by_slot[t] = 0xFFFFFFFFu;
+      for (int k = 0; k < ns; ++k)
+        if (cnt[s[k]] > 3) by_slot[slot_of[k]] = s[k];
+      for (int t = 0; t < 8; ++t)
+        if (by_slot[t] != 0xFFFFFFFFu) queue.push_back(by_slot[t]);
+      if (!nodes_out) continue;
+      uint8_t rec[80];
+      std::memset(rec, 0, sizeof(rec));
+      std::memcpy(rec, lo, 12);
+      rec[12] = (uint8_t)e[0]; rec[13] = (uint8_t)e[1]; rec[14] = (uint8_t)e[2]; rec[15] = (uint8_t)imask;
+      std::memcpy(rec + 16, &child_base, 4);
+      std::memcpy(rec + 20, &tri_base, 4);
+      uint32_t tri_off = 0;
+      for (int k = 0; k < ns; ++k) {
+        const float* bx = &b.boxes[(uint64_t)s[k] * 6];
+        const uint32_t slot = slot_of[k];
+        for (int a = 0; a < 3; ++a) {
+          rec[32 + 8 * a + slot] = (uint8_t)quant_lo(bx[a], lo[a], e[a]);
+          rec[56 + 8 * a + slot] = (uint8_t)quant_hi(bx[3 + a], lo[a], e[a]);
+        }
+        if (cnt[s[k]] > 3) {
+          rec[24 + slot] = (uint8_t)(0x20u | (24u + slot));
+        } else {
+          rec[24 + slot] = (uint8_t)((((1u << cnt[s[k]]) - 1u) << 5) | tri_off);
+          for (uint32_t t = 0; t < cnt[s[k]]; ++t) {
+            const uint32_t prim = b.idx[first[s[k]] + t];
+            const float* src = b.T + (uint64_t)prim * 12;
+            float* dst = tris_out + (uint64_t)(tri_base + tri_off + t) * 12;
+            for (int v = 0; v < 3; ++v) { dst[4 * v] = src[4 * v]; dst[4 * v + 1] = src[4 * v + 1]; dst[4 * v + 2] = src[4 * v + 2]; dst[4 * v + 3] = 0.0f; }
+            std::memcpy(dst + 3, &prim, 4);
+          }
+          tri_off += cnt[s[k]];
+        }
+      }
+      std::memcpy(nodes_out + (uint64_t)at * 80, rec, 80);
+    }
+    return queue.size();
+  }
+};
+}  // namespace
+
+ORC_API uint64_t orc_collapse8(const void* h, uint64_t cap, uint8_t* nodes, float* tris) {
+  const Bvh& b = *(const Bvh*)h;
+  if (b.n <= 3) return 0;
+  Collapser8 c{b, 0, {}, {}};
+  c.ranges();
+  const uint64_t m = c.run(nullptr, nullptr);
+  if (cap >= m && nodes && tris) c.run(nodes, tris);
+  return m;
+}
+
+// The same wide tree in canonical (breadth-first) numbering: the device allocates child blocks
+// and triangle runs with atomics, so its numbers depend on arrival order; its TREE does not.
+// in_nodes: m x 80 bytes, in_tris: n x 12 floats -> out_nodes, out_tris.  Returns the nodes
+// reached from node 0 (== m for a well-formed tree), or 0 on a malformed tree.
+ORC_API uint64_t orc_canon8(const uint8_t* in_nodes, uint64_t m, const float* in_tris, uint64_t n,
+                            uint8_t* out_nodes, float* out_tris) {
+  std::vector<uint32_t> queue{0};
+  uint32_t next_tri = 0;
+  for (size_t at = 0; at < queue.size(); ++at) {
+    if (queue[at] >= m || queue.size() > m) return 0;
+    uint8_t rec[80];
+    std::memcpy(rec, in_nodes + (uint64_t)queue[at] * 80, 80);
+    uint32_t child_base, tri_base;
+    std::memcpy(&child_base, rec + 16, 4);
+    std::memcpy(&tri_base, rec + 20, 4);
+    const uint32_t imask = rec[15];
+    uint32_t n_int = 0, n_tri = 0;
+    for (int t = 0; t < 8; ++t) {
+      const uint32_t mt = rec[24 + t];
+      if (!mt) continue;
+      if ((mt & 0x18u) == 0x18u && (mt >> 5) == 1u) ++n_int;
+      else n_tri += (uint32_t)__builtin_popcount(mt >> 5);
+    }
+    if (n_int != (uint32_t)__builtin_popcount(imask) || next_tri + n_tri > n || (n_tri && tri_base + n_tri > n)) return 0;
+    const uint32_t new_child_base = n_int ? (uint32_t)queue.size() : 0u;
+    const uint32_t new_tri_base = n_tri ? next_tri : 0u;
+    for (uint32_t r = 0; r < n_int; ++r) queue.push_back(child_base + r);
+    if (n_tri) std::memcpy(out_tris + (uint64_t)new_tri_base * 12, in_tris + (uint64_t)tri_base * 12, (size_t)n_tri * 48);
+    next_tri += n_tri;
+    std::memcpy(rec + 16, &new_child_base, 4);
+    std::memcpy(rec + 20, &new_tri_base, 4);
+    std::memcpy(out_nodes + (uint64_t)at * 80, rec, 80);
+  }
+  return next_tri == n ? queue.size() : 0;
+}
+
 // T0: all-pairs intersector, no BVH.  Same triangle test and acceptance rule.
 ORC_API void orc_brute(const float* tris, uint64_t n, const float* rays, uint64_t nr, uint32_t flags,
                        float* hits) {
