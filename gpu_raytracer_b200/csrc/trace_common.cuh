@@ -74,10 +74,30 @@ __device__ __forceinline__ bool slab(const float4 lo, const float4 hi, const Ray
   return slab(lo.x, lo.y, lo.z, hi.x, hi.y, hi.z, r, tn);
 }
 
-// acceptance rule (A6): closest t in (tmin, best]; on equal t the smaller primitive wins
-__device__ __forceinline__ bool accept_hit(float t, float u, float v, int prim, RayState& r) {
-  const bool ok = (t > r.tmin) &&
-                  ((t < r.best_t) || (t == r.best_t && r.best_prim >= 0 && prim < r.best_prim));
+// Acceptance rule (A6): closest t in (tmin, best]; on equal t the smaller primitive wins; and the
+// hit must be CONSISTENT WITH THE TRIANGLE'S OWN BOX: slab() passes on the box of its three
+// vertices (ordered min/max, the tree's leaf box) and the box's entry distance satisfies
+// tnear <= t * kSlabPad.  The last condition is what makes the result independent of the
+// traversal: a node is culled when tnear(node) > min(tfar, best_t) * pad, every ancestor's box
+// contains the leaf box and slab() is monotone in the box, so a triangle whose hit is
+// acceptable (t <= best_t) can never sit below a culled node.  The accepted hit is therefore
+// min over {triangles with a consistent hit} by (t, prim): a function of the ray and the
+// triangles alone, which the binary tree, both wide layouts, any visiting order and the
+// all-pairs intersector (oracle brute) all return bit for bit.  (Without it the answer
+// depended on the order in marginal cases: a triangle whose computed t lies a few ulps before
+// its own flat box could be culled, or not, depending on what had been found before.)
+// The box is only evaluated for candidates that would otherwise be accepted: rare, so free.
+__device__ __forceinline__ bool accept_hit(float t, float u, float v, const float4 v0, const float4 v1,
+                                           const float4 v2, RayState& r) {
+  const int prim = __float_as_int(v0.w);
+  bool ok = (t > r.tmin) &&
+            ((t < r.best_t) || (t == r.best_t && r.best_prim >= 0 && prim < r.best_prim));
+  if (ok) {
+    float tn;
+    ok = slab(omin(omin(v0.x, v1.x), v2.x), omin(omin(v0.y, v1.y), v2.y), omin(omin(v0.z, v1.z), v2.z),
+              omax(omax(v0.x, v1.x), v2.x), omax(omax(v0.y, v1.y), v2.y), omax(omax(v0.z, v1.z), v2.z), r, tn) &&
+         tn <= t * kSlabPad;
+  }
   if (ok) {
     r.best_t = t;
     r.bu = u;
@@ -110,7 +130,7 @@ __device__ __forceinline__ bool intersect(const SortedTri* __restrict__ stris, u
   const float v = fmaf(r.dx, qx, fmaf(r.dy, qy, r.dz * qz)) * inv;
   const float t = fmaf(e2x, qx, fmaf(e2y, qy, e2z * qz)) * inv;
   if (!((u >= 0.0f) && (v >= 0.0f) && ((u + v) <= 1.0f))) return false;
-  return accept_hit(t, u, v, __float_as_int(v0.w), r);
+  return accept_hit(t, u, v, v0, v1, v2, r);
 }
 
 // Watertight test (Woop, Benthin & Wald 2013), RT_TRACE_WATERTIGHT: the ray is
@@ -169,7 +189,7 @@ __device__ __forceinline__ bool intersect_wt(const SortedTri* __restrict__ stris
   const float Az = w.Sz * Akz, Bz = w.Sz * Bkz, Cz = w.Sz * Ckz;
   const float T = (U * Az + V * Bz) + W * Cz;
   const float inv = 1.0f / det;
-  return accept_hit(T * inv, V * inv, W * inv, __float_as_int(v0.w), r);
+  return accept_hit(T * inv, V * inv, W * inv, v0, v1, v2, r);
 }
 
 // 1/d of one direction component, clamped to +-FLT_MAX so that a denormal component gives

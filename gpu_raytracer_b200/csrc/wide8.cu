@@ -27,10 +27,11 @@
 // passes slab() (every ancestor's box contains it, and slab() is monotone in the box), so the
 // closest accepted hit is a function of the per-triangle boxes alone.  Here the inner nodes
 // cull with a CONSERVATIVE test (quantised boxes, one FMA per plane, an explicit rounding
-// allowance: never rejects what slab() on the exact box accepts), and every candidate
-// triangle then takes slab() on its exact box (recomputed from the three vertices) before the
-// triangle test.  Same candidates tested, same acceptance rule: the oracle's bytes, whatever
-// the tree shape and the visiting order (tests/test_wide8.py).
+// allowance: never rejects what slab() on the exact box accepts), and the acceptance rule
+// (trace_common.cuh accept_hit) makes the accepted hit a function of the ray and the
+// triangles alone: min over the triangles whose hit is consistent with their own box by (t,
+// prim).  Conservative culling cannot lose such a triangle, so this tree returns the oracle's
+// bytes whatever its shape and visiting order (tests/test_wide8.py).
 #include "trace_common.cuh"
 
 namespace rt {
@@ -247,21 +248,10 @@ __device__ __forceinline__ uint32_t sign_extend_s8x4(uint32_t x) {  // 0x80 byte
   asm("prmt.b32 %0, %1, 0, 0xba98;" : "=r"(r) : "r"(x));
   return r;
 }
-__device__ __forceinline__ float byte_f(uint32_t w, int j) { return (float)((w >> (8 * j)) & 0xFFu); }
-
-// exact test of one candidate triangle: slab() on the triangle's own box (what the binary tree
-// tests at the leaf's parent), then the triangle test
-template <bool WT>
-__device__ __forceinline__ bool test_triangle8(const SortedTri* __restrict__ tris8, uint32_t j, RayState& r,
-                                               const WtRay& wr, uint32_t& n_tests) {
-  const float4* tp = reinterpret_cast<const float4*>(tris8 + j);
-  const float4 v0 = __ldg(tp), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
-  float tn;
-  if (!slab(fminf(fminf(v0.x, v1.x), v2.x), fminf(fminf(v0.y, v1.y), v2.y), fminf(fminf(v0.z, v1.z), v2.z),
-            fmaxf(fmaxf(v0.x, v1.x), v2.x), fmaxf(fmaxf(v0.y, v1.y), v2.y), fmaxf(fmaxf(v0.z, v1.z), v2.z), r, tn))
-    return false;
-  ++n_tests;
-  return WT ? intersect_wt(tris8, j, r, wr) : intersect(tris8, j, r);
+// byte j of w as a float: one PRMT puts the byte into the mantissa of 2^23, one FADD takes 2^23
+// away (exact for 0..255); I2F is a quarter-rate instruction and a node step converts 48 bytes
+__device__ __forceinline__ float byte_f(uint32_t w, int j) {
+  return __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7650u + (uint32_t)j)) - 8388608.0f;
 }
 
 template <bool ANY, bool STATS, bool WT>
@@ -282,7 +272,7 @@ trace_wide8_kernel(const Node8* __restrict__ nodes8, const SortedTri* __restrict
   unsigned long long my_ray = 0;
   RayState r;
   r.best_prim = -1;
-  float cix = 0.0f, ciy = 0.0f, ciz = 0.0f;  // 1/d for the conservative test: NaN where d is exactly zero
+  float cix = 0.0f, ciy = 0.0f, ciz = 0.0f;  // 1/d for the conservative test: 2^100 where d is exactly zero
   uint32_t octinv4 = 0u;
   WtRay wr = {0, 1, 2, 0.0f, 0.0f, 0.0f};
   unsigned long long chunk_next = 0, chunk_end = 0;  // warp-uniform
@@ -311,10 +301,17 @@ trace_wide8_kernel(const Node8* __restrict__ nodes8, const SortedTri* __restrict
         if (perm) my_ray = perm[my_ray];
         const float4 rd = ld_stream(rays + 2 * my_ray + 1);
         load_ray(r, ld_stream(rays + 2 * my_ray), rd);
-        const float nan = __int_as_float(0x7FC00000);
-        cix = rd.x == 0.0f ? nan : r.ix;
-        ciy = rd.y == 0.0f ? nan : r.iy;
-        ciz = rd.z == 0.0f ? nan : r.iz;
+        // a component that is exactly zero: slab() works with +-inf / NaN plane distances there
+        // (the ray is inside the closed slab for every t, or for none).  One FMA per plane
+        // cannot: q * inf + b is NaN for every plane, the axis would never cull, and a ray in a
+        // coordinate plane would visit a 2-D slice of the whole tree (one row of the 4K frame
+        // has d.y == 0: 3,840 rays took 13 of the frame's 15 ms).  2^100 instead of inf keeps
+        // every product finite and the sign of (plane - origin): strictly outside -> both
+        // distances huge with one sign -> culled; inside or within the allowance -> passes.
+        const float big = 1.2676506e30f;  // 2^100
+        cix = rd.x == 0.0f ? big : r.ix;
+        ciy = rd.y == 0.0f ? big : r.iy;
+        ciz = rd.z == 0.0f ? big : r.iz;
         octinv4 = ((rd.x < 0.0f ? 0u : 4u) | (rd.y < 0.0f ? 0u : 2u) | (rd.z < 0.0f ? 0u : 1u)) * 0x01010101u;
         if (WT) wr = wt_setup(r);
         has_ray = true;
@@ -355,14 +352,17 @@ trace_wide8_kernel(const Node8* __restrict__ nodes8, const SortedTri* __restrict
         const float bx = (__uint_as_float(w0.x) - r.ox) * cix;
         const float by = (__uint_as_float(w0.y) - r.oy) * ciy;
         const float bz = (__uint_as_float(w0.z) - r.oz) * ciz;
-        // rounding allowance (DESIGN.md §5 "wide8"): each plane distance is within
-        // 2^-21 (|b| + 256 |s|) of what slab() computes for a box the quantised one contains;
-        // NaN terms (zero direction components: the axis does not cull) count as 0
+        // Rounding allowance, per axis (DESIGN.md §5 "wide8"): a plane distance computed here is
+        // within d = 2^-21 (|b| + 256 |s|) of what slab() computes for any box the quantised one
+        // contains (b: two roundings, the FMA one, slab()'s own two), so near planes are taken d
+        // earlier and far planes d later.  Per axis, because a direction component close to zero
+        // makes that axis's |b| huge: folded into one allowance for all axes it switched the
+        // culling off for such rays.
         const float eps = 4.76837158203125e-07f;  // 2^-21
-        const float delta = (fmaxf(fmaf(256.0f, fabsf(sx), fabsf(bx)), 0.0f) +
-                             fmaxf(fmaf(256.0f, fabsf(sy), fabsf(by)), 0.0f) +
-                             fmaxf(fmaf(256.0f, fabsf(sz), fabsf(bz)), 0.0f)) * eps;
-        const float tmin_p = r.tmin + delta, tmax_m = r.best_t - delta, delta3 = 2.5f * delta;
+        const float dx8 = fmaf(256.0f, fabsf(sx), fabsf(bx)) * eps;
+        const float dy8 = fmaf(256.0f, fabsf(sy), fabsf(by)) * eps;
+        const float dz8 = fmaf(256.0f, fabsf(sz), fabsf(bz)) * eps;
+        const float bnx = bx - dx8, bfx = bx + dx8, bny = by - dy8, bfy = by + dy8, bnz = bz - dz8, bfz = bz + dz8;
         // near / far planes by the sign of the direction
         const bool nx = r.dx < 0.0f, ny = r.dy < 0.0f, nz = r.dz < 0.0f;
         uint32_t hitmask = 0u;
@@ -380,12 +380,12 @@ trace_wide8_kernel(const Node8* __restrict__ nodes8, const SortedTri* __restrict
           const uint32_t nqz = nz ? qhz : qlz, fqz = nz ? qlz : qhz;
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
-            const float tnx = fmaf(byte_f(nqx, j), sx, bx), tfx = fmaf(byte_f(fqx, j), sx, bx);
-            const float tny = fmaf(byte_f(nqy, j), sy, by), tfy = fmaf(byte_f(fqy, j), sy, by);
-            const float tnz = fmaf(byte_f(nqz, j), sz, bz), tfz = fmaf(byte_f(fqz, j), sz, bz);
-            const float cmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, tmin_p));
-            const float cmax = fminf(fminf(tfx, tfy), fminf(tfz, tmax_m));
-            if (cmin <= fmaf(cmax, kSlabPad, delta3))
+            const float tnx = fmaf(byte_f(nqx, j), sx, bnx), tfx = fmaf(byte_f(fqx, j), sx, bfx);
+            const float tny = fmaf(byte_f(nqy, j), sy, bny), tfy = fmaf(byte_f(fqy, j), sy, bfy);
+            const float tnz = fmaf(byte_f(nqz, j), sz, bnz), tfz = fmaf(byte_f(fqz, j), sz, bfz);
+            const float cmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, r.tmin));
+            const float cmax = fminf(fminf(tfx, tfy), fminf(tfz, r.best_t));
+            if (cmin <= cmax * kSlabPad)
               hitmask |= ((child_bits4 >> (8 * j)) & 0xFFu) << ((bit_index4 >> (8 * j)) & 0xFFu);
           }
         }
@@ -401,7 +401,8 @@ trace_wide8_kernel(const Node8* __restrict__ nodes8, const SortedTri* __restrict
     if (has_ray && tg.y != 0u) {
       const uint32_t bit = 31u - (uint32_t)__clz((int)tg.y);
       tg.y &= ~(1u << bit);
-      const bool hit = test_triangle8<WT>(tris8, tg.x + bit, r, wr, n_tests);
+      if (STATS) ++n_tests;
+      const bool hit = WT ? intersect_wt(tris8, tg.x + bit, r, wr) : intersect(tris8, tg.x + bit, r);
       if (ANY && hit) {
         tg.y = 0u;
         ng.y = 0u;

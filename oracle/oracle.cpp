@@ -613,6 +613,23 @@ inline float inv_dir(float d) {
   return nmin(nmax(1.0f / d, -fmx), fmx);
 }
 
+// A6, second half of the acceptance rule: the hit must be consistent with the triangle's own
+// box (the tree's leaf box: ordered min/max of the three vertices): slab() passes on it and its
+// entry distance satisfies tnear <= t * kSlabPad.  A node is culled when tnear > min(tfar,
+// best_t) * pad, ancestors contain the leaf box and slab() is monotone in the box, so a
+// triangle with an acceptable hit is never below a culled node: the result is min over the
+// triangles with a consistent hit by (t, prim), whatever the tree and the visiting order, and
+// the all-pairs intersector below returns the same bytes as any BVH traversal.
+inline bool own_box_admits(const float* p, const Ray& r, const float idir[3], float best_t, float t) {
+  float bx[6];
+  for (int k = 0; k < 3; ++k) {
+    bx[k] = omin(omin(p[k], p[4 + k]), p[8 + k]);
+    bx[3 + k] = omax(omax(p[k], p[4 + k]), p[8 + k]);
+  }
+  float tn;
+  return slab(bx, r, idir, best_t, tn) && tn <= t * kSlabPad;
+}
+
 enum { TRACE_CLOSEST = 0, TRACE_ANY = 1, TRACE_WATERTIGHT = 2 };
 const int32_t kAnyHitPrim = 0x7FFFFFFF;
 
@@ -641,7 +658,7 @@ Hit trace_one(const Bvh& b, const Ray& r, uint32_t flags, uint64_t& nodes, uint6
       ++tests;
       const float* tp = b.T + (uint64_t)prim * 12;
       if ((wt ? tri_test_wt(tp, r, wr, t, u, v) : tri_test(tp, r, t, u, v)) &&
-          accept(t, (int32_t)prim, r.tmin, best_t, best_prim)) {
+          accept(t, (int32_t)prim, r.tmin, best_t, best_prim) && own_box_admits(tp, r, idir, best_t, t)) {
         best_t = t; best_prim = (int32_t)prim; bu = u; bv = v;
         if (any) break;
       }
@@ -1243,9 +1260,11 @@ ORC_API void orc_brute(const float* tris, uint64_t n, const float* rays, uint64_
     const bool wt = (flags & TRACE_WATERTIGHT) != 0;
     WtRay wr = {0, 1, 2, 0, 0, 0};
     if (wt) wr = wt_setup(r);
+    const float idir[3] = {inv_dir(r.d[0]), inv_dir(r.d[1]), inv_dir(r.d[2])};
     for (uint64_t p = 0; p < n; ++p) {
       float t, u, v;
-      if ((wt ? tri_test_wt(tris + p * 12, r, wr, t, u, v) : tri_test(tris + p * 12, r, t, u, v)) && accept(t, (int32_t)p, r.tmin, best_t, best_prim)) {
+      if ((wt ? tri_test_wt(tris + p * 12, r, wr, t, u, v) : tri_test(tris + p * 12, r, t, u, v)) &&
+          accept(t, (int32_t)p, r.tmin, best_t, best_prim) && own_box_admits(tris + p * 12, r, idir, best_t, t)) {
         best_t = t; best_prim = (int32_t)p; bu = u; bv = v;
       }
     }
