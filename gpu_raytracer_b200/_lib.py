@@ -20,6 +20,7 @@ RT_SCENE_CORNELL, RT_SCENE_SOUP, RT_SCENE_SPHEREFLAKE, RT_SCENE_TERRAIN = 0, 1, 
 RT_MULTI_REDUNDANT, RT_MULTI_BROADCAST = 0, 1
 RT_STAGE_NAMES = ("bounds", "morton", "sort", "topology", "refit", "total", "wide")
 RT_MAX_TRIS = (1 << 30) - 1
+RT_SORT_STATIC_MAX_PAIRS = 1 << 20
 
 
 class BuildOpts(C.Structure):
@@ -71,6 +72,7 @@ SIGNATURES = {
     "rt_set_param": (_i32, [C.c_char_p, C.c_int64]),
     "rt_sort_pairs": (_i32, [_vp, _vp, _u64, _u32, _vp]),
     "rt_trim": (_i32, [_i32]),
+    "rt_sort_pairs_static": (_i32, [_vp, _vp, _u64, _vp]),
     "trace_camera": (_i32, [_vp, _vp, _u32, _u32, _u64, _u64, _u32, _vp]),
     "rt_shard_range": (_i32, [_u64, _i32, _i32, C.POINTER(_u64), C.POINTER(_u64)]),
     "build_bvh_multi": (_i32, [_vp, _u64, C.POINTER(BuildOpts), C.POINTER(_i32), _i32, _i32,

@@ -407,6 +407,13 @@ def sort_pairs(keys, vals, key_bits: int = 30) -> float:
     return float(ms.value)
 
 
+def sort_pairs_static(keys, vals, stream: int = 0) -> None:
+    """rt_sort_pairs_static: in-place device sort of (30-bit u32 keys, u32 payloads) that
+    allocates nothing (static device scratch, at most RT_SORT_STATIC_MAX_PAIRS pairs);
+    enqueued on ``stream``, not synchronised."""
+    L.check(L.lib().rt_sort_pairs_static(keys.data_ptr(), vals.data_ptr(), int(keys.numel()), stream or None))
+
+
 def set_param(name: str, value: int) -> None:
     L.check(L.lib().rt_set_param(name.encode(), value))
 

@@ -318,6 +318,19 @@ RT_API int rt_set_param(const char* name, int64_t value);
  * u64 keys.  keys/vals are overwritten with the sorted result. ms (may be
  * NULL) receives the device time of the sort alone. */
 RT_API int rt_sort_pairs(void* keys, uint32_t* vals, uint64_t n, uint32_t key_bits, float* ms);
+/* The same sort without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid it).  Sorts n pairs of 30-bit keys (u32, bits 30-31
+ * zero) and u32 payloads, both device memory of the CURRENT device, in place, stably, on
+ * `stream` (cudaStream_t, NULL = legacy default stream); it enqueues memsets and kernels and
+ * returns without synchronising, and calls no cudaMalloc / cudaFree / allocating routine.  The
+ * scratch memory is a static device array of 19.9 MB that every GPU which loads the library
+ * holds until the process exits; hence the limit: n <= RT_SORT_STATIC_MAX_PAIRS, beyond which
+ * the call fails with RT_ERR_LIMIT.  All calls share that array: calls that overlap on one GPU
+ * (two streams, two host threads) race on it; calls on one stream are safe back to back.  Same
+ * result as rt_sort_pairs(keys, vals, n, 30, NULL), bit for bit. */
+#define RT_SORT_STATIC_MAX_PAIRS (1ull << 20)
+RT_API int rt_sort_pairs_static(uint32_t* keys, uint32_t* vals, uint64_t n, void* stream);
 RT_API const char* rt_version(void);
 
 #ifdef __cplusplus
