@@ -72,6 +72,10 @@ SIGNATURES = {
     "rt_set_param": (_i32, [C.c_char_p, C.c_int64]),
     "rt_sort_pairs": (_i32, [_vp, _vp, _u64, _u32, _vp]),
     "rt_trim": (_i32, [_i32]),
+    "rt_merge_hits": (_i32, [C.POINTER(_vp), C.POINTER(_u32), _i32, _u64, _u32, _vp, _vp]),
+    "build_bvh_sharded": (_i32, [_vp, _u64, C.POINTER(BuildOpts), C.POINTER(_i32), _i32, C.POINTER(_vp),
+                                 C.POINTER(_u32)]),
+    "trace_rays_merged": (_i32, [C.POINTER(_vp), C.POINTER(_u32), _i32, _vp, _u64, _u32, _vp]),
     "rt_sort_pairs_static": (_i32, [_vp, _vp, _u64, _vp]),
     "trace_camera": (_i32, [_vp, _vp, _u32, _u32, _u64, _u64, _u32, _vp]),
     "rt_shard_range": (_i32, [_u64, _i32, _i32, C.POINTER(_u64), C.POINTER(_u64)]),

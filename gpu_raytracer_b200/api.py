@@ -387,6 +387,57 @@ class MultiBvh:
         self.close()
 
 
+def merge_hits(parts, prim_base=None, flags: int = L.RT_TRACE_CLOSEST, out=None, stream: int = 0):
+    """rt_merge_hits: per ray the best of the parts' hits by (t, prim + base); parts: CUDA tensors
+    [n, 4] of the same rays traced against different parts of a scene."""
+    k = len(parts)
+    n = _rows(parts[0], 4)
+    ptrs = (C.c_void_p * k)(*[p.data_ptr() for p in parts])
+    base = (C.c_uint32 * k)(*([int(b) for b in prim_base] if prim_base is not None else [0] * k))
+    if out is None:
+        out = torch.empty((n, 4), dtype=torch.float32, device=parts[0].device)
+    L.check(L.lib().rt_merge_hits(ptrs, base, k, n, flags, _ptr(out), stream or None))
+    return out
+
+
+class ShardedBvh:
+    """The SCENE sharded over devices in this process (build_bvh_sharded / trace_rays_merged):
+    part i holds a contiguous range of the triangles; hits are merged by (t, prim)."""
+
+    def __init__(self, handles, prim_base):
+        self.handles, self.prim_base = handles, list(prim_base)
+        self._arr = (C.c_void_p * len(handles))(*[h._h for h in handles])
+        self._base = (C.c_uint32 * len(handles))(*self.prim_base)
+
+    @classmethod
+    def build(cls, tris, devices, key_bits: int = 30) -> "ShardedBvh":
+        n = _rows(tris, 12)
+        opts = L.BuildOpts(key_bits=key_bits, flags=0, device=-1, reserved=0, stream=None)
+        devs = (C.c_int32 * len(devices))(*devices)
+        out = (C.c_void_p * len(devices))()
+        base = (C.c_uint32 * len(devices))()
+        L.check(L.lib().build_bvh_sharded(_ptr(tris) if n else None, n, C.byref(opts), devs, len(devices), out, base))
+        return cls([Bvh(out[i]) for i in range(len(devices))], [int(b) for b in base])
+
+    def trace(self, rays, flags: int = L.RT_TRACE_CLOSEST, out=None):
+        n = _rows(rays, 8)
+        if out is None:
+            out = _empty_like_kind(rays, (n, 4), None)
+        L.check(L.lib().trace_rays_merged(self._arr, self._base, len(self.handles), _ptr(rays), n, flags, _ptr(out)))
+        return out
+
+    def close(self) -> None:
+        for h in self.handles:
+            h.close()
+        self.handles = []
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+
 def trim(device: int = -1) -> None:
     """Returns the library's cached pool memory to the driver (rt_trim)."""
     L.check(L.lib().rt_trim(device))

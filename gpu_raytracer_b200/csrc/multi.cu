@@ -266,3 +266,166 @@ extern "C" int trace_random_sharded(rt_bvh* const* handles, int n_devices, const
     return 0;
   });
 }
+
+// ===========================================================================
+// Sharded build: the SCENE is cut, not the rays.
+//
+// Device i builds a BVH over a contiguous range of the triangle array (1/N of the build work
+// and of the memory per GPU: the way to scenes beyond one GPU's memory), every device traces
+// all rays against its part, and the parts' hits are merged: per ray the minimum by (t,
+// primitive index), the primitive index made global by adding the range's first triangle.
+// This is exact, not approximate: the acceptance rule (trace_common.cuh accept_hit) makes the
+// accepted hit of a ray min over {triangles with a consistent hit} by (t, prim), a function
+// of the ray and the triangles alone, so the minimum over the parts' minima is what one BVH
+// over all triangles returns, bit for bit (tests/test_round2_gpu.py).  Any-hit: occluded when
+// any part is.  The merge is the path's one exchange step; between processes it is an
+// all-to-all of hit records (gpu_raytracer_b200/sharding.py ShardedScene), inside one process
+// peer copies to the first device.
+// ===========================================================================
+namespace {
+
+constexpr int kMaxParts = 16;
+struct MergeParts {
+  const float4* part[kMaxParts];
+  uint32_t base[kMaxParts];
+  int n;
+};
+
+__global__ void __launch_bounds__(256)
+merge_hits_kernel(MergeParts parts, uint64_t n, bool any, float4* __restrict__ out) {
+  const float inf = __int_as_float(0x7f800000);
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+    float4 best = make_float4(inf, 0.0f, 0.0f, __int_as_float(-1));
+    int best_prim = -1;
+    for (int k = 0; k < parts.n; ++k) {
+      const float4 h = parts.part[k][i];
+      const int prim = __float_as_int(h.w);
+      if (prim < 0) continue;
+      if (any) {
+        best = make_float4(0.0f, 0.0f, 0.0f, __int_as_float(0x7FFFFFFF));
+        best_prim = 0x7FFFFFFF;
+        break;
+      }
+      const int gp = prim + (int)parts.base[k];
+      if (best_prim < 0 || h.x < best.x || (h.x == best.x && gp < best_prim)) {
+        best = make_float4(h.x, h.y, h.z, __int_as_float(gp));
+        best_prim = gp;
+      }
+    }
+    out[i] = best;
+  }
+}
+
+}  // namespace
+
+extern "C" int rt_merge_hits(const float* const* parts, const uint32_t* prim_base, int n_parts, uint64_t n,
+                             uint32_t flags, float* out, void* stream) {
+  if (!parts || n_parts <= 0 || n_parts > kMaxParts)
+    return fail(RT_ERR_INVALID, "rt_merge_hits: 1..%d parts", kMaxParts);
+  if (n == 0) return RT_OK;
+  if (!out) return fail(RT_ERR_INVALID, "rt_merge_hits: out is NULL");
+  RT_TRY(ensure_device());
+  MergeParts mp;
+  mp.n = n_parts;
+  for (int k = 0; k < n_parts; ++k) {
+    if (!parts[k] || !classify(parts[k], nullptr)) return fail(RT_ERR_INVALID, "rt_merge_hits: part %d is not device memory", k);
+    mp.part[k] = reinterpret_cast<const float4*>(parts[k]);
+    mp.base[k] = prim_base ? prim_base[k] : 0u;
+  }
+  if (!classify(out, nullptr)) return fail(RT_ERR_INVALID, "rt_merge_hits: out is not device memory");
+  uint64_t blocks = (n + 255) / 256;
+  const uint64_t cap = (uint64_t)num_sms() * 16;
+  if (blocks > cap) blocks = cap;
+  merge_hits_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(mp, n, (flags & RT_TRACE_ANY) != 0,
+                                                                       reinterpret_cast<float4*>(out));
+  RT_LAUNCHED();
+  return RT_OK;
+}
+
+extern "C" int build_bvh_sharded(const float* tris, uint64_t n_tris, const rt_build_opts* opts,
+                                 const int* devices, int n_devices, rt_bvh** out, uint32_t* prim_base) {
+  if (!out || !prim_base) return fail(RT_ERR_INVALID, "build_bvh_sharded: out or prim_base is NULL");
+  for (int i = 0; i < (n_devices > 0 ? n_devices : 0); ++i) out[i] = nullptr;
+  RT_TRY(check_devices(devices, n_devices, "build_bvh_sharded"));
+  if (n_devices > kMaxParts) return fail(RT_ERR_LIMIT, "build_bvh_sharded: at most %d parts", kMaxParts);
+  if (n_tris > 0x7FFFFFFEull) return fail(RT_ERR_LIMIT, "build_bvh_sharded: global primitive indices are 31-bit");
+  if (n_tris && !tris) return fail(RT_ERR_INVALID, "build_bvh_sharded: tris is NULL");
+  if (n_tris && classify(tris, nullptr))
+    return fail(RT_ERR_INVALID, "build_bvh_sharded: tris is a host array (each device uploads its own range)");
+  if (opts && opts->stream) return fail(RT_ERR_INVALID, "build_bvh_sharded: leave opts->stream NULL");
+  for (int i = 0; i < n_devices; ++i) prim_base[i] = (uint32_t)(n_tris * (uint64_t)i / (uint64_t)n_devices);
+  const int rc = for_each_device(n_devices, [&](int i) -> int {
+    const uint64_t first = prim_base[i];
+    const uint64_t last = n_tris * (uint64_t)(i + 1) / (uint64_t)n_devices;
+    rt_build_opts o;
+    memset(&o, 0, sizeof(o));
+    if (opts) o = *opts;
+    o.device = devices[i];
+    o.stream = nullptr;
+    return build_bvh(tris + 12 * first, last - first, &o, &out[i]);
+  });
+  if (rc != 0) {
+    std::string keep = bvh_last_error();
+    for (int i = 0; i < n_devices; ++i) {
+      free_bvh(out[i]);
+      out[i] = nullptr;
+    }
+    return fail(rc, "%s", keep.c_str());
+  }
+  return RT_OK;
+}
+
+extern "C" int trace_rays_merged(rt_bvh* const* handles, const uint32_t* prim_base, int n_devices,
+                                 const float* rays, uint64_t n_rays, uint32_t flags, float* hits) {
+  if (!handles || n_devices <= 0 || n_devices > kMaxParts)
+    return fail(RT_ERR_INVALID, "trace_rays_merged: 1..%d handles", kMaxParts);
+  for (int i = 0; i < n_devices; ++i)
+    if (!handles[i]) return fail(RT_ERR_INVALID, "trace_rays_merged: handle %d is NULL", i);
+  if (n_rays == 0) return RT_OK;
+  if (!rays || !hits) return fail(RT_ERR_INVALID, "trace_rays_merged: rays or hits is NULL");
+  if (flags > 7u) return fail(RT_ERR_INVALID, "trace_rays_merged: unknown flags 0x%x", flags);
+  if (classify(rays, nullptr) || classify(hits, nullptr))
+    return fail(RT_ERR_INVALID, "trace_rays_merged: rays and hits are host buffers");
+  const int dev0 = handles[0]->device;
+  const uint64_t kBatch = 1ull << 22;  // rays per round: 128 MiB up, 64 MiB of hits per part
+  for (uint64_t first = 0; first < n_rays; first += kBatch) {
+    const uint64_t cnt = n_rays - first < kBatch ? n_rays - first : kBatch;
+    // the parts' hits, gathered on the first handle's device
+    DeviceScope scope0;
+    RT_TRY(scope0.enter(dev0));
+    cudaStream_t s0 = 0;
+    TempPool tmp0(s0);
+    float4* gathered = nullptr;
+    float4* merged = nullptr;
+    RT_TRY(tmp0.alloc((void**)&gathered, (size_t)n_devices * cnt * 16));
+    RT_TRY(tmp0.alloc((void**)&merged, cnt * 16));
+    RT_CUDA(cudaStreamSynchronize(s0));
+    RT_TRY(for_each_device(n_devices, [&](int i) -> int {
+      const rt_bvh* h = handles[i];
+      DeviceScope scope;
+      RT_TRY(scope.enter(h->device));
+      cudaStream_t s = 0;
+      TempPool tmp(s);
+      float4 *d_rays = nullptr, *d_hits = nullptr;
+      RT_TRY(tmp.alloc((void**)&d_rays, cnt * 32));
+      RT_CUDA(cudaMemcpyAsync(d_rays, rays + 8 * first, cnt * 32, cudaMemcpyHostToDevice, s));
+      float4* dst = gathered + (size_t)i * cnt;
+      if (h->device == dev0) {
+        RT_TRY(trace_device(h, d_rays, cnt, flags, dst, s));
+      } else {
+        RT_TRY(tmp.alloc((void**)&d_hits, cnt * 16));
+        RT_TRY(trace_device(h, d_rays, cnt, flags, d_hits, s));
+        allow_peer(dev0, h->device);
+        RT_CUDA(cudaMemcpyPeerAsync(dst, dev0, d_hits, h->device, cnt * 16, s));
+      }
+      RT_CUDA(cudaStreamSynchronize(s));
+      return 0;
+    }));
+    const float* parts[kMaxParts];
+    for (int i = 0; i < n_devices; ++i) parts[i] = reinterpret_cast<const float*>(gathered + (size_t)i * cnt);
+    RT_TRY(rt_merge_hits(parts, prim_base, n_devices, cnt, flags, reinterpret_cast<float*>(merged), s0));
+    RT_CUDA(cudaMemcpyAsync(hits + 4 * first, merged, cnt * 16, cudaMemcpyDeviceToHost, s0));
+    RT_CUDA(cudaStreamSynchronize(s0));
+  }
+  return RT_OK;
+}

@@ -86,18 +86,25 @@ __device__ __forceinline__ bool slab(const float4 lo, const float4 hi, const Ray
 // all-pairs intersector (oracle brute) all return bit for bit.  (Without it the answer
 // depended on the order in marginal cases: a triangle whose computed t lies a few ulps before
 // its own flat box could be culled, or not, depending on what had been found before.)
-// The box is only evaluated for candidates that would otherwise be accepted: rare, so free.
-__device__ __forceinline__ bool accept_hit(float t, float u, float v, const float4 v0, const float4 v1,
-                                           const float4 v2, RayState& r) {
-  const int prim = __float_as_int(v0.w);
-  bool ok = (t > r.tmin) &&
-            ((t < r.best_t) || (t == r.best_t && r.best_prim >= 0 && prim < r.best_prim));
-  if (ok) {
-    float tn;
-    ok = slab(omin(omin(v0.x, v1.x), v2.x), omin(omin(v0.y, v1.y), v2.y), omin(omin(v0.z, v1.z), v2.z),
+// The box is only evaluated for candidates that would otherwise be accepted (about one in three
+// triangle tests), in a function of its own that reads the vertices again (L1 hits): inlined,
+// the twelve vertex floats stayed live across the triangle test and cost 7-9 registers, i.e.
+// one of five resident CTAs per SM.
+static __device__ __noinline__ bool own_box_admits(const float4* __restrict__ tp, float ox, float oy, float oz,
+                                            float ix, float iy, float iz, float tmin, float best_t, float t) {
+  const float4 v0 = __ldg(tp), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
+  RayState r;
+  r.ox = ox; r.oy = oy; r.oz = oz; r.ix = ix; r.iy = iy; r.iz = iz; r.tmin = tmin; r.best_t = best_t;
+  float tn;
+  return slab(omin(omin(v0.x, v1.x), v2.x), omin(omin(v0.y, v1.y), v2.y), omin(omin(v0.z, v1.z), v2.z),
               omax(omax(v0.x, v1.x), v2.x), omax(omax(v0.y, v1.y), v2.y), omax(omax(v0.z, v1.z), v2.z), r, tn) &&
          tn <= t * kSlabPad;
-  }
+}
+__device__ __forceinline__ bool accept_hit(float t, float u, float v, int prim, const float4* __restrict__ tp,
+                                           RayState& r) {
+  bool ok = (t > r.tmin) &&
+            ((t < r.best_t) || (t == r.best_t && r.best_prim >= 0 && prim < r.best_prim));
+  if (ok) ok = own_box_admits(tp, r.ox, r.oy, r.oz, r.ix, r.iy, r.iz, r.tmin, r.best_t, t);
   if (ok) {
     r.best_t = t;
     r.bu = u;
@@ -130,7 +137,7 @@ __device__ __forceinline__ bool intersect(const SortedTri* __restrict__ stris, u
   const float v = fmaf(r.dx, qx, fmaf(r.dy, qy, r.dz * qz)) * inv;
   const float t = fmaf(e2x, qx, fmaf(e2y, qy, e2z * qz)) * inv;
   if (!((u >= 0.0f) && (v >= 0.0f) && ((u + v) <= 1.0f))) return false;
-  return accept_hit(t, u, v, v0, v1, v2, r);
+  return accept_hit(t, u, v, __float_as_int(v0.w), tp, r);
 }
 
 // Watertight test (Woop, Benthin & Wald 2013), RT_TRACE_WATERTIGHT: the ray is
@@ -189,7 +196,7 @@ __device__ __forceinline__ bool intersect_wt(const SortedTri* __restrict__ stris
   const float Az = w.Sz * Akz, Bz = w.Sz * Bkz, Cz = w.Sz * Ckz;
   const float T = (U * Az + V * Bz) + W * Cz;
   const float inv = 1.0f / det;
-  return accept_hit(T * inv, V * inv, W * inv, v0, v1, v2, r);
+  return accept_hit(T * inv, V * inv, W * inv, __float_as_int(v0.w), tp, r);
 }
 
 // 1/d of one direction component, clamped to +-FLT_MAX so that a denormal component gives

@@ -148,7 +148,7 @@ __device__ __forceinline__ float4 ld_cg_f4(const float4* p) {
 }
 
 template <bool ANY, bool STATS, bool WT, bool PIPE, int SHS>
-__global__ void __launch_bounds__(kTraceThreads)
+__global__ void __launch_bounds__(kTraceThreads, (PIPE || WT || STATS) ? 1 : 5)
 trace_kernel_dyn(const Node* __restrict__ nodes, const SortedTri* __restrict__ stris,
                  uint32_t n_tris, int root, const float4* __restrict__ rays,
                  unsigned long long n_rays, float4* __restrict__ hits,

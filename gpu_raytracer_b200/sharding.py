@@ -100,3 +100,79 @@ def gather_hits(local_hits: np.ndarray, n_rays: int, rank: int, world: int, grou
     outs = [torch.empty_like(mine) for _ in range(world)]
     dist.all_gather(outs, mine, group=group)
     return np.concatenate([outs[r].numpy()[:counts[r]] for r in range(world)], axis=0)
+
+
+# ---------------------------------------------------------------------------
+# Sharded BUILD: the scene is cut, the hits are exchanged
+# ---------------------------------------------------------------------------
+def tri_range(n_tris: int, rank: int, world: int) -> Tuple[int, int]:
+    """(first, count) of rank's contiguous range of the triangle array (build_bvh_sharded's cut)."""
+    first = n_tris * rank // world
+    return first, n_tris * (rank + 1) // world - first
+
+
+def merge_hits_host(parts, prim_base, any_hit: bool = False) -> np.ndarray:
+    """numpy statement of rt_merge_hits (tests; the product path is the CUDA kernel): per ray
+    the minimum over the parts by (t, prim + base); any-hit: occluded if any part is."""
+    parts = [np.ascontiguousarray(p, dtype=np.float32).reshape(-1, 4) for p in parts]
+    n = parts[0].shape[0]
+    out = np.zeros((n, 4), dtype=np.float32)
+    out[:, 0] = np.inf
+    best_prim = np.full(n, -1, dtype=np.int64)
+    for p, base in zip(parts, prim_base):
+        prim = np.ascontiguousarray(p[:, 3]).view(np.int32).astype(np.int64)
+        hit = prim >= 0
+        if any_hit:
+            best_prim[hit] = 0x7FFFFFFF
+            continue
+        gp = prim + int(base)
+        better = hit & ((best_prim < 0) | (p[:, 0] < out[:, 0]) | ((p[:, 0] == out[:, 0]) & (gp < best_prim)))
+        out[better, :3] = p[better, :3]
+        best_prim[better] = gp[better]
+    if any_hit:
+        out[best_prim >= 0, 0] = 0.0
+    out[:, 3] = best_prim.astype(np.int32).view(np.float32)
+    return out
+
+
+def exchange_layout(n_rays: int, world: int):
+    """Send/receive counts (in rays) of the all-to-all that turns "every rank holds the hits of
+    ALL rays against ITS part" into "every rank holds ALL parts' hits of ITS ray range"."""
+    counts = [shard_range(n_rays, r, world)[1] for r in range(world)]
+    return counts
+
+
+class ShardedScene:
+    """One part of a scene per rank (one process per GPU).  Every rank traces the whole ray
+    batch against its part; one all-to-all moves, for every ray range, the parts' hit records
+    to the rank that owns the range; rt_merge_hits reduces them by (t, prim).  The result is
+    sharded by rays like everything else here, and equals the single-BVH hits bit for bit."""
+
+    def __init__(self, bvh, first_tri: int, n_tris_total: int, group=None):
+        self.bvh, self.first_tri, self.n_tris_total, self.group = bvh, first_tri, n_tris_total, group
+
+    @classmethod
+    def build(cls, tris_local, first_tri: int, n_tris_total: int, key_bits: int = 30, group=None):
+        from .api import Bvh
+        return cls(Bvh.build(tris_local, key_bits=key_bits), first_tri, n_tris_total, group)
+
+    def trace(self, rays, flags: int = 0):
+        """rays: CUDA tensor [n, 8], the SAME batch on every rank.  Returns (first, hits) of this
+        rank's ray range, merged over all parts."""
+        import torch
+        import torch.distributed as dist
+        from . import api
+        rank, world = dist.get_rank(self.group), dist.get_world_size(self.group)
+        n = int(rays.shape[0])
+        local = self.bvh.trace(rays, flags)                       # hits of all rays against this part
+        counts = exchange_layout(n, world)
+        first, mine = shard_range(n, rank, world)
+        recv = torch.empty((world * mine, 4), dtype=torch.float32, device=rays.device)
+        dist.all_to_all_single(recv, local, output_split_sizes=[mine] * world,
+                               input_split_sizes=counts, group=self.group)
+        bases = [tri_range(self.n_tris_total, r, world)[0] for r in range(world)]
+        parts = [recv[r * mine:(r + 1) * mine] for r in range(world)]
+        return first, api.merge_hits(parts, bases, flags & 1) if mine else recv[:0]
+
+    def close(self):
+        self.bvh.close()

@@ -251,6 +251,27 @@ RT_API int trace_random_sharded(rt_bvh* const* handles, int n_devices, const flo
                                 uint64_t first, uint64_t n_rays, uint32_t flags, uint64_t batch,
                                 float* hits, uint64_t* n_hit, float* trace_ms);
 
+/* Sharded BUILD: the scene is cut instead of the rays, for scenes beyond one
+ * GPU's memory and for 1/N of the build time.  Part i is an ordinary BVH over a contiguous range
+ * of the triangle array; every part traces all rays; the parts' hits are merged per ray by (t,
+ * primitive index + the range's first triangle).  Because a ray's accepted hit is the minimum
+ * over all triangles by (t, prim) whatever tree holds them, the merged hits equal one
+ * build_bvh + trace_rays over the whole array bit for bit (any-hit: occluded if any part is).
+ *
+ * rt_merge_hits: parts: host array of n_parts (<= 16) DEVICE pointers to n x 4 hit records of
+ * the same rays; prim_base[k] is added to part k's primitive indices (NULL = zeros); out:
+ * device, n x 4; enqueued on stream.  This is the exchange step: between processes, move the
+ * parts with an all-to-all or all-gather of hit records and call it (sharding.ShardedScene).
+ * build_bvh_sharded: tris: HOST array; device i builds triangles [prim_base[i], prim_base[i+1]).
+ * trace_rays_merged: host rays / host hits; each device uploads and traces all rays, the hits
+ * are gathered on handles[0]'s device by peer copies and merged there. */
+RT_API int rt_merge_hits(const float* const* parts, const uint32_t* prim_base, int n_parts, uint64_t n,
+                         uint32_t flags, float* out, void* stream);
+RT_API int build_bvh_sharded(const float* tris, uint64_t n_tris, const rt_build_opts* opts,
+                             const int* devices, int n_devices, rt_bvh** out, uint32_t* prim_base);
+RT_API int trace_rays_merged(rt_bvh* const* handles, const uint32_t* prim_base, int n_devices,
+                             const float* rays, uint64_t n_rays, uint32_t flags, float* hits);
+
 /* ---- scene input and BVH files --------------------- */
 
 /* Reads a Wavefront OBJ file: "v x y z" and "f a b c ..." records (a, a/t, a//n,

@@ -421,3 +421,39 @@ def test_c99_program_runs_on_the_device(rt, tmp_path):
                     f"-Wl,-rpath,{lib_dir}", "-lm"], check=True)
     res = subprocess.run([str(exe)], capture_output=True, text=True)
     assert res.returncode == 0 and res.stdout.strip() == "ok", res.stdout + res.stderr
+
+
+# ---- sharded BUILD (§8f.4) -------------------------------------------------------------------------------
+@pytest.mark.parametrize("parts", [1, 2, 3, 5])
+def test_sharded_build_merges_to_the_single_bvh(rt, oracle, parts):
+    """build_bvh_sharded / trace_rays_merged / rt_merge_hits: the SCENE cut into contiguous ranges
+    of the triangle array, one BVH per range (all on GPU 0 here; the last on another GPU when
+    there is one), every part traces all rays, hits merged by (t, prim + base): the single
+    BVH's hits, bit for bit, for closest / any-hit / watertight."""
+    devices = [0] * parts
+    if torch.cuda.device_count() > 1 and parts > 1:
+        devices[-1] = torch.cuda.device_count() - 1
+    tris = oracle.gen_scene(oracle.SCENE_SPHEREFLAKE, 3, 4, 0)
+    ob = oracle.OracleBvh(tris)
+    rays = oracle.gen_random_rays(ob.bounds, 4, 0, 300_001)
+    cam = rt.camera.frame_box(ob.bounds, 320, 200)
+    rays = np.concatenate([rays, oracle.gen_primary_rays(cam, 320, 200)])
+    with rt.ShardedBvh.build(tris, devices) as sb:
+        from gpu_raytracer_b200 import sharding
+        assert sb.prim_base == [sharding.tri_range(ob.n, r, parts)[0] for r in range(parts)]
+        assert sum(h.n_tris for h in sb.handles) == ob.n
+        for flags in (0, rt.RT_TRACE_ANY, rt.RT_TRACE_WATERTIGHT):
+            want = ob.trace(rays, flags)
+            got = sb.trace(rays, flags)
+            assert np.array_equal(bits(got), bits(want)), (parts, flags)
+        # the exchange step alone: device hits of every part, merged by the kernel == numpy statement
+        d_rays = dev(rays)
+        local = [h.trace(d_rays) for h in sb.handles if h.info().device == 0]
+        if len(local) == parts:
+            merged = rt.merge_hits(local, sb.prim_base).cpu().numpy()
+            assert np.array_equal(bits(merged), bits(ob.trace(rays)))
+            host = sharding.merge_hits_host([x.cpu().numpy() for x in local], sb.prim_base)
+            assert np.array_equal(bits(host), bits(merged))
+    ob.close()
+    with pytest.raises(rt.RtError):
+        rt.ShardedBvh.build(dev(tris), [0])          # device triangles: each part uploads its own range
