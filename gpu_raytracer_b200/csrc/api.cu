@@ -22,6 +22,7 @@ namespace rt {
 
 std::atomic<uint64_t> g_kernel_launches{0};
 int g_pdl = 1;
+extern int g_build_walk_shape;  // refit.cu
 
 namespace {
 thread_local char t_error[512] = "";
@@ -1406,6 +1407,7 @@ extern "C" int rt_set_param(const char* name, int64_t value) {
   else if (!strcmp(name, "trace.leaf_min")) p.trace_leaf_min = (int)value;
   else if (!strcmp(name, "trace.sh_stack")) p.trace_sh_stack = (int)value;
   else if (!strcmp(name, "build.pdl")) g_pdl = value != 0;
+  else if (!strcmp(name, "build.walk")) g_build_walk_shape = (int)value;
   else if (!strcmp(name, "pool.keep_mb")) {
     p.pool_keep_mb = (int)value;
     std::lock_guard<std::mutex> lock(g_pool_mu);

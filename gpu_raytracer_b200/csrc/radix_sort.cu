@@ -172,10 +172,12 @@ struct SortCfg {
 // 32-bit keys travel between the passes as packed 64-bit records
 // (key << 32 | payload): one load, one shared-memory slot and one scattered
 // store per element instead of two.  64-bit keys keep separate arrays.
-template <typename KeyT, int BITS, int THREADS, int IPT>
+template <typename KeyT, int BITS, int THREADS, int IPT, bool TMA = false>
 struct SortSmem {
   using C = SortCfg<KeyT, BITS, THREADS, IPT>;
   static constexpr bool kPacked = sizeof(KeyT) == 4;
+  alignas(16) uint64_t in_tile[TMA ? C::kTile : 2];  // TMA: the next input tile, landed by cp.async.bulk
+  alignas(8) uint64_t mbar;                            // TMA: its mbarrier
   uint64_t keys[C::kTile];                   // packed records, or the 64-bit keys
   uint32_t vals[kPacked ? 1 : C::kTile];     // payload of 64-bit keys
   uint32_t bin_base[C::kBins];
@@ -221,18 +223,46 @@ __device__ __forceinline__ uint32_t warp_rank(volatile uint16_t* wh, volatile ui
   return c + __popc(peers & lt_mask);
 }
 
+// ---- TMA-staged input tiles (variant 3; BASELINE.json:5 "shared-memory/TMA-staged tiles") ----------
+// One elected thread asks the copy engine for the whole tile (a 1-D cp.async.bulk, SASS
+// UBLKCP) and the CTA waits on an mbarrier; the LSU then carries no global loads for the
+// records.  Measured against the register prefetch: profiles/r02j_sort_tma_ab.md.
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void tma_load_1d(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t}"
+      ::"r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+}
+
 // IN: kInSplit (keys_in + vals_in), kInIota (keys_in, payload = position),
 //     kInRec (recs_in, 32-bit keys only).   OUT: kOutSplit or kOutRec.
-template <typename KeyT, int BITS, int THREADS, int IPT, int MIN_BLOCKS, int IN, int OUT>
+template <typename KeyT, int BITS, int THREADS, int IPT, int MIN_BLOCKS, int IN, int OUT, bool TMA = false>
 __global__ void __launch_bounds__(THREADS, MIN_BLOCKS)
 scatter_kernel(const KeyT* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                const uint2* __restrict__ recs_in, KeyT* __restrict__ keys_out,
                uint32_t* __restrict__ vals_out, uint2* __restrict__ recs_out,
                const uint32_t* __restrict__ chunk_offsets, ChunkGeom g, int shift) {
   using C = SortCfg<KeyT, BITS, THREADS, IPT>;
-  using Smem = SortSmem<KeyT, BITS, THREADS, IPT>;
+  using Smem = SortSmem<KeyT, BITS, THREADS, IPT, TMA>;
   constexpr bool kPacked = Smem::kPacked;
   static_assert(kPacked || (IN != kInRec && OUT != kOutRec), "records carry 32-bit keys");
+  static_assert(!TMA || IN == kInRec, "TMA stages packed records");
   constexpr int kTile = C::kTile, kBins = C::kBins, kBPT = C::kBPT, kPPT = C::kPPT;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   Smem& sm = *reinterpret_cast<Smem*>(smem_raw);
@@ -287,11 +317,43 @@ scatter_kernel(const KeyT* __restrict__ keys_in, const uint32_t* __restrict__ va
       else if (IN == kInSplit) val[k] = (whole || (k < steps && idx < chunk_end)) ? vals_in[idx] : 0u;
     }
   };
-  if (n_tiles) load_keys(chunk_begin);
+  // TMA: a tile whose byte count is a multiple of 16 comes through the copy engine, any
+  // other (only the odd-sized last tile of the array) through plain loads
+  auto tma_ok = [&](uint32_t tile_begin) {
+    return TMA && ((min(tile_size, chunk_end - tile_begin) & 1u) == 0u);
+  };
+  auto tma_issue = [&](uint32_t tile_begin) {  // one thread; in_tile is free (everybody has read it)
+    if (TMA && tid == 0)
+      tma_load_1d(sm.in_tile, recs_in + tile_begin, min(tile_size, chunk_end - tile_begin) * 8u, &sm.mbar);
+  };
+  auto tma_consume = [&](uint32_t tile_begin, uint32_t parity) {
+    mbar_wait(&sm.mbar, parity);
+    const uint32_t off = (uint32_t)warp * seg + lane;
+#pragma unroll
+    for (int k = 0; k < IPT; ++k) {
+      const uint32_t idx = tile_begin + off + k * 32;
+      const bool ok = k < steps && idx < chunk_end;
+      const uint64_t r = ok ? sm.in_tile[off + k * 32] : 0xFFFFFFFF00000000ull;
+      key[k] = (KeyT)(uint32_t)(r >> 32);
+      val[k] = (uint32_t)r;
+    }
+  };
+  uint32_t tma_phase = 0;
+  if (TMA) {
+    if (tid == 0) mbar_init(&sm.mbar, 1);
+    __syncthreads();
+  }
+  if (n_tiles) {
+    if (tma_ok(chunk_begin)) tma_issue(chunk_begin); else load_keys(chunk_begin);
+  }
 
   for (uint32_t t = 0; t < n_tiles; ++t) {
     const uint32_t tile_begin = chunk_begin + t * tile_size;
     const uint32_t tile_n = min(tile_size, chunk_end - tile_begin);
+    if (tma_ok(tile_begin)) {
+      tma_consume(tile_begin, tma_phase);
+      tma_phase ^= 1u;
+    }
 
     {  // each warp clears its private counters (32-bit words = two counters)
       uint32_t* w32 = reinterpret_cast<uint32_t*>(sm.warp_hist[warp]);
@@ -318,6 +380,8 @@ scatter_kernel(const KeyT* __restrict__ keys_in, const uint32_t* __restrict__ va
     // payload: issued now so the loads fly during the fold
     if (IN != kInRec) load_vals(tile_begin);
     __syncthreads();
+    // TMA: everybody has taken its records out of in_tile: the next tile may land in it
+    if (TMA && t + 1 < n_tiles && tma_ok(tile_begin + tile_size)) tma_issue(tile_begin + tile_size);
 
     // ---- fold the warp counters, scan the bin totals ---------------------------
     uint32_t total[kBPT];
@@ -390,7 +454,7 @@ scatter_kernel(const KeyT* __restrict__ keys_in, const uint32_t* __restrict__ va
     __syncthreads();
 
     // next tile's keys travel while this tile is written out
-    if (t + 1 < n_tiles) load_keys(tile_begin + tile_size);
+    if (t + 1 < n_tiles && !tma_ok(tile_begin + tile_size)) load_keys(tile_begin + tile_size);
 
     // ---- coalesced write-out -------------------------------------------------------
     auto emit = [&](uint32_t p) {
@@ -423,9 +487,11 @@ scatter_kernel(const KeyT* __restrict__ keys_in, const uint32_t* __restrict__ va
 struct Shape {
   int threads, ipt32, ipt64, ctas_per_sm;
 };
-// variant 0: 512 threads, 2 CTAs/SM; variant 1: 256 threads, 4 CTAs/SM
-constexpr int kNumVariants = 2;
-constexpr Shape kShapes[kNumVariants] = {{512, 15, 10, 2}, {256, 16, 11, 4}};
+// variant 0: 512 threads, 2 CTAs/SM; variant 1: 256 threads, 4 CTAs/SM; variants 2 and 3 (30-bit
+// keys, 10-bit digits only; experiments): 512 threads x 9 keys, 2 CTAs/SM, without and with
+// TMA-staged record tiles (two tile buffers of 36 KB fit next to the counters twice per SM)
+constexpr int kNumVariants = 4;
+constexpr Shape kShapes[kNumVariants] = {{512, 15, 10, 2}, {256, 16, 11, 4}, {512, 9, 10, 2}, {512, 9, 10, 2}};
 
 int clamp_variant() {
   int v = params().sort_variant;
@@ -434,7 +500,9 @@ int clamp_variant() {
 
 }  // namespace
 ChunkGeom sort_geometry(uint64_t n, uint32_t key_bits) {
-  const Shape& sh = kShapes[clamp_variant()];
+  int v = clamp_variant();
+  if (v >= 2 && (key_bits != 30 || sort_plan(30).bits != 10)) v = 0;  // variants 2, 3: 30-bit keys, 10-bit digits
+  const Shape& sh = kShapes[v];
   const uint64_t tile = (uint64_t)sh.threads * (key_bits == 30 ? sh.ipt32 : sh.ipt64);
   uint64_t max_ctas = (uint64_t)num_sms() * sh.ctas_per_sm;
   // chunk_offsets_kernel scans at most 32 * kOffMaxRounds chunks per bin
@@ -466,12 +534,12 @@ struct PassIO {
   int in = kInSplit, out = kOutSplit;
 };
 
-template <typename KeyT, int BITS, int THREADS, int IPT, int MIN_BLOCKS, int IN, int OUT>
+template <typename KeyT, int BITS, int THREADS, int IPT, int MIN_BLOCKS, int IN, int OUT, bool TMA = false>
 int launch_scatter_io(const PassIO& io, const uint32_t* offsets, const ChunkGeom& g, int shift,
                       cudaStream_t s) {
-  using Smem = SortSmem<KeyT, BITS, THREADS, IPT>;
+  using Smem = SortSmem<KeyT, BITS, THREADS, IPT, TMA>;
   const size_t smem = sizeof(Smem);
-  auto kern = scatter_kernel<KeyT, BITS, THREADS, IPT, MIN_BLOCKS, IN, OUT>;
+  auto kern = scatter_kernel<KeyT, BITS, THREADS, IPT, MIN_BLOCKS, IN, OUT, TMA>;
   RT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   RT_CUDA(launch_pdl(kern, g.chunks, THREADS, smem, s, (const KeyT*)io.keys_in, io.vals_in,
                      io.recs_in, (KeyT*)io.keys_out, io.vals_out, io.recs_out, offsets, g, shift));
@@ -479,7 +547,7 @@ int launch_scatter_io(const PassIO& io, const uint32_t* offsets, const ChunkGeom
   return 0;
 }
 
-template <typename KeyT, int BITS, int THREADS, int IPT, int MIN_BLOCKS>
+template <typename KeyT, int BITS, int THREADS, int IPT, int MIN_BLOCKS, bool TMA = false>
 int launch_scatter(const PassIO& io, const uint32_t* offsets, const ChunkGeom& g, int shift,
                    cudaStream_t s) {
   if (sizeof(KeyT) == 8) {
@@ -495,8 +563,8 @@ int launch_scatter(const PassIO& io, const uint32_t* offsets, const ChunkGeom& g
     if (io.in == kInSplit)
       return launch_scatter_io<K, BITS, THREADS, IPT, MIN_BLOCKS, kInSplit, kOutRec>(io, offsets, g, shift, s);
     if (io.out == kOutRec)
-      return launch_scatter_io<K, BITS, THREADS, IPT, MIN_BLOCKS, kInRec, kOutRec>(io, offsets, g, shift, s);
-    return launch_scatter_io<K, BITS, THREADS, IPT, MIN_BLOCKS, kInRec, kOutSplit>(io, offsets, g, shift, s);
+      return launch_scatter_io<K, BITS, THREADS, IPT, MIN_BLOCKS, kInRec, kOutRec, TMA>(io, offsets, g, shift, s);
+    return launch_scatter_io<K, BITS, THREADS, IPT, MIN_BLOCKS, kInRec, kOutSplit, TMA>(io, offsets, g, shift, s);
   }
 }
 
@@ -517,6 +585,10 @@ int run_pass(int variant, const PassIO& io, uint32_t* chunk_hist, uint32_t* tota
   RT_CUDA(launch_pdl(chunk_offsets_kernel<BITS>, kBins / kOffWarps, kOffWarps * 32, 0, s, chunk_hist,
                      totals, g.chunks));
   RT_LAUNCHED();
+  if constexpr (BITS == 10 && !k64) {
+    if (variant == 2) return launch_scatter<KeyT, BITS, 512, 9, 2>(io, chunk_hist, g, shift, s);
+    if (variant == 3) return launch_scatter<KeyT, BITS, 512, 9, 2, true>(io, chunk_hist, g, shift, s);
+  }
   if (variant == 1)
     return launch_scatter<KeyT, BITS, 256, k64 ? 11 : 16, 4>(io, chunk_hist, g, shift, s);
   return launch_scatter<KeyT, BITS, 512, k64 ? 10 : 15, 2>(io, chunk_hist, g, shift, s);

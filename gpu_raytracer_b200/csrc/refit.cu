@@ -219,100 +219,135 @@ __device__ __forceinline__ void park_or_climb(const Box& bx, int enc, uint32_t L
   }
 }
 
-template <typename KeyT>
-__global__ void __launch_bounds__(kRefitLeaves)
+// Shared state of one build CTA: G = THREADS x LPT consecutive leaves (the table-driven refit
+// keeps its own group size, kRefitLeaves; the two are independent).
+template <int G>
+struct BuildSmem {
+  float4 dep_lo[2][G];  // min.xyz, child id
+  float4 dep_hi[2][G];  // max.xyz, far end of the child's leaf range
+  uint32_t flag[G];
+  uint8_t delta[G + 8];  // delta(base - 1 + t), t in [0, G]
+};
+
+// LPT consecutive leaves per thread, climbed one after the other through the same meeting
+// protocol (a first arriver deposits and stops, whoever comes second — another thread, or
+// the same thread with its next leaf — unions and climbs on).  The lowest levels of the
+// tree, where most meetings happen, are then mostly meetings of a thread with itself, the
+// work per thread is the sum of LPT climbs instead of one (less variance inside a warp: ncu
+// showed 9.9 of 32 lanes active with one leaf per thread), a thread has 3 x LPT independent
+// triangle loads in flight, and a group of G leaves parks 1/LPT of the walkers per leaf.
+template <typename KeyT, int THREADS, int LPT>
+__global__ void __launch_bounds__(THREADS)
 build_walk_kernel(const float4* __restrict__ tris, const uint32_t* __restrict__ sorted_idx,
                   const KeyT* __restrict__ keys, uint32_t n, uint32_t* __restrict__ flags,
                   Node* __restrict__ nodes,
                   SortedTri* __restrict__ stris, BvhHeader* __restrict__ header,
                   Continuation* __restrict__ queue, uint32_t* __restrict__ queue_count,
                   uint32_t capacity, const uint32_t* __restrict__ abort_flag) {
+  constexpr int G = THREADS * LPT;
   extern __shared__ __align__(16) unsigned char refit_smem_raw[];
-  RefitSmem& sm = *reinterpret_cast<RefitSmem*>(refit_smem_raw);
+  BuildSmem<G>& sm = *reinterpret_cast<BuildSmem<G>*>(refit_smem_raw);
   pdl_enter();
   if (abort_flag != nullptr && *abort_flag != 0u) return;  // the sort gave up (hybrid order, long run)
   const uint32_t tid = threadIdx.x;
-  const uint32_t base = blockIdx.x * kRefitLeaves;
-  const uint32_t j = base + tid;
-  sm.flag[tid] = 0;
-  // delta(i) for i = base - 1 + t: thread t owns slot t, thread 0 also the last one
-  {
-    const uint32_t i = j - 1u;  // wraps for j == 0: guarded
-    if (j >= 1u && j < n) sm.delta[tid] = (uint8_t)delta_adj<KeyT>(keys[i], keys[j], i);
-    if (tid == 0) {
-      const uint32_t e = base + kRefitLeaves;  // delta(e - 1)
-      if (e < n) sm.delta[kRefitLeaves] = (uint8_t)delta_adj<KeyT>(keys[e - 1], keys[e], e - 1);
+  const uint32_t base = blockIdx.x * G;
+  // delta(i) for i = base - 1 + t, t in [0, G]
+  for (uint32_t t = tid; t <= (uint32_t)G; t += THREADS) {
+    const uint32_t j = base + t;
+    if (t < (uint32_t)G) sm.flag[t] = 0;
+    if (j >= 1u && j < n) sm.delta[t] = (uint8_t)delta_adj<KeyT>(keys[j - 1u], keys[j], j - 1u);
+  }
+  // the thread's leaves: gather the triangles (all loads first), store them in traversal form
+  const uint32_t j0 = base + tid * LPT;
+  Box bx[LPT];
+  uint32_t prim[LPT];
+  float4 va[LPT], vb[LPT], vc[LPT];
+#pragma unroll
+  for (int i = 0; i < LPT; ++i) prim[i] = (j0 + i < n) ? sorted_idx[j0 + i] : 0u;
+#pragma unroll
+  for (int i = 0; i < LPT; ++i) {
+    if (j0 + i < n) {
+      va[i] = __ldg(tris + 3 * (uint64_t)prim[i]);
+      vb[i] = __ldg(tris + 3 * (uint64_t)prim[i] + 1);
+      vc[i] = __ldg(tris + 3 * (uint64_t)prim[i] + 2);
     }
   }
-  Box bx;
-  int enc = ~(int)j;
-  uint32_t L = j, R = j;
-  bool alive = j < n;
-  if (alive) {
-    const uint32_t prim = sorted_idx[j];
-    const float4 a = __ldg(tris + 3 * (uint64_t)prim), b = __ldg(tris + 3 * (uint64_t)prim + 1),
-                 c = __ldg(tris + 3 * (uint64_t)prim + 2);
-    // 48-byte records: the 32-byte aligned part goes out as one full sector
-    float4* st = reinterpret_cast<float4*>(stris + j);
-    const float4 r0 = make_float4(a.x, a.y, a.z, __uint_as_float(prim));
-    const float4 r1 = make_float4(b.x, b.y, b.z, 0.0f), r2 = make_float4(c.x, c.y, c.z, 0.0f);
-    if ((j & 1u) == 0u) {
-      st_v8(st, r0, r1);
-      st[2] = r2;
-    } else {
-      st[0] = r0;
-      st_v8(st + 1, r1, r2);
+#pragma unroll
+  for (int i = 0; i < LPT; ++i) {
+    const uint32_t j = j0 + i;
+    if (j < n) {
+      const float4 a = va[i], b = vb[i], c = vc[i];
+      // 48-byte records: the 32-byte aligned part goes out as one full sector
+      float4* st = reinterpret_cast<float4*>(stris + j);
+      const float4 r0 = make_float4(a.x, a.y, a.z, __uint_as_float(prim[i]));
+      const float4 r1 = make_float4(b.x, b.y, b.z, 0.0f), r2 = make_float4(c.x, c.y, c.z, 0.0f);
+      if ((j & 1u) == 0u) {
+        st_v8(st, r0, r1);
+        st[2] = r2;
+      } else {
+        st[0] = r0;
+        st_v8(st + 1, r1, r2);
+      }
+      bx[i].lx = omin(omin(a.x, b.x), c.x); bx[i].ly = omin(omin(a.y, b.y), c.y); bx[i].lz = omin(omin(a.z, b.z), c.z);
+      bx[i].hx = omax(omax(a.x, b.x), c.x); bx[i].hy = omax(omax(a.y, b.y), c.y); bx[i].hz = omax(omax(a.z, b.z), c.z);
     }
-    bx.lx = omin(omin(a.x, b.x), c.x); bx.ly = omin(omin(a.y, b.y), c.y); bx.lz = omin(omin(a.z, b.z), c.z);
-    bx.hx = omax(omax(a.x, b.x), c.x); bx.hy = omax(omax(a.y, b.y), c.y); bx.hz = omax(omax(a.z, b.z), c.z);
   }
   __syncthreads();
 
   // ---- phase 1: meetings inside the group, in shared memory -----------------------
-  while (alive) {
-    if (L == 0u && R == n - 1u) {
-      store_root(bx, enc, header);
-      break;
+#pragma unroll 1
+  for (int i = 0; i < LPT; ++i) {
+    const uint32_t j = j0 + i;
+    Box b = bx[i];
+    int enc = ~(int)j;
+    uint32_t L = j, R = j;
+    bool alive = j < n;
+    while (alive) {
+      if (L == 0u && R == n - 1u) {
+        store_root(b, enc, header);
+        break;
+      }
+      // L >= base and R < base + G hold for every walker in this loop
+      bool left = (L == 0u);
+      if (!left && R != n - 1u) left = sm.delta[R - base + 1u] > sm.delta[L - base];
+      const uint32_t g = left ? R : L - 1u, slot = left ? 0u : 1u;
+      const float4 my_lo = make_float4(b.lx, b.ly, b.lz, __int_as_float(enc));
+      const float4 my_hi = make_float4(b.hx, b.hy, b.hz, __uint_as_float(left ? L : R));
+      float4* np = reinterpret_cast<float4*>(nodes + g) + 2 * slot;
+      if (g < base || g + 1u >= base + (uint32_t)G) {
+        // the sibling starts or ends in another group: device-scope meeting
+        park_or_climb<KeyT>(b, enc, L, R, queue, queue_count, capacity, keys, n, flags, nodes, header);
+        break;
+      }
+      const uint32_t k = g - base;
+      sm.dep_lo[slot][k] = my_lo;
+      sm.dep_hi[slot][k] = my_hi;
+      const uint32_t seen = arrive_or_cta(&sm.flag[k], 1u << slot);
+      // the node half goes out after the meeting, so no fence ever waits for it
+      st_v8(np, my_lo, my_hi);
+      if (seen == 0u) break;  // first arriver stops
+      const float4 slo = lds_volatile_v4(&sm.dep_lo[slot ^ 1u][k]);
+      const float4 shi = lds_volatile_v4(&sm.dep_hi[slot ^ 1u][k]);
+      b.lx = omin(b.lx, slo.x); b.ly = omin(b.ly, slo.y); b.lz = omin(b.lz, slo.z);
+      b.hx = omax(b.hx, shi.x); b.hy = omax(b.hy, shi.y); b.hz = omax(b.hz, shi.z);
+      if (left) R = __float_as_uint(shi.w); else L = __float_as_uint(shi.w);
+      enc = (int)g;
     }
-    // L >= base and R < base + kRefitLeaves hold for every walker in this loop
-    bool left = (L == 0u);
-    if (!left && R != n - 1u) left = sm.delta[R - base + 1u] > sm.delta[L - base];
-    const uint32_t g = left ? R : L - 1u, slot = left ? 0u : 1u;
-    const float4 my_lo = make_float4(bx.lx, bx.ly, bx.lz, __int_as_float(enc));
-    const float4 my_hi = make_float4(bx.hx, bx.hy, bx.hz, __uint_as_float(left ? L : R));
-    float4* np = reinterpret_cast<float4*>(nodes + g) + 2 * slot;
-    if (g < base || g + 1u >= base + kRefitLeaves) {
-      // the sibling starts or ends in another group: device-scope meeting
-      park_or_climb<KeyT>(bx, enc, L, R, queue, queue_count, capacity, keys, n, flags, nodes,
-                          header);
-      break;
-    }
-    const uint32_t k = g - base;
-    sm.dep_lo[slot][k] = my_lo;
-    sm.dep_hi[slot][k] = my_hi;
-    const uint32_t seen = arrive_or_cta(&sm.flag[k], 1u << slot);
-    // the node half goes out after the meeting, so no fence ever waits for it
-    st_v8(np, my_lo, my_hi);
-    if (seen == 0u) break;  // first arriver stops
-    const float4 slo = lds_volatile_v4(&sm.dep_lo[slot ^ 1u][k]);
-    const float4 shi = lds_volatile_v4(&sm.dep_hi[slot ^ 1u][k]);
-    bx.lx = omin(bx.lx, slo.x); bx.ly = omin(bx.ly, slo.y); bx.lz = omin(bx.lz, slo.z);
-    bx.hx = omax(bx.hx, shi.x); bx.hy = omax(bx.hy, shi.y); bx.hz = omax(bx.hz, shi.z);
-    if (left) R = __float_as_uint(shi.w); else L = __float_as_uint(shi.w);
-    enc = (int)g;
   }
   __syncthreads();
 
   // ---- phase 2: a slot with one child only waits for a sibling from elsewhere --------
-  const uint32_t f = sm.flag[tid];
-  if (f == 1u || f == 2u) {
-    const uint32_t slot = f - 1u, g = base + tid;
-    const float4 dlo = sm.dep_lo[slot][tid], dhi = sm.dep_hi[slot][tid];
-    Box b2{dlo.x, dlo.y, dlo.z, dhi.x, dhi.y, dhi.z};
-    const uint32_t far_end = __float_as_uint(dhi.w);
-    const uint32_t l2 = slot ? g + 1u : far_end, r2 = slot ? far_end : g;
-    park_or_climb<KeyT>(b2, __float_as_int(dlo.w), l2, r2, queue, queue_count, capacity, keys, n, flags,
-                        nodes, header);
+  for (uint32_t k = tid; k < (uint32_t)G; k += THREADS) {
+    const uint32_t f = sm.flag[k];
+    if (f == 1u || f == 2u) {
+      const uint32_t slot = f - 1u, g = base + k;
+      const float4 dlo = sm.dep_lo[slot][k], dhi = sm.dep_hi[slot][k];
+      Box b2{dlo.x, dlo.y, dlo.z, dhi.x, dhi.y, dhi.z};
+      const uint32_t far_end = __float_as_uint(dhi.w);
+      const uint32_t l2 = slot ? g + 1u : far_end, r2 = slot ? far_end : g;
+      park_or_climb<KeyT>(b2, __float_as_int(dlo.w), l2, r2, queue, queue_count, capacity, keys, n, flags,
+                          nodes, header);
+    }
   }
 }
 
@@ -567,22 +602,44 @@ size_t refit_queue_bytes(uint64_t n) {
   return 32 + (size_t)queue_capacity(n) * sizeof(Continuation);
 }
 
+template <typename KeyT, int THREADS, int LPT>
+static int launch_walk(const float4* tris, const uint32_t* sorted_idx, const KeyT* keys, uint64_t n,
+                       uint32_t* flags, Node* nodes, SortedTri* stris, BvhHeader* header,
+                       Continuation* queue, uint32_t* queue_count, uint32_t capacity, cudaStream_t s,
+                       const uint32_t* abort_flag) {
+  constexpr int G = THREADS * LPT;
+  const unsigned blocks = (unsigned)((n + G - 1) / G);
+  const size_t smem = sizeof(BuildSmem<G>);
+  auto kern = build_walk_kernel<KeyT, THREADS, LPT>;
+  RT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  RT_CUDA(launch_pdl(kern, blocks, THREADS, smem, s, tris, sorted_idx, keys, (uint32_t)n, flags, nodes, stris,
+                     header, queue, queue_count, capacity, abort_flag));
+  RT_LAUNCHED();
+  return 0;
+}
+
+int g_build_walk_shape = 0;  // rt_set_param("build.walk"): THREADS * 16 + LPT; 0 = default
+
 template <typename KeyT>
 static int build_tree_impl(const float4* tris, const uint32_t* sorted_idx, const KeyT* keys,
                            uint64_t n, uint32_t* flags, Node* nodes, SortedTri* stris,
                            BvhHeader* header, void* queue_buf, cudaStream_t s,
                            const uint32_t* abort_flag) {
-  const unsigned blocks = (unsigned)((n + kRefitLeaves - 1) / kRefitLeaves);
   const uint32_t capacity = queue_capacity(n);
   uint32_t* queue_count;
   Continuation* queue;
   queue_layout(queue_buf, &queue_count, &queue);
-  const size_t smem = sizeof(RefitSmem);
-  RT_CUDA(cudaFuncSetAttribute(build_walk_kernel<KeyT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                               (int)smem));
-  RT_CUDA(launch_pdl(build_walk_kernel<KeyT>, blocks, kRefitLeaves, smem, s, tris, sorted_idx, keys,
-                     (uint32_t)n, flags, nodes, stris, header, queue, queue_count, capacity, abort_flag));
-  RT_LAUNCHED();
+#define RT_WALK(T, L) launch_walk<KeyT, T, L>(tris, sorted_idx, keys, n, flags, nodes, stris, header, queue, \
+                                               queue_count, capacity, s, abort_flag)
+  switch (g_build_walk_shape) {
+    case 256 * 16 + 2: RT_TRY(RT_WALK(256, 2)); break;
+    case 256 * 16 + 4: RT_TRY(RT_WALK(256, 4)); break;
+    case 128 * 16 + 2: RT_TRY(RT_WALK(128, 2)); break;
+    case 128 * 16 + 4: RT_TRY(RT_WALK(128, 4)); break;
+    case 64 * 16 + 4: RT_TRY(RT_WALK(64, 4)); break;
+    default: RT_TRY(RT_WALK(256, 1)); break;
+  }
+#undef RT_WALK
   RT_CUDA(launch_pdl(build_top_kernel<KeyT>, (capacity + 255) / 256, 256, 0, s,
                      (const Continuation*)queue, (const uint32_t*)queue_count, capacity, keys,
                      (uint32_t)n, flags, nodes, header, abort_flag));

@@ -232,7 +232,7 @@ def test_edge_cases(rt, oracle):
 
 
 # ---- sort alone (A3) ----------------------------------------------------------------
-@pytest.mark.parametrize("variant", [0, 1])
+@pytest.mark.parametrize("variant", [0, 1, 2, 3])
 @pytest.mark.parametrize("bits", [0, 8, 9, 10, 11])
 @pytest.mark.parametrize("key_bits", [30, 63])
 def test_sort_pairs_is_stable(rt, variant, bits, key_bits):
