@@ -457,3 +457,21 @@ def test_sharded_build_merges_to_the_single_bvh(rt, oracle, parts):
     ob.close()
     with pytest.raises(rt.RtError):
         rt.ShardedBvh.build(dev(tris), [0])          # device triangles: each part uploads its own range
+
+
+@pytest.mark.parametrize("shape", [256 * 16 + 2, 128 * 16 + 4, 64 * 16 + 4])
+def test_walk_kernel_shapes_build_the_same_tree(rt, oracle, shape):
+    """`build.walk` (threads * 16 + leaves per thread): the bottom-up pass with several consecutive
+    leaves per thread (measured slower than one, profiles/r02k_walk_shapes.jsonl; kept as a knob)
+    builds the oracle's tree bit for bit."""
+    rt.set_param("build.walk", shape)
+    try:
+        for n, kb in [(2, 30), (3, 30), (255, 30), (257, 63), (1025, 30), (40001, 30), (200000, 63)]:
+            t = oracle.gen_scene(oracle.SCENE_SOUP, n, 0, seed=n)
+            ob = oracle.OracleBvh(t, kb)
+            with rt.Bvh.build(dev(t), key_bits=kb) as b:
+                l, r, p = b.read_topology()
+                assert np.array_equal(l, ob.left) and np.array_equal(r, ob.right) and np.array_equal(p, ob.parent), n
+                assert np.array_equal(bits(b.read_boxes()), bits(ob.boxes)), n
+    finally:
+        rt.set_param("build.walk", 0)
