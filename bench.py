@@ -519,6 +519,8 @@ def run_ours(args):
     h_hits = torch.empty((count, 4), dtype=torch.float32).pin_memory()
     h_rgb = torch.empty((count, 3), dtype=torch.float32).pin_memory()
     Ke = max(3, min(K, 10))
+    s_down = torch.cuda.Stream()
+    ev_hits = torch.cuda.Event()
     eb = et = ec = 0.0
     d_rgb = None
     for it in range(2 + Ke):
@@ -537,7 +539,10 @@ def run_ours(args):
             # and consumed (rt_shade) on the device: they are intermediates, not results
             d_rays = h_rays.cuda(non_blocking=True)
             bvh.trace_async(d_rays, hits)
-            h_hits.copy_(hits, non_blocking=True)
+            ev_hits.record()
+            with torch.cuda.stream(s_down):                # the hits go down while the AO pass runs
+                s_down.wait_event(ev_hits)
+                h_hits.copy_(hits, non_blocking=True)
             g.gen_ao_rays(d_tris, d_rays, hits, wl.ao_spp, wl.ao_seed, radius, out=ao_rays)
             bvh.trace_async(ao_rays, ao_hits, g.RT_TRACE_ANY)
             d_rgb = g.shade(d_tris, d_rays, hits, ao_hits, wl.ao_spp)
