@@ -358,11 +358,14 @@ def run_ours(args):
             for name in ("plain", "reorder"):
                 gbs = bpr * rec[name]["mrays_s"] / 1e3
                 rec[name]["roofline"] = {"achieved_gbs": gbs, "frac": gbs / peak}
-            nc = ncu_record("random1b")
-            if nc.get("dram_bytes_per_ray"):
-                rec["per_ray"]["dram_bytes_ncu"] = nc["dram_bytes_per_ray"]
-                rec["plain"]["roofline"]["dram_frac"] = (
-                    nc["dram_bytes_per_ray"] * rec["plain"]["mrays_s"] / 1e3 / peak)
+            for name, key in (("plain", "random1b"), ("reorder", "random1b:reorder")):
+                nc = ncu_record(key)
+                if nc.get("dram_bytes_per_ray"):
+                    rec[name]["roofline"]["dram_bytes_per_ray_ncu"] = nc["dram_bytes_per_ray"]
+                    rec[name]["roofline"]["dram_frac"] = nc["dram_bytes_per_ray"] * rec[name]["mrays_s"] / 1e3 / peak
+                if nc.get("l1_lsu_wavefront_pct") and nc.get("ncu_us"):
+                    rec[name]["roofline"]["l1_frac"] = (nc["l1_lsu_wavefront_pct"] / 100.0 *
+                                                        (nc["ncu_us"] / nc["rays"]) * rec[name]["mrays_s"])
         return rec
 
     wl = WORKLOADS[args.workload]
@@ -625,10 +628,11 @@ def run_ours(args):
              "traffic": nc.get("dram_bytes"),
              # (i) what the launch really moved over HBM, as a fraction of peak
              "dram_frac": (nc["dram_bytes"] / ms / 1e6 / peak) if nc.get("dram_bytes") else None,
-             # (ii) L1 sector roofline: sectors the launch requested / time, against the
-             # L1's 4 sectors (128 B) per clock and SM at the maximum clock
+             # (ii) L1 roofline: the unit ncu shows busiest is the LSU data pipe (one wavefront per
+             # clock and SM): its share of peak under ncu, rescaled to this run's duration
              "l1_sectors": nc.get("l1_sectors"),
-             "l1_frac": (nc["l1_sectors"] / (ms * 1e-3) / (4 * 148 * 1.965e9)) if nc.get("l1_sectors") else None}
+             "l1_frac": (nc["l1_lsu_wavefront_pct"] / 100.0 * (nc["ncu_us"] / 1e3) / ms)
+                        if nc.get("l1_lsu_wavefront_pct") and nc.get("ncu_us") else None}
         return r
     kr = {"primary": kernel_roofline(wl.name + ":primary", "trace_kernel_dyn<closest>", bytes_primary,
                                      trace_ms / K, count, nodes, tests)}
@@ -642,7 +646,7 @@ def run_ours(args):
             "note": "achieved = algorithmic bytes (48 + 64 x nodes fetched + 48 x triangles tested per ray, "
                     "counted by trace_rays_stats) / CUDA-event time.  The BVH of a coherent frame is served "
                     "from L1/L2, so `frac` can exceed 1 and says nothing about distance to a bound; "
-                    "`dram_frac` (ncu dram bytes) and `l1_frac` (ncu l1tex sectors against 4 sectors/clk/SM) "
+                    "`dram_frac` (ncu dram bytes / time / peak) and `l1_frac` (ncu: LSU data-pipe wavefronts, share of the pipe's peak) "
                     "are the fractions of real limits, and configs.random1b.*.roofline is the genuine "
                     "HBM fraction of §8(d) (working set 1.1 GB >> L2)",
             "stages": stages}

@@ -45,9 +45,9 @@ def main():
         rec = {"kernel": r[ix["Kernel Name"]][:80], "ncu_us": col(r, "gpu__time_duration.sum"),
                "dram_bytes": dram, "dram_bytes_per_ray": dram / n_rays,
                "l1_sectors": col(r, "l1tex__t_sectors.sum"),
-               "l1_hit_pct": col(r, "l1tex__t_sector_hit_rate.pct"),
+               "l1_sectors_miss": col(r, "l1tex__t_sectors_lookup_miss.sum"),
+               "l1_lsu_wavefront_pct": col(r, "l1tex__data_pipe_lsu_wavefronts.avg.pct_of_peak_sustained_elapsed"),
                "l2_hit_pct": col(r, "lts__t_sector_hit_rate.pct"),
-               "l1tex_pct": col(r, "l1tex__throughput.avg.pct_of_peak_sustained_elapsed"),
                "lts_pct": col(r, "lts__throughput.avg.pct_of_peak_sustained_elapsed"),
                "dram_pct": col(r, "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed"),
                "issue_pct": col(r, "smsp__issue_active.avg.pct_of_peak_sustained_active"),
