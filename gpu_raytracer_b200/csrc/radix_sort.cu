@@ -2,7 +2,8 @@
 // primitive index) pairs.
 //
 // B200 shape of the algorithm.  A decoupled look-back onesweep (Adinets &
-// Merrill 2022) was built and measured first (profiles/r01c_*): at ~0.05 us
+// Merrill 2022) was built and measured first (round 1; the kernel is in the history, git show
+// 8291441:gpu_raytracer_b200/csrc/radix_sort.cu; its measurements were not kept): at ~0.05 us
 // between tile starts and ~0.7 us per L2 round trip every tile had to walk
 // 10-20 predecessors for each of its 256-1024 bins, and the look-back words
 // cost more L2 traffic than the pairs themselves.  This version has no
