@@ -21,8 +21,8 @@
 namespace rt {
 
 std::atomic<uint64_t> g_kernel_launches{0};
-int g_pdl = 1;
-extern int g_build_walk_shape;  // refit.cu
+std::atomic<int> g_pdl{1};
+extern std::atomic<int> g_build_walk_shape;  // refit.cu
 
 namespace {
 thread_local char t_error[512] = "";

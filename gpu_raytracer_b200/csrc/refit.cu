@@ -618,7 +618,7 @@ static int launch_walk(const float4* tris, const uint32_t* sorted_idx, const Key
   return 0;
 }
 
-int g_build_walk_shape = 0;  // rt_set_param("build.walk"): THREADS * 16 + LPT; 0 = default
+std::atomic<int> g_build_walk_shape{0};  // rt_set_param("build.walk"): THREADS * 16 + LPT; 0 = default
 
 template <typename KeyT>
 static int build_tree_impl(const float4* tris, const uint32_t* sorted_idx, const KeyT* keys,
@@ -631,7 +631,7 @@ static int build_tree_impl(const float4* tris, const uint32_t* sorted_idx, const
   queue_layout(queue_buf, &queue_count, &queue);
 #define RT_WALK(T, L) launch_walk<KeyT, T, L>(tris, sorted_idx, keys, n, flags, nodes, stris, header, queue, \
                                                queue_count, capacity, s, abort_flag)
-  switch (g_build_walk_shape) {
+  switch (g_build_walk_shape.load(std::memory_order_relaxed)) {
     case 256 * 16 + 2: RT_TRY(RT_WALK(256, 2)); break;
     case 256 * 16 + 4: RT_TRY(RT_WALK(256, 4)); break;
     case 128 * 16 + 2: RT_TRY(RT_WALK(128, 2)); break;
