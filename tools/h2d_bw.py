@@ -1,0 +1,58 @@
+"""Per-rank PCIe bandwidth with all ranks copying at once (run under torchrun, one rank per GPU):
+H2D alone, D2H alone, both directions together; pinned host memory, 512 MiB per copy, CUDA
+events, all ranks start behind a barrier.  Shows whether the end-to-end leg of bench.py at
+N = 8 is bound by one host memory system feeding eight links.
+One JSON line from rank 0: per-rank GB/s min / mean over ranks."""
+import json, os
+import torch
+import torch.distributed as dist
+
+rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
+torch.cuda.set_device(local)
+if world > 1:
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+n = 512 << 20
+h_a = torch.empty(n, dtype=torch.uint8).pin_memory()
+h_b = torch.empty(n, dtype=torch.uint8).pin_memory()
+d_a = torch.empty(n, dtype=torch.uint8, device="cuda")
+d_b = torch.empty(n, dtype=torch.uint8, device="cuda")
+s2 = torch.cuda.Stream()
+
+
+def timed(fn, reps=6):
+    best = 1e9
+    for _ in range(reps):
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        fn()
+        s2.synchronize() if False else None
+        e1.record()
+        torch.cuda.synchronize()
+        best = min(best, e0.elapsed_time(e1))
+    return n / best / 1e6  # GB/s
+
+
+def duplex():
+    d_a.copy_(h_a, non_blocking=True)
+    with torch.cuda.stream(s2):
+        h_b.copy_(d_b, non_blocking=True)
+    torch.cuda.current_stream().wait_stream(s2)
+
+
+res = [timed(lambda: d_a.copy_(h_a, non_blocking=True)), timed(lambda: h_b.copy_(d_b, non_blocking=True)), timed(duplex)]
+t = torch.tensor(res, dtype=torch.float64, device="cuda")
+if world > 1:
+    allr = [torch.zeros_like(t) for _ in range(world)]
+    dist.all_gather(allr, t)
+    allr = torch.stack(allr).cpu()
+else:
+    allr = t.cpu()[None]
+if rank == 0:
+    names = ["h2d_gbs", "d2h_gbs", "duplex_each_way_gbs"]
+    print(json.dumps({"n_gpus": world, **{k: {"min": float(allr[:, i].min()), "mean": float(allr[:, i].mean())} for i, k in enumerate(names)},
+                      "aggregate_h2d_gbs": float(allr[:, 0].sum())}), flush=True)
+if world > 1:
+    dist.destroy_process_group()
