@@ -36,8 +36,38 @@ for kind, p0, p1, seed, kb in [(g.RT_SCENE_CORNELL, 0, 0, 0, 30), (g.RT_SCENE_SO
         b.read_sorted(); b.read_topology(); b.read_boxes(); b.read_wide()
         b.refit(tris)
         b.trace(rays.cpu().numpy())           # staged host path
+    # round 2: compressed 8-wide layout, reorder, camera entry, sharded scene + merge, no-alloc sort
+    with g.Bvh.build(tris, key_bits=kb, wide8=True) as b8:
+        for flags in (0, 1, 2, g.RT_TRACE_REORDER):
+            b8.trace(g.gen_random_rays(box, 4, 0, 70000), flags)
+        b8.read_wide8()
+        b8.trace_camera(cam, 96, 64)
+        b8.refit(tris)
+    host = tris.cpu().numpy()
+    with g.ShardedBvh.build(host, [0, 0, 0]) as sb:
+        sb.trace(rays.cpu().numpy())
+    with g.MultiBvh.build(host, [0, 0], strategy=g.RT_MULTI_BROADCAST) as mb:
+        mb.trace(rays.cpu().numpy())
+        mb.trace_random(box, 4, 0, 50000, g.RT_TRACE_REORDER, batch=20000)
     print("ok", kind, int(tris.shape[0]), flush=True)
 k = torch.randint(0, 1 << 30, (100003,), device="cuda", dtype=torch.int32)
 g.sort_pairs(k, torch.arange(100003, device="cuda", dtype=torch.int32), 30)
 torch.cuda.synchronize()
 print("sanitize pass done")
+
+# round 2: the sort without allocations, twice on the shared static scratch; a BVH file round trip
+for n in (100003, 7001):
+    k2 = torch.randint(0, 1 << 30, (n,), device="cuda", dtype=torch.int32)
+    v2 = torch.arange(n, device="cuda", dtype=torch.int32)
+    g.sort_pairs_static(k2, v2)
+    torch.cuda.synchronize()
+    assert bool((k2[1:] >= k2[:-1]).all())
+import tempfile
+with tempfile.TemporaryDirectory() as d:
+    t = g.gen_scene(g.RT_SCENE_SOUP, 5000, 0, 3)
+    with g.Bvh.build(t) as b:
+        b.save(os.path.join(d, "a.bvh"))
+    with g.Bvh.load(os.path.join(d, "a.bvh")) as b:
+        b.widen8()
+        b.trace(g.gen_random_rays(b.bounds, 4, 0, 20000))
+print("round-2 paths ok", flush=True)
