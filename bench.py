@@ -524,8 +524,9 @@ def run_ours(args):
     Ke = max(3, min(K, 10))
     s_down = torch.cuda.Stream()
     ev_hits = torch.cuda.Event()
-    eb = et = ec = 0.0
+    eb = et = ec = es = 0.0
     d_rgb = None
+    one_call_rgb = None
     for it in range(2 + Ke):
         barrier()
         t0 = time.perf_counter()
@@ -538,8 +539,19 @@ def run_ours(args):
             bvh = g.Bvh.build(h_tris, key_bits=wl.key_bits)
         t1 = time.perf_counter()
         if wl.ao_spp:
-            # host rays up, primary hits + the shaded frame down; the AO rays are made, traced
-            # and consumed (rt_shade) on the device: they are intermediates, not results
+            # one call: host rays up, primary hits + the shaded frame down, in 1M-ray bands over
+            # three streams; the AO rays are made, traced and consumed on the device
+            bvh.render_ao(d_tris, h_rays, wl.ao_spp, wl.ao_seed, radius, hits=h_hits, rgb=h_rgb)
+        else:
+            bvh.trace(h_rays, out=h_hits)
+        t2 = time.perf_counter()
+        # the same frame from the 12-float camera: no ray upload (trace_camera)
+        bvh.trace_camera(cam, wl.width, wl.height, out=h_hits)
+        t3 = time.perf_counter()
+        if wl.ao_spp:
+            # the same frame through the four separate calls (whole-frame upload, then compute)
+            if it == 0:
+                one_call_rgb = h_rgb.clone()
             d_rays = h_rays.cuda(non_blocking=True)
             bvh.trace_async(d_rays, hits)
             ev_hits.record()
@@ -551,19 +563,16 @@ def run_ours(args):
             d_rgb = g.shade(d_tris, d_rays, hits, ao_hits, wl.ao_spp)
             h_rgb.copy_(d_rgb, non_blocking=True)
             torch.cuda.synchronize()
-        else:
-            bvh.trace(h_rays, out=h_hits)
-        t2 = time.perf_counter()
-        # the same frame from the 12-float camera: no ray upload (trace_camera)
-        bvh.trace_camera(cam, wl.width, wl.height, out=h_hits)
-        t3 = time.perf_counter()
+        t4 = time.perf_counter()
         bvh.close()
         if it >= 2:
-            eb, et, ec = eb + (t1 - t0), et + (t2 - t1), ec + (t3 - t2)
+            eb, et, ec, es = eb + (t1 - t0), et + (t2 - t1), ec + (t3 - t2), es + (t4 - t3)
     e2e_ok = bool(torch.equal(h_hits.view(torch.int32), hits.cpu().view(torch.int32)))  # bit compare: miss prim = -1 is a NaN pattern
+    if one_call_rgb is not None:                                # rt_render_ao's frame == the separate calls' frame
+        e2e_ok = e2e_ok and bool(torch.equal(one_call_rgb.view(torch.int32), h_rgb.view(torch.int32)))
     del h_tris, h_rays
 
-    build_ms, trace_ms, ao_ms, wall, eb, et, ec = max_over_ranks([build_ms, trace_ms, ao_ms, wall, eb, et, ec])
+    build_ms, trace_ms, ao_ms, wall, eb, et, ec, es = max_over_ranks([build_ms, trace_ms, ao_ms, wall, eb, et, ec, es])
 
     # ---- sub-records: config 5 at every N (strong scaling), config 4 at N = 1 ----
     configs = {}
@@ -680,11 +689,14 @@ def run_ours(args):
                 "d2h_bytes_per_step": int(count * 16 + (n_img * 12 if wl.ao_spp else 0) + 64),
                 "build_mtri_s": n_tris * Ke / eb / 1e6, "build_ms": eb / Ke * 1e3,
                 "trace_ms": et / Ke * 1e3, "steps": Ke, "hits_equal_device_path": e2e_ok,
+                "separate_calls": ({"mrays_s": e2e_rays * world * Ke / es / 1e6, "ms": es / Ke * 1e3,
+                                    "note": "trace_rays + rt_gen_ao_rays + trace_rays(any) + rt_shade, whole-frame copies"}
+                                   if wl.ao_spp else None),
                 "camera": {"mrays_s": count * world * Ke / ec / 1e6, "ms": ec / Ke * 1e3,
                            "h2d_bytes": 48, "d2h_bytes": int(count * 16),
                            "note": "trace_camera: primary rays generated on the device, hits to pinned host"},
-                "note": ("pinned host triangles -> build_bvh; pinned host primary rays up, primary hits + "
-                         "shaded frame (rt_shade over the AO hits) down; AO rays are device intermediates"
+                "note": ("pinned host triangles -> build_bvh; rt_render_ao: pinned host primary rays up, primary "
+                         "hits + shaded frame down in 1M-ray bands over three streams; AO rays are device intermediates"
                          if wl.ao_spp else
                          "pinned host tris/rays/hits through build_bvh / trace_rays")},
         "roofline": roof,

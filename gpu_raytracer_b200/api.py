@@ -218,6 +218,22 @@ class Bvh:
                                      _ptr(out)))
         return out
 
+    def render_ao(self, tris, rays, spp: int, seed: int, radius: float, flags: int = 0, hits=None, rgb=None):
+        """One frame in one call (rt_render_ao): primary trace, spp AO rays per pixel, their any-hit
+        trace and the shaded frame, pipelined in bands.  tris: CUDA tensor, original order.
+        Returns (hits [n, 4], rgb [n, 3]) of the same kind as ``rays``."""
+        n = _rows(rays, 8)
+        pin = _is_tensor(rays) and not rays.is_cuda and rays.is_pinned()
+        if hits is None:
+            hits = _empty_like_kind(rays, (n, 4), None)
+            hits = hits.pin_memory() if pin else hits
+        if rgb is None:
+            rgb = _empty_like_kind(rays, (n, 3), None)
+            rgb = rgb.pin_memory() if pin else rgb
+        L.check(L.lib().rt_render_ao(self._h, _ptr(tris), _ptr(rays), n, spp, seed, C.c_float(radius), flags,
+                                     _ptr(hits), _ptr(rgb)))
+        return hits, rgb
+
     def trace_async(self, rays, out, flags: int = L.RT_TRACE_CLOSEST, stream: int = 0):
         n = _rows(rays, 8)
         L.check(L.lib().trace_rays_async(self._h, _ptr(rays), n, flags, _ptr(out), stream or None))

@@ -576,9 +576,10 @@ struct Pipeline {
   static constexpr uint64_t kChunk = 1ull << 20;  // staging slot capacity in rays (32 MiB in, 16 MiB out)
   int device = -1;
   cudaStream_t s_in = nullptr, s_run = nullptr, s_out = nullptr;
+  cudaStream_t s_run2 = nullptr;  // rt_render_ao: the odd bands' compute stream
   float4* rays[2] = {nullptr, nullptr};
   float4* hits[2] = {nullptr, nullptr};
-  unsigned long long* counters = nullptr;  // 2
+  unsigned long long* counters = nullptr;  // 4: one per trace launch that can be in flight
   cudaEvent_t ev_in[2], ev_run[2], ev_out[2];
   bool ready = false;
   // streamed mode (trace_streamed): one device control block = watermark (u64), error
@@ -618,7 +619,8 @@ struct Pipeline {
     if (s_in) cudaStreamDestroy(s_in);
     if (s_run) cudaStreamDestroy(s_run);
     if (s_out) cudaStreamDestroy(s_out);
-    s_in = s_run = s_out = nullptr;
+    if (s_run2) cudaStreamDestroy(s_run2);
+    s_in = s_run = s_out = s_run2 = nullptr;
     if (prev != device && prev >= 0) cudaSetDevice(prev);
     cudaGetLastError();  // a context torn down at process exit is not an error here
     ready = false;
@@ -632,6 +634,7 @@ struct Pipeline {
     RT_CUDA(cudaStreamCreateWithFlags(&s_in, cudaStreamNonBlocking));
     RT_CUDA(cudaStreamCreateWithFlags(&s_run, cudaStreamNonBlocking));
     RT_CUDA(cudaStreamCreateWithFlags(&s_out, cudaStreamNonBlocking));
+    RT_CUDA(cudaStreamCreateWithFlags(&s_run2, cudaStreamNonBlocking));
     for (int b = 0; b < 2; ++b) {
       RT_CUDA(cudaMalloc((void**)&rays[b], kChunk * 32));
       RT_CUDA(cudaMalloc((void**)&hits[b], kChunk * 16));
@@ -639,7 +642,7 @@ struct Pipeline {
       RT_CUDA(cudaEventCreateWithFlags(&ev_run[b], cudaEventDisableTiming));
       RT_CUDA(cudaEventCreateWithFlags(&ev_out[b], cudaEventDisableTiming));
     }
-    RT_CUDA(cudaMalloc((void**)&counters, 2 * sizeof(unsigned long long)));
+    RT_CUDA(cudaMalloc((void**)&counters, 4 * sizeof(unsigned long long)));
     RT_CUDA(cudaMalloc((void**)&d_ctl, kCtlBytes));
     RT_CUDA(cudaHostAlloc((void**)&h_flags, (size_t)kMaxSegs * 4, cudaHostAllocMapped));
     RT_CUDA(cudaHostAlloc((void**)&h_marks, (size_t)kMaxChunks * 8, cudaHostAllocDefault));
@@ -923,6 +926,146 @@ extern "C" int trace_rays(const rt_bvh* h, const float* rays, uint64_t n_rays, u
   if (hits_k) return trace_staged(h, rays, rays_dev, n_rays, flags, (float*)hits_k, true);
   if (rays_k) return trace_staged(h, (const float*)rays_k, true, n_rays, flags, hits, hits_dev);
   return trace_staged(h, rays, rays_dev, n_rays, flags, hits, hits_dev);
+}
+
+// One frame of the config-3 pipeline in one call: closest-hit trace of the primary rays, spp
+// occlusion rays per pixel from the hit points (rt_gen_ao_rays), their any-hit trace, and the
+// shaded frame (rt_shade) — the bytes the four separate calls give.  The frame is cut into bands
+// of 1M rays that flow through three streams: band k+1 is uploaded while band k is traced, and
+// band k's hits and pixels go down while band k+1 is traced; the occlusion rays and their hits
+// never leave the device.  Host buffers should be page-locked for the copies to overlap.
+extern "C" int rt_render_ao(const rt_bvh* h, const float* tris, const float* rays, uint64_t n_rays,
+                            uint32_t spp, uint64_t seed, float radius, uint32_t flags, float* hits,
+                            float* rgb) {
+  if (!h) return fail(RT_ERR_INVALID, "rt_render_ao: handle is NULL");
+  if (n_rays == 0) return RT_OK;
+  if (!tris || !rays || !rgb) return fail(RT_ERR_INVALID, "rt_render_ao: tris, rays or rgb is NULL");
+  if (flags & ~(uint32_t)RT_TRACE_WATERTIGHT) return fail(RT_ERR_INVALID, "rt_render_ao: flags may only hold RT_TRACE_WATERTIGHT");
+  if (spp > 64) return fail(RT_ERR_LIMIT, "rt_render_ao: at most 64 occlusion rays per pixel");
+  DeviceScope scope;
+  RT_TRY(scope.enter(h->device));
+  int dt = -1, dr = -1, dh = -1, dg = -1;
+  if (!classify(tris, &dt) || dt != h->device)
+    return fail(RT_ERR_INVALID, "rt_render_ao: tris (original order) must be device memory of the handle's device");
+  const bool rays_dev = classify(rays, &dr) != 0, hits_dev = hits && classify(hits, &dh) != 0,
+             rgb_dev = classify(rgb, &dg) != 0;
+  if ((rays_dev && dr != h->device) || (hits_dev && dh != h->device) || (rgb_dev && dg != h->device))
+    return fail(RT_ERR_INVALID, "rt_render_ao: device buffers are not on the handle's device %d", h->device);
+  Pipeline& p = t_pipe;
+  RT_TRY(p.init(h->device));
+  RT_CUDA(cudaStreamSynchronize(0));  // the legacy default stream may still be producing the inputs
+  // bands: 1M rays (render.band), halved until a band's occlusion rays fit 8M; four buffer slots so that
+  // neither the uploads nor the launches wait for a slot to drain in the steady state
+  constexpr int kSlots = 4;
+  const int band_log2 = params().render_band;
+  uint64_t band_max = band_log2 >= 16 && band_log2 <= 20 ? 1ull << band_log2 : Pipeline::kChunk;
+  while (spp && band_max * spp > (8ull << 20) && band_max > (1ull << 16)) band_max >>= 1;
+  const uint64_t band = n_rays < band_max ? n_rays : band_max;
+  // the first bands are a quarter and a half of a band: the first launch waits for less
+  const bool taper = !rays_dev && n_rays >= 4 * band && params().render_taper != 0;
+  const uint64_t head = taper ? band / 4 + band / 2 : 0;
+  const uint64_t bands = (n_rays - head + band - 1) / band + (taper ? 2 : 0);
+  const int slots = bands < (uint64_t)kSlots ? (int)bands : kSlots;
+  TempPool tmp(p.s_run);
+  float4 *d_rays[kSlots] = {}, *d_hits[kSlots] = {}, *d_ao[kSlots] = {}, *d_aoh[kSlots] = {};
+  float* d_rgb[kSlots] = {};
+  for (int b = 0; b < slots; ++b) {
+    if (!rays_dev) RT_TRY(tmp.alloc((void**)&d_rays[b], band * 32));
+    if (!hits_dev) RT_TRY(tmp.alloc((void**)&d_hits[b], band * 16));
+    if (spp) {
+      RT_TRY(tmp.alloc((void**)&d_ao[b], band * spp * 32));
+      RT_TRY(tmp.alloc((void**)&d_aoh[b], band * spp * 16));
+    }
+    if (!rgb_dev) RT_TRY(tmp.alloc((void**)&d_rgb[b], band * 12));
+  }
+  RT_CUDA(cudaStreamSynchronize(p.s_run));  // the allocations are now usable from the other streams
+  struct Drain {  // no stream may still touch the band buffers when they are freed
+    Pipeline& p;
+    ~Drain() {
+      cudaStreamSynchronize(p.s_in);
+      cudaStreamSynchronize(p.s_run);
+      cudaStreamSynchronize(p.s_run2);
+      cudaStreamSynchronize(p.s_out);
+    }
+  } drain{p};
+  // per slot: rays uploaded, primary hits final (their download may start before the AO pass
+  // ends), band computed, band downloaded
+  struct BandEvents {
+    cudaEvent_t in[kSlots], hit[kSlots], run[kSlots], out[kSlots];
+    int made = 0;
+    int create(int n) {
+      for (; made < n; ++made) {
+        RT_CUDA(cudaEventCreateWithFlags(&in[made], cudaEventDisableTiming));
+        RT_CUDA(cudaEventCreateWithFlags(&hit[made], cudaEventDisableTiming));
+        RT_CUDA(cudaEventCreateWithFlags(&run[made], cudaEventDisableTiming));
+        RT_CUDA(cudaEventCreateWithFlags(&out[made], cudaEventDisableTiming));
+      }
+      return 0;
+    }
+    ~BandEvents() {
+      for (int i = 0; i < made; ++i) {
+        cudaEventDestroy(in[i]);
+        cudaEventDestroy(hit[i]);
+        cudaEventDestroy(run[i]);
+        cudaEventDestroy(out[i]);
+      }
+    }
+  } ev;
+  RT_TRY(ev.create(slots));
+  const float4* tris4 = reinterpret_cast<const float4*>(tris);
+  // Even and odd bands compute on their own streams: every trace launch is a persistent grid
+  // that fills the GPU, so the next band's blocks start as the blocks of this band's launch
+  // retire — the drain of one launch (the last, longest rays) is covered by the other band.
+  cudaStream_t s_cmp[2] = {p.s_run, p.s_run2};
+  for (uint64_t k = 0; k < bands; ++k) {
+    const int b = (int)(k % (uint64_t)slots), c = (int)(k & 1);
+    cudaStream_t sc = s_cmp[c];
+    const bool reused = k >= (uint64_t)slots;
+    uint64_t first = k * band, cnt = band;
+    if (taper) {
+      first = k == 0 ? 0 : k == 1 ? band / 4 : head + (k - 2) * band;
+      cnt = k == 0 ? band / 4 : k == 1 ? band / 2 : band;
+    }
+    if (n_rays - first < cnt) cnt = n_rays - first;
+    const float4* r4;
+    if (rays_dev) {
+      r4 = reinterpret_cast<const float4*>(rays) + 2 * first;
+    } else {
+      if (reused) RT_CUDA(cudaStreamWaitEvent(p.s_in, ev.run[b], 0));  // the slot's last reader (shade)
+      RT_CUDA(cudaMemcpyAsync(d_rays[b], rays + 8 * first, cnt * 32, cudaMemcpyHostToDevice, p.s_in));
+      RT_CUDA(cudaEventRecord(ev.in[b], p.s_in));
+      RT_CUDA(cudaStreamWaitEvent(sc, ev.in[b], 0));
+      r4 = d_rays[b];
+    }
+    if (reused) {
+      // the slot's buffers: its previous band ran on either compute stream and was then downloaded
+      RT_CUDA(cudaStreamWaitEvent(sc, ev.run[b], 0));
+      RT_CUDA(cudaStreamWaitEvent(sc, ev.out[b], 0));
+    }
+    float4* h4 = hits_dev ? reinterpret_cast<float4*>(hits) + first : d_hits[b];
+    float* g3 = rgb_dev ? rgb + 3 * first : d_rgb[b];
+    RT_TRY(launch_trace_h(h, r4, cnt, flags, h4, p.counters + 2 * c, sc));
+    RT_CUDA(cudaEventRecord(ev.hit[b], sc));
+    if (spp) {
+      RT_TRY(launch_gen_ao(tris4, r4, h4, cnt, spp, seed, radius, d_ao[b], sc, first));
+      RT_TRY(launch_trace_h(h, d_ao[b], cnt * spp, flags | RT_TRACE_ANY, d_aoh[b], p.counters + 2 * c + 1, sc));
+    }
+    RT_TRY(launch_shade(tris4, r4, h4, spp ? d_aoh[b] : nullptr, cnt, spp, g3, sc));
+    RT_CUDA(cudaEventRecord(ev.run[b], sc));
+    if (hits && !hits_dev) {
+      RT_CUDA(cudaStreamWaitEvent(p.s_out, ev.hit[b], 0));
+      RT_CUDA(cudaMemcpyAsync(hits + 4 * first, h4, cnt * 16, cudaMemcpyDeviceToHost, p.s_out));
+    }
+    if (!rgb_dev) {
+      RT_CUDA(cudaStreamWaitEvent(p.s_out, ev.run[b], 0));
+      RT_CUDA(cudaMemcpyAsync(rgb + 3 * first, g3, cnt * 12, cudaMemcpyDeviceToHost, p.s_out));
+    }
+    RT_CUDA(cudaEventRecord(ev.out[b], p.s_out));
+  }
+  RT_CUDA(cudaStreamSynchronize(p.s_run2));
+  RT_CUDA(cudaStreamSynchronize(p.s_run));
+  RT_CUDA(cudaStreamSynchronize(p.s_out));
+  return RT_OK;
 }
 
 // Primary rays never cross PCIe: the 12-float camera goes in, the rays are generated on the
@@ -1408,6 +1551,8 @@ extern "C" int rt_set_param(const char* name, int64_t value) {
   else if (!strcmp(name, "trace.sh_stack")) p.trace_sh_stack = (int)value;
   else if (!strcmp(name, "build.pdl")) g_pdl = value != 0;
   else if (!strcmp(name, "build.walk")) g_build_walk_shape = (int)value;
+  else if (!strcmp(name, "render.band")) p.render_band = (int)value;
+  else if (!strcmp(name, "render.taper")) p.render_taper = (int)value;
   else if (!strcmp(name, "pool.keep_mb")) {
     p.pool_keep_mb = (int)value;
     std::lock_guard<std::mutex> lock(g_pool_mu);

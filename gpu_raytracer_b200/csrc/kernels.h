@@ -58,8 +58,10 @@ int launch_gen_primary(const float* cam12, uint32_t width, uint32_t height, uint
                        uint64_t count, float4* out, cudaStream_t s);
 int launch_gen_random(const float* box6, uint64_t seed, uint64_t first, uint64_t count,
                       float4* out, cudaStream_t s);
+// first: global index of rays[0] (the samples of ray i are drawn for index first + i)
 int launch_gen_ao(const float4* tris, const float4* rays, const float4* hits, uint64_t n,
-                  uint32_t spp, uint64_t seed, float radius, float4* out, cudaStream_t s);
+                  uint32_t spp, uint64_t seed, float radius, float4* out, cudaStream_t s,
+                  uint64_t first = 0);
 int launch_shade(const float4* tris, const float4* rays, const float4* hits,
                  const float4* ao_hits, uint64_t n, uint32_t spp, float* rgb, cudaStream_t s);
 // *out += number of hit records with prim >= 0 (closest hits, or occluded any-hit rays)
@@ -267,6 +269,8 @@ struct Params {
   Knob zero_copy{0};
   Knob stage_chunk{0};          // rays per staged chunk (0 = 1M)
   Knob streamed{1};             // 1 = pinned host batches go through the single-launch streamed mode
+  Knob render_band{0};          // rt_render_ao: log2 of the rays per band (16..20); 0 = 20
+  Knob render_taper{1};         // rt_render_ao with host rays: 1 = the first two bands are 1/4 and 1/2 of a band
   Knob pool_keep_mb{0};         // build/trace temporaries kept cached per device after a call; 0 = all
 };
 Params& params();

@@ -71,7 +71,7 @@ __device__ __forceinline__ void facing_normal(const float4* __restrict__ tris, i
 __global__ void __launch_bounds__(256)
 ao_kernel(const float4* __restrict__ tris, const float4* __restrict__ rays,
           const float4* __restrict__ hits, uint64_t n, uint32_t spp, uint64_t key, float radius,
-          float4* __restrict__ out) {
+          float4* __restrict__ out, uint64_t first) {
   const float eps = radius * 1e-3f;
   for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
        i += (uint64_t)gridDim.x * blockDim.x) {
@@ -92,7 +92,7 @@ ao_kernel(const float4* __restrict__ tris, const float4* __restrict__ rays,
     float oz = fmaf(h.x, rd.z, ro.z) + nz * eps;
     for (uint32_t s = 0; s < spp; ++s) {
       float sx, sy, sz;
-      sphere_sample(key, i * spp + s, 0, sx, sy, sz);
+      sphere_sample(key, (first + i) * spp + s, 0, sx, sy, sz);  // the sample of GLOBAL ray first + i
       float dx = nx + sx, dy = ny + sy, dz = nz + sz;
       float l2 = dx * dx + dy * dy + dz * dz;
       if (l2 < 1e-12f) {
@@ -178,10 +178,10 @@ int launch_gen_random(const float* box6, uint64_t seed, uint64_t first, uint64_t
 }
 
 int launch_gen_ao(const float4* tris, const float4* rays, const float4* hits, uint64_t n,
-                  uint32_t spp, uint64_t seed, float radius, float4* out, cudaStream_t s) {
+                  uint32_t spp, uint64_t seed, float radius, float4* out, cudaStream_t s, uint64_t first) {
   if (n == 0 || spp == 0) return 0;
   ao_kernel<<<grid_for(n), 256, 0, s>>>(tris, rays, hits, n, spp, stream_key(seed, kStreamAO),
-                                        radius, out);
+                                        radius, out, first);
   RT_LAUNCHED();
   return 0;
 }

@@ -314,6 +314,17 @@ RT_API int rt_gen_ao_rays(const float* tris, const float* rays, const float* hit
 RT_API int rt_shade(const float* tris, const float* rays, const float* hits, const float* ao_hits,
              uint64_t n, uint32_t spp, float* rgb);
 
+/* One frame in one call (BASELINE.json config 3: primary + spp occlusion rays per pixel): the
+ * closest-hit trace of n_rays primary rays, rt_gen_ao_rays from their hit points, the any-hit
+ * trace of those, and rt_shade: hits (may be NULL) and rgb (n_rays x 3) hold the bytes the four
+ * separate calls give.  tris: DEVICE memory, original order (what build_bvh was given);
+ * rays / hits / rgb: [host|device]; flags: 0 or RT_TRACE_WATERTIGHT.  The frame flows through
+ * three streams in bands of 1M rays, so with page-locked host buffers the upload of band k+1
+ * and the download of band k-1 overlap the tracing of band k; the occlusion rays never leave
+ * the device.  Synchronous on return. */
+RT_API int rt_render_ao(const rt_bvh* h, const float* tris, const float* rays, uint64_t n_rays, uint32_t spp,
+                        uint64_t seed, float radius, uint32_t flags, float* hits, float* rgb);
+
 /* ---- runtime --------------------------------------------------------------*/
 
 RT_API int rt_device_count(void);
@@ -329,7 +340,8 @@ RT_API int rt_trim(int device);
  * keeps everything, which makes repeated builds allocation-free), "sort.variant", "sort.bits",
  * "trace.variant", "trace.blocks_per_sm", "trace.chunk", "trace.refill_min", "trace.leaf_min",
  * "trace.wide", "wide.leaf_max", "trace.streamed" (0 = always stage host batches),
- * "trace.stage_chunk", "trace.zero_copy", "trace.sh_stack" (0 | 8 | 16 | 24 stack levels in
+ * "trace.stage_chunk", "trace.zero_copy", "render.band" (rt_render_ao: log2 of the rays per band,
+ * 16..20; 0, the default, = 20), "trace.sh_stack" (0 | 8 | 16 | 24 stack levels in
  * shared memory; -1, the default: 8 for RT_TRACE_REORDER launches, else 0), "build.pdl" (1 = build kernels launched as programmatic dependents, the
  * default), "sort.hybrid" (63-bit builds: 1 = packed passes on the top 30 bits, then ranks inside
  * runs of equal top bits, the default; 0 = seven passes over all 63 bits; same order either way).  Returns RT_ERR_INVALID for an unknown name. */

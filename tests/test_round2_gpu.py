@@ -220,6 +220,47 @@ def test_trace_camera_equals_generated_rays(rt, oracle):
     ob.close()
 
 
+def test_render_ao_equals_the_separate_calls(rt):
+    """rt_render_ao (banded, three streams) gives the bytes of trace_rays -> rt_gen_ao_rays ->
+    trace_rays(any) -> rt_shade, for device, pageable and pinned buffers, over several bands
+    (1.44M rays > 1M per band) and with a ragged last band."""
+    w, h, spp, seed = 1600, 901, 3, 77
+    cam = rt.camera.cornell_camera(w, h)
+    d_tris = rt.gen_scene(rt.RT_SCENE_CORNELL)
+    for flags in (0, rt.RT_TRACE_WATERTIGHT):
+        with rt.Bvh.build(d_tris) as gb:
+            rays = rt.gen_primary_rays(cam, w, h)
+            radius = float(np.float32(0.05) * np.float32(np.linalg.norm(gb.bounds[3:] - gb.bounds[:3])))
+            hits = gb.trace(rays, flags)
+            ao = rt.gen_ao_rays(d_tris, rays, hits, spp, seed, radius)
+            occ = gb.trace(ao, flags | rt.RT_TRACE_ANY)
+            rgb = rt.shade(d_tris, rays, hits, occ, spp)
+            want_h, want_g = bits(hits.cpu().numpy()), bits(rgb.cpu().numpy())
+            got_h, got_g = gb.render_ao(d_tris, rays, spp, seed, radius, flags)                 # device
+            assert got_h.is_cuda and np.array_equal(bits(got_h.cpu().numpy()), want_h)
+            assert np.array_equal(bits(got_g.cpu().numpy()), want_g)
+            got_h, got_g = gb.render_ao(d_tris, rays.cpu().numpy(), spp, seed, radius, flags)   # pageable
+            assert isinstance(got_g, np.ndarray)
+            assert np.array_equal(bits(got_h), want_h) and np.array_equal(bits(got_g), want_g)
+            pinned = rays.cpu().pin_memory()
+            for _ in range(2):                                                                  # slots are reused
+                got_h, got_g = gb.render_ao(d_tris, pinned, spp, seed, radius, flags)
+                assert got_g.is_pinned()
+                assert np.array_equal(bits(got_h.numpy()), want_h) and np.array_equal(bits(got_g.numpy()), want_g)
+            # mixed: host rays, device frame; and no occlusion pass at all
+            d_rgb = torch.empty((w * h, 3), dtype=torch.float32, device="cuda")
+            gb.render_ao(d_tris, pinned, spp, seed, radius, flags, rgb=d_rgb)
+            assert np.array_equal(bits(d_rgb.cpu().numpy()), want_g)
+            _, plain = gb.render_ao(d_tris, pinned, 0, seed, radius, flags)
+            assert np.array_equal(bits(plain.numpy()), bits(rt.shade(d_tris, rays, hits).cpu().numpy()))
+            with pytest.raises(rt.RtError):
+                gb.render_ao(d_tris.cpu().numpy(), pinned, spp, seed, radius)                   # tris must be on the device
+            with pytest.raises(rt.RtError):
+                gb.render_ao(d_tris, pinned, 65, seed, radius)
+            with pytest.raises(rt.RtError):
+                gb.render_ao(d_tris, pinned, spp, seed, radius, rt.RT_TRACE_ANY)
+
+
 # ---- shading and the image ------------------------------------------------------------------------------
 def test_shade_and_frame_match_the_oracle(rt, oracle, tmp_path):
     """§8(f).1: rt_shade bit-equal to the oracle's shade on the Cornell frame of the golden
