@@ -15,7 +15,7 @@ SO_PATH = os.environ.get("RT_LIB") or os.path.join(_HERE, "libgpu_raytracer_b200
 RT_OK, RT_ERR_INVALID, RT_ERR_CUDA, RT_ERR_OOM, RT_ERR_NO_DEVICE, RT_ERR_LIMIT = 0, -1, -2, -3, -4, -5
 RT_TRACE_CLOSEST, RT_TRACE_ANY, RT_TRACE_WATERTIGHT, RT_TRACE_REORDER = 0, 1, 2, 4
 RT_ANY_HIT_PRIM = 0x7FFFFFFF
-RT_BUILD_KEEP_KEYS, RT_BUILD_TIMINGS, RT_BUILD_WIDE4, RT_BUILD_WIDE8 = 1, 2, 4, 8
+RT_BUILD_KEEP_KEYS, RT_BUILD_TIMINGS, RT_BUILD_WIDE4, RT_BUILD_WIDE8, RT_BUILD_COMPACT = 1, 2, 4, 8, 16
 RT_SCENE_CORNELL, RT_SCENE_SOUP, RT_SCENE_SPHEREFLAKE, RT_SCENE_TERRAIN = 0, 1, 2, 3
 RT_MULTI_REDUNDANT, RT_MULTI_BROADCAST = 0, 1
 RT_STAGE_NAMES = ("bounds", "morton", "sort", "topology", "refit", "total", "wide")
@@ -51,6 +51,8 @@ SIGNATURES = {
     "bvh_widen": (_i32, [_vp]),
     "bvh_read_wide": (_i32, [_vp, _vp, C.POINTER(_u32)]),
     "bvh_widen8": (_i32, [_vp]),
+    "bvh_compact": (_i32, [_vp]),
+    "bvh_read_compact": (_i32, [_vp, _vp, _vp]),
     "bvh_read_wide8": (_i32, [_vp, _vp, _vp, C.POINTER(_u32)]),
     "bvh_device_buffers": (_i32, [_vp, C.POINTER(_vp), C.POINTER(_u64)]),
     "bvh_alloc_empty": (_i32, [_u64, _u32, C.POINTER(_vp)]),

@@ -123,6 +123,8 @@ WIDE_LEAF_BIT, WIDE_EMPTY, WIDE_FIRST_MASK = 0x80000000, 0x7FFFFFFF, (1 << 29) -
 WIDE8_NODE_DTYPE = np.dtype([("p", np.float32, 3), ("e", np.uint8, 3), ("imask", np.uint8),
                              ("child_base", np.uint32), ("tri_base", np.uint32), ("meta", np.uint8, 8),
                              ("qlo", np.uint8, (3, 8)), ("qhi", np.uint8, (3, 8))])
+# one node of bvh_read_compact (32 bytes): box[c, a] = lo | hi << 16 of child c on axis a
+COMPACT_NODE_DTYPE = np.dtype([("box", np.uint32, (2, 3)), ("child", np.int32, 2)])
 
 
 # ---------------------------------------------------------------------------
@@ -168,12 +170,14 @@ class Bvh:
     # -- build_bvh -----------------------------------------------------------
     @classmethod
     def build(cls, tris, key_bits: int = 30, keep_keys: bool = False, timings: bool = False,
-              device: int = -1, stream: int = 0, wide: bool = False, wide8: bool = False) -> "Bvh":
+              device: int = -1, stream: int = 0, wide: bool = False, wide8: bool = False,
+              compact: bool = False) -> "Bvh":
         n = _rows(tris, 12)
         opts = L.BuildOpts(key_bits=key_bits,
                            flags=(L.RT_BUILD_KEEP_KEYS if keep_keys else 0) |
                                  (L.RT_BUILD_TIMINGS if timings else 0) |
-                                 (L.RT_BUILD_WIDE4 if wide else 0) | (L.RT_BUILD_WIDE8 if wide8 else 0),
+                                 (L.RT_BUILD_WIDE4 if wide else 0) | (L.RT_BUILD_WIDE8 if wide8 else 0) |
+                                 (L.RT_BUILD_COMPACT if compact else 0),
                            device=device, reserved=0, stream=stream or None)
         h = C.c_void_p()
         L.check(L.lib().build_bvh(_ptr(tris) if n else None, n, C.byref(opts), C.byref(h)))
@@ -257,6 +261,17 @@ class Bvh:
     def widen8(self) -> None:
         """Collapse to the compressed 8-wide layout (needs keep_keys=True); ``trace`` then walks it."""
         L.check(L.lib().bvh_widen8(self._h))
+
+    def compact(self) -> None:
+        """Pack the binary tree into 32-byte nodes (bvh_compact); ``trace`` then walks those."""
+        L.check(L.lib().bvh_compact(self._h))
+
+    def read_compact(self):
+        """(nodes, grid6): the 32-byte nodes as a structured array and the grid (origin xyz, step xyz)."""
+        nodes = np.zeros(max(self.n_tris - 1, 0), dtype=COMPACT_NODE_DTYPE)
+        grid = np.zeros(6, dtype=np.float32)
+        L.check(L.lib().bvh_read_compact(self._h, nodes.ctypes.data if len(nodes) else None, grid.ctypes.data))
+        return nodes, grid
 
     def read_wide8(self):
         """(nodes, tris): the 8-wide layout as a structured array and the triangles in its order."""

@@ -20,7 +20,7 @@ CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "build")
 SO = os.path.join(HERE, "libgpu_raytracer_b200.so")
 SOURCES = ["api.cu", "scene_gen.cu", "ray_gen.cu", "morton.cu", "radix_sort.cu",
-           "refit.cu", "traverse.cu", "wide.cu", "wide8.cu", "scene_io.cu", "multi.cu", "noalloc.cu"]
+           "refit.cu", "traverse.cu", "wide.cu", "wide8.cu", "compact.cu", "scene_io.cu", "multi.cu", "noalloc.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-fmad=false",
               "-std=c++17", "-Xcompiler", "-fPIC,-fvisibility=hidden",
               "-diag-suppress", "177"]

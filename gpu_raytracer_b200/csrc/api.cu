@@ -186,6 +186,7 @@ void release(rt_bvh* h) {
   if (h->wide) cudaFreeAsync(h->wide, 0);
   if (h->wide8.nodes) cudaFreeAsync(h->wide8.nodes, 0);
   if (h->wide8.tris) cudaFreeAsync(h->wide8.tris, 0);
+  if (h->compact.nodes) cudaFreeAsync(h->compact.nodes, 0);
   if (prev != h->device && prev >= 0) cudaSetDevice(prev);
   delete h;
 }
@@ -254,6 +255,20 @@ int widen8(rt_bvh* h, cudaStream_t s) {
   return 0;
 }
 
+// (re)packs the 32-byte binary layout of a finished BVH2 (compact.cu); needs h->bounds
+int compact(rt_bvh* h, cudaStream_t s) {
+  if (h->n < 2) return fail(RT_ERR_INVALID, "compact: the layout needs at least 2 triangles");
+  h->compact.valid = false;
+  if (!h->compact.nodes) {
+    RT_TRY(pool_alloc((void**)&h->compact.nodes, (h->n - 1) * sizeof(NodeQ), s));
+    h->bytes += (h->n - 1) * sizeof(NodeQ);
+  }
+  h->compact.grid = make_qgrid(h->bounds);
+  RT_TRY(launch_pack_nodes(h->nodes, h->n - 1, h->compact.grid, h->compact.nodes, s));
+  h->compact.valid = true;
+  return 0;
+}
+
 }  // namespace
 // traversal of whichever layout the handle holds
 int rt::launch_trace_h(const rt_bvh* h, const float4* rays, uint64_t n_rays, uint32_t flags,
@@ -265,7 +280,7 @@ int rt::launch_trace_h(const rt_bvh* h, const float4* rays, uint64_t n_rays, uin
     return launch_trace_wide(h->wide, h->stris, h->n, h->wide_root, rays, n_rays, flags, hits,
                              counter, s, stats);
   return launch_trace(h->nodes, h->stris, h->n, h->root, rays, n_rays, flags, hits, counter, s,
-                      stats);
+                      stats, nullptr, nullptr, &h->compact);
 }
 
 namespace {
@@ -393,7 +408,7 @@ int build_impl(rt_bvh* h, const float* tris_in, uint32_t flags, cudaStream_t s) 
   RT_TRY(launch_build_tree(tris, svals, skeys, h->key_bits, n, (uint32_t*)flags_buf, h->nodes,
                            h->stris, h->header, queue_buf, s, hybrid ? long_run : nullptr));
   RT_TRY(mark(5));
-  const bool want_wide = (flags & (RT_BUILD_WIDE4 | RT_BUILD_WIDE8)) != 0;
+  const bool want_wide = (flags & (RT_BUILD_WIDE4 | RT_BUILD_WIDE8 | RT_BUILD_COMPACT)) != 0;
   if (!want_wide) RT_TRY(mark(6));
   uint32_t long_flag = 0;
   if (hybrid) RT_CUDA(cudaMemcpyAsync(&long_flag, long_run, 4, cudaMemcpyDeviceToHost, s));
@@ -428,6 +443,7 @@ int build_impl(rt_bvh* h, const float* tris_in, uint32_t flags, cudaStream_t s) 
   if (want_wide) {  // A5w, optional: needs the root
     if (flags & RT_BUILD_WIDE4) RT_TRY(widen(h, s));
     if ((flags & RT_BUILD_WIDE8) && n > wide8_leaf_max()) RT_TRY(widen8(h, s));
+    if ((flags & RT_BUILD_COMPACT) && n >= 2) RT_TRY(compact(h, s));
     RT_TRY(mark(6));
     RT_CUDA(cudaStreamSynchronize(s));
   }
@@ -519,6 +535,10 @@ extern "C" int refit_bvh(rt_bvh* h, const float* tris_in) {
     RT_TRY(widen8(h, s));
     RT_CUDA(cudaStreamSynchronize(s));
   }
+  if (h->compact.valid) {  // and the 32-byte nodes, on the grid of the new scene box
+    RT_TRY(compact(h, s));
+    RT_CUDA(cudaStreamSynchronize(s));
+  }
   return RT_OK;
 }
 
@@ -551,6 +571,26 @@ extern "C" int bvh_widen8(rt_bvh* h) {
   cudaStream_t s = 0;
   RT_TRY(widen8(h, s));
   RT_CUDA(cudaStreamSynchronize(s));
+  return RT_OK;
+}
+
+extern "C" int bvh_compact(rt_bvh* h) {
+  if (!h) return fail(RT_ERR_INVALID, "bvh_compact: handle is NULL");
+  DeviceScope scope;
+  RT_TRY(scope.enter(h->device));
+  cudaStream_t s = 0;
+  RT_TRY(compact(h, s));
+  RT_CUDA(cudaStreamSynchronize(s));
+  return RT_OK;
+}
+
+extern "C" int bvh_read_compact(const rt_bvh* h, void* nodes, float* grid6) {
+  if (!h) return fail(RT_ERR_INVALID, "bvh_read_compact: handle is NULL");
+  if (!h->compact.valid) return fail(RT_ERR_INVALID, "bvh_read_compact: the handle holds no compact layout");
+  if (grid6) memcpy(grid6, &h->compact.grid, 6 * sizeof(float));
+  DeviceScope scope;
+  RT_TRY(scope.enter(h->device));
+  if (nodes) RT_CUDA(cudaMemcpy(nodes, h->compact.nodes, (h->n - 1) * sizeof(NodeQ), cudaMemcpyDeviceToHost));
   return RT_OK;
 }
 
@@ -682,7 +722,7 @@ int trace_reordered(const rt_bvh* h, const float4* rays, uint64_t n_rays, uint32
                                 counter, s, nullptr, perm));
     else
       RT_TRY(launch_trace(h->nodes, h->stris, h->n, h->root, rays + 2 * first, n, flags & 3u,
-                          hits + first, counter, s, nullptr, nullptr, perm));
+                          hits + first, counter, s, nullptr, nullptr, perm, &h->compact));
   }
   return 0;
 }
@@ -1541,6 +1581,7 @@ extern "C" int rt_set_param(const char* name, int64_t value) {
   else if (!strcmp(name, "trace.blocks_per_sm")) p.trace_blocks_per_sm = (int)value;
   else if (!strcmp(name, "trace.variant")) p.trace_variant = (int)value;
   else if (!strcmp(name, "trace.wide")) p.trace_wide = (int)value;
+  else if (!strcmp(name, "trace.compact")) p.trace_compact = (int)value;
   else if (!strcmp(name, "trace.streamed")) p.streamed = (int)value;
   else if (!strcmp(name, "wide.leaf_max")) p.wide_leaf_max = (int)value;
   else if (!strcmp(name, "trace.zero_copy")) p.zero_copy = (int)value;

@@ -80,6 +80,7 @@ struct rt_bvh {
   bool is_wide = false;
   uint32_t wide_leaf_max = rt::kWideLeafDefault;
   rt::Wide8 wide8;            // only with RT_BUILD_WIDE8 / bvh_widen8: compressed 8-wide layout
+  rt::Compact compact;        // only with RT_BUILD_COMPACT / bvh_compact: 32-byte binary nodes
   float bounds[6] = {0, 0, 0, 0, 0, 0};
   int root = 0;  // node id where traversal starts (header.root_node)
   float times[RT_STAGE_COUNT] = {0, 0, 0, 0, 0, 0, 0};

@@ -223,6 +223,27 @@ int launch_trace_wide8(const Node8* nodes8, const SortedTri* tris8, const float4
                        uint32_t flags, float4* hits, unsigned long long* ray_counter, cudaStream_t s,
                        unsigned long long* stats = nullptr, const uint32_t* perm = nullptr);
 
+// ---- compact binary layout (compact.cu; traversal in traverse.cu) ----------------
+// The BVH2 node in 32 bytes, i.e. ONE 32-byte request per node step instead of two: the six
+// planes of each child box as 16-bit coordinates on a grid that spans the scene box
+// (plane = origin + q * step per axis), rounded outwards by at least one step, plus the two
+// child ids of Node.  word 3c + a = lo | hi << 16 of child c on axis a.
+struct __align__(32) NodeQ {
+  uint32_t box[6];
+  int32_t c0, c1;
+};
+struct QGrid {
+  float ox, oy, oz;  // plane 0 of each axis (below the scene box by three steps)
+  float sx, sy, sz;  // step, > 0
+};
+struct Compact {
+  NodeQ* nodes = nullptr;  // n - 1 nodes, same ids as Node
+  QGrid grid = {0, 0, 0, 1, 1, 1};
+  bool valid = false;
+};
+QGrid make_qgrid(const float bounds[6]);
+int launch_pack_nodes(const Node* nodes, uint64_t n_nodes, QGrid grid, NodeQ* out, cudaStream_t s);
+
 // ---- traversal (traverse.cu) -------------------------------------------------
 // Hand-shake of the streamed mode (host-resident batches): rays arrive while the kernel runs.
 struct TracePipe {
@@ -236,7 +257,8 @@ int launch_trace(const Node* nodes, const SortedTri* stris, uint64_t n_tris, int
                  const float4* rays,
                  uint64_t n_rays, uint32_t flags, float4* hits, unsigned long long* ray_counter,
                  cudaStream_t s, unsigned long long* stats = nullptr,
-                 const TracePipe* pipe = nullptr, const uint32_t* perm = nullptr);
+                 const TracePipe* pipe = nullptr, const uint32_t* perm = nullptr,
+                 const Compact* compact = nullptr);
 // RT_TRACE_REORDER: 20-bit coherence keys (origin cell, direction bin) of n device rays;
 // box = the scene bounds {min.xyz, max.xyz} (host values)
 int launch_ray_keys(const float4* rays, uint64_t n, const float* box, uint32_t* keys, cudaStream_t s);
@@ -261,6 +283,7 @@ struct Params {
   Knob trace_variant{1};        // 0 = plain while-while, 1 = dynamic fetch + voted leaf loop
   Knob trace_chunk{0}, trace_refill_min{0}, trace_leaf_min{0};  // 0 = defaults
   Knob trace_sh_stack{-1};      // stack levels kept in shared memory (0, 8, 16, 24); -1 = 8 with RT_TRACE_REORDER, else 0
+  Knob trace_compact{1};        // 1 = use the 32-byte binary layout of handles that hold one (RT_BUILD_COMPACT)
   Knob trace_wide{1};           // 1 = use the wide layout of handles that hold one (RT_BUILD_WIDE4 / RT_BUILD_WIDE8)
   Knob wide_leaf_max{kWideLeafDefault};  // triangles per BVH4 leaf (1..4), read when collapsing
   // bit 0: kernels read pinned host rays in place, bit 1: store hits to pinned host in

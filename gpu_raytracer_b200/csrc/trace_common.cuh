@@ -100,11 +100,18 @@ static __device__ __noinline__ bool own_box_admits(const float4* __restrict__ tp
               omax(omax(v0.x, v1.x), v2.x), omax(omax(v0.y, v1.y), v2.y), omax(omax(v0.z, v1.z), v2.z), r, tn) &&
          tn <= t * kSlabPad;
 }
+// RECIP: the caller does not keep r.ix / iy / iz alive (compact layout); they are computed again
+// from the direction, by the same inv_dir(), for the few candidates that get this far.
+__device__ __forceinline__ float inv_dir(float d);
+template <bool RECIP = false>
 __device__ __forceinline__ bool accept_hit(float t, float u, float v, int prim, const float4* __restrict__ tp,
                                            RayState& r) {
   bool ok = (t > r.tmin) &&
             ((t < r.best_t) || (t == r.best_t && r.best_prim >= 0 && prim < r.best_prim));
-  if (ok) ok = own_box_admits(tp, r.ox, r.oy, r.oz, r.ix, r.iy, r.iz, r.tmin, r.best_t, t);
+  if (ok) {
+    if (RECIP) ok = own_box_admits(tp, r.ox, r.oy, r.oz, inv_dir(r.dx), inv_dir(r.dy), inv_dir(r.dz), r.tmin, r.best_t, t);
+    else ok = own_box_admits(tp, r.ox, r.oy, r.oz, r.ix, r.iy, r.iz, r.tmin, r.best_t, t);
+  }
   if (ok) {
     r.best_t = t;
     r.bu = u;
@@ -117,6 +124,7 @@ __device__ __forceinline__ bool accept_hit(float t, float u, float v, int prim, 
 // Moeller-Trumbore, two-sided.  The triangle record holds the raw vertices
 // {v0 | prim, v1, v2}; the edges are one subtraction each, as in the oracle.
 // Returns true when the hit was accepted.
+template <bool RECIP = false>
 __device__ __forceinline__ bool intersect(const SortedTri* __restrict__ stris, uint32_t j,
                                           RayState& r) {
   const float4* tp = reinterpret_cast<const float4*>(stris + j);
@@ -137,7 +145,7 @@ __device__ __forceinline__ bool intersect(const SortedTri* __restrict__ stris, u
   const float v = fmaf(r.dx, qx, fmaf(r.dy, qy, r.dz * qz)) * inv;
   const float t = fmaf(e2x, qx, fmaf(e2y, qy, e2z * qz)) * inv;
   if (!((u >= 0.0f) && (v >= 0.0f) && ((u + v) <= 1.0f))) return false;
-  return accept_hit(t, u, v, __float_as_int(v0.w), tp, r);
+  return accept_hit<RECIP>(t, u, v, __float_as_int(v0.w), tp, r);
 }
 
 // Watertight test (Woop, Benthin & Wald 2013), RT_TRACE_WATERTIGHT: the ray is
@@ -215,6 +223,57 @@ __device__ __forceinline__ void load_ray(RayState& r, const float4 ro, const flo
   r.iz = inv_dir(rd.z);
   r.best_t = rd.w; r.bu = 0.0f; r.bv = 0.0f; r.best_prim = -1;
 }
+
+// ---- compact layout (NodeQ): per-ray constants and the slab test on 16-bit planes ----------
+// A plane q of axis a lies at origin + q * step; its distance along the ray is
+//   T(q) = (origin - o) * c + q * (step * c),      c = r.ix (2^64 for a component that is exactly 0)
+// computed as fma(m, A, B) with m = 2^23 + q (PRMT puts the 16 bits under the exponent of 2^23),
+// A = step * c and B = (origin - o) * c - 2^23 * A.  The NEAR plane of an axis is its low plane
+// when c >= 0, else its high plane: the ray holds the PRMT selector of each (sel, sel ^ 0x22), so
+// no min / max per axis is needed, and the near planes use B - d, the far planes B + d,
+// d = 2^-20 |(origin - o) * c|, which covers the roundings that grow with the distance of the
+// origin; those that grow with the step (at most 0.53 |A|) are covered by the whole step that
+// packing adds to every box (compact.cu).  NaNs (overflowing constants) drop out of the
+// NaN-ignoring min / max: the test never culls what slab() passes on a box inside this one.
+struct QRay {
+  float ax, ay, az;  // A
+  float nx, ny, nz;  // B - d
+  float fx, fy, fz;  // B + d
+  uint32_t sx, sy, sz;  // PRMT selector of the near plane: 0x7610 (low half) or 0x7632
+};
+__device__ __forceinline__ void q_axis(float origin, float step, float o, float d, float& A, float& Bn, float& Bf,
+                                       uint32_t& sel) {
+  const float c = d == 0.0f ? 18446744073709551616.0f : inv_dir(d);
+  A = step * c;
+  const float B = (origin - o) * c;
+  const float e = fabsf(B) * 9.5367431640625e-07f;  // 2^-20
+  Bn = fmaf(-8388608.0f, A, B - e);
+  Bf = fmaf(-8388608.0f, A, B + e);
+  sel = c >= 0.0f ? 0x7610u : 0x7632u;
+}
+__device__ __forceinline__ QRay q_setup(const RayState& r, const QGrid& g) {
+  QRay q;
+  q_axis(g.ox, g.sx, r.ox, r.dx, q.ax, q.nx, q.fx, q.sx);
+  q_axis(g.oy, g.sy, r.oy, r.dy, q.ay, q.ny, q.fy, q.sy);
+  q_axis(g.oz, g.sz, r.oz, r.dz, q.az, q.nz, q.fz, q.sz);
+  return q;
+}
+__device__ __forceinline__ float q_plane(uint32_t w, uint32_t sel) {
+  uint32_t r;  // prmt directly: __byte_perm masks a run-time selector with 0x7777 first (one LOP3 each)
+  asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(w), "r"(0x4B000000u), "r"(sel));
+  return __uint_as_float(r);
+}
+__device__ __forceinline__ bool slab_q(uint32_t wx, uint32_t wy, uint32_t wz, const QRay& q, const RayState& r,
+                                       float& tn) {
+  const float nx = fmaf(q_plane(wx, q.sx), q.ax, q.nx), fx = fmaf(q_plane(wx, q.sx ^ 0x22u), q.ax, q.fx);
+  const float ny = fmaf(q_plane(wy, q.sy), q.ay, q.ny), fy = fmaf(q_plane(wy, q.sy ^ 0x22u), q.ay, q.fy);
+  const float nz = fmaf(q_plane(wz, q.sz), q.az, q.nz), fz = fmaf(q_plane(wz, q.sz ^ 0x22u), q.az, q.fz);
+  tn = fmaxf(fmaxf(nx, ny), fmaxf(nz, r.tmin));
+  float tf = fminf(fminf(fx, fy), fminf(fz, r.best_t));
+  tf = tf * kSlabPad;
+  return tn <= tf;
+}
+__device__ __forceinline__ F8 ldg256u(const void* p) { return ldg256(p); }
 
 __device__ __forceinline__ float4 hit_record(const RayState& r, bool any) {
   if (r.best_prim < 0) return make_float4(__int_as_float(0x7f800000), 0.0f, 0.0f, __int_as_float(-1));

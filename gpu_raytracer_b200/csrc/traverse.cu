@@ -147,14 +147,17 @@ __device__ __forceinline__ float4 ld_cg_f4(const float4* p) {
   return r;
 }
 
-template <bool ANY, bool STATS, bool WT, bool PIPE, int SHS>
+// Q: the nodes are the 32-byte NodeQ records of the compact layout (qnodes, grid); one request
+// per node step, the slab test on 16-bit planes (trace_common.cuh slab_q).
+template <bool ANY, bool STATS, bool WT, bool PIPE, int SHS, bool Q = false>
 __global__ void __launch_bounds__(kTraceThreads, (PIPE || WT || STATS) ? 1 : 5)
 trace_kernel_dyn(const Node* __restrict__ nodes, const SortedTri* __restrict__ stris,
                  uint32_t n_tris, int root, const float4* __restrict__ rays,
                  unsigned long long n_rays, float4* __restrict__ hits,
                  unsigned long long* __restrict__ ray_counter,
                  unsigned long long* __restrict__ stats, int chunk, int refill_min, int leaf_min,
-                 TracePipe pipe, const uint32_t* __restrict__ perm) {
+                 TracePipe pipe, const uint32_t* __restrict__ perm,
+                 const NodeQ* __restrict__ qnodes = nullptr, QGrid grid = QGrid()) {
   const int lane = threadIdx.x & 31;
   const uint32_t lt_mask = (1u << lane) - 1u;
   const float inf = __int_as_float(0x7f800000);
@@ -180,6 +183,7 @@ trace_kernel_dyn(const Node* __restrict__ nodes, const SortedTri* __restrict__ s
   RayState r;
   r.best_prim = -1;
   WtRay wr = {0, 1, 2, 0.0f, 0.0f, 0.0f};
+  QRay qr = {};
   unsigned long long chunk_next = 0, chunk_end = 0;  // warp-uniform
   bool exhausted = false;                            // warp-uniform
   unsigned long long uploaded = 0;                   // warp-uniform: last watermark seen (PIPE)
@@ -289,6 +293,7 @@ trace_kernel_dyn(const Node* __restrict__ nodes, const SortedTri* __restrict__ s
         const float4 rd = PIPE ? ld_cg_f4(rays + 2 * my_ray + 1) : ld_stream(rays + 2 * my_ray + 1);
         load_ray(r, ro, rd);
         if (WT) wr = wt_setup(r);
+        if (Q) qr = q_setup(r, grid);
         has_ray = true;
         sp = 0;
         node = (n_tris != 0) ? root : kEmpty;
@@ -298,25 +303,37 @@ trace_kernel_dyn(const Node* __restrict__ nodes, const SortedTri* __restrict__ s
       chunk_next += took;
       if (PIPE) live_b += (uint32_t)took;
     }
-    if (__ballot_sync(0xFFFFFFFFu, has_ray) == 0u) {
+    const uint32_t live = __ballot_sync(0xFFFFFFFFu, has_ray);  // does not change in the node loop
+    if (live == 0u) {
       if (exhausted) break;
       continue;
     }
 
     // ---- internal nodes, until enough lanes wait at a leaf ----------------------
+    // one vote per trip: the lanes with a ray and no inner node are the ones that wait (leaf or finished)
+    const int inner_min = __popc(live) - leaf_min;  // leave when fewer lanes than this still walk
     while (true) {
       const uint32_t inner = __ballot_sync(0xFFFFFFFFu, has_ray && node >= 0);
-      if (inner == 0u) break;
-      const uint32_t waiting = __ballot_sync(0xFFFFFFFFu, has_ray && node < 0);  // leaf or finished
-      if (__popc(waiting) >= leaf_min) break;
+      if (inner == 0u || __popc(inner) <= inner_min) break;
       if (has_ray && node >= 0) {
         if (STATS) ++n_nodes;
-        const F8 c0h = ldg256(nodes + node), c1h = ldg256(&nodes[node].lo1);
-        const float4 lo0 = c0h.a, hi0 = c0h.b, lo1 = c1h.a, hi1 = c1h.b;
         float tn0, tn1;
-        const bool h0 = slab(lo0, hi0, r, tn0);
-        const bool h1 = slab(lo1, hi1, r, tn1);
-        const int c0 = __float_as_int(lo0.w), c1 = __float_as_int(lo1.w);
+        bool h0, h1;
+        int c0, c1;
+        if (Q) {
+          const F8 w = ldg256(qnodes + node);
+          h0 = slab_q(__float_as_uint(w.a.x), __float_as_uint(w.a.y), __float_as_uint(w.a.z), qr, r, tn0);
+          h1 = slab_q(__float_as_uint(w.a.w), __float_as_uint(w.b.x), __float_as_uint(w.b.y), qr, r, tn1);
+          c0 = __float_as_int(w.b.z);
+          c1 = __float_as_int(w.b.w);
+        } else {
+          const F8 c0h = ldg256(nodes + node), c1h = ldg256(&nodes[node].lo1);
+          const float4 lo0 = c0h.a, hi0 = c0h.b, lo1 = c1h.a, hi1 = c1h.b;
+          h0 = slab(lo0, hi0, r, tn0);
+          h1 = slab(lo1, hi1, r, tn1);
+          c0 = __float_as_int(lo0.w);
+          c1 = __float_as_int(lo1.w);
+        }
         if (h0 && h1) {
           const bool swap = tn1 < tn0;
           node = swap ? c1 : c0;
@@ -335,7 +352,7 @@ trace_kernel_dyn(const Node* __restrict__ nodes, const SortedTri* __restrict__ s
     if (has_ray && node < 0 && node != kEmpty) {
       if (STATS) ++n_tests;
       const bool hit = WT ? intersect_wt(stris, (uint32_t)(~node), r, wr)
-                          : intersect(stris, (uint32_t)(~node), r);
+                          : intersect<Q>(stris, (uint32_t)(~node), r);
       if (ANY && hit) {
         node = kEmpty;
         sp = 0;
@@ -449,7 +466,7 @@ int launch_trace(const Node* nodes, const SortedTri* stris, uint64_t n_tris, int
                  const float4* rays,
                  uint64_t n_rays, uint32_t flags, float4* hits, unsigned long long* ray_counter,
                  cudaStream_t s, unsigned long long* stats, const TracePipe* pipe,
-                 const uint32_t* perm) {
+                 const uint32_t* perm, const Compact* compact) {
   if (n_rays == 0) return 0;
   if (perm && (pipe || params().trace_variant == 0))
     return fail(-1, "launch_trace: a ray permutation needs the dynamic-fetch kernel, device buffers");
@@ -497,7 +514,18 @@ int launch_trace(const Node* nodes, const SortedTri* stris, uint64_t n_tris, int
     // auto: rays that come through a permutation are incoherent by the caller's word, and for
     // those the shared-memory stack top pays (config 5 with the flag: 4,050 -> 4,145 Mrays/s)
     const int shs = p.trace_sh_stack >= 0 ? p.trace_sh_stack : (perm ? 8 : 0);
-    if (!st && !wt && shs > 0) {  // experiment: stack top in shared memory
+    if (compact && compact->valid && !wt && p.trace_compact != 0) {
+      // 32-byte nodes (watertight launches stay on the 64-byte layout)
+      const NodeQ* qn = compact->nodes;
+      const QGrid grid = compact->grid;
+#define RT_TRACE_Q(A, S, K)                                                                \
+  trace_kernel_dyn<A, S, false, false, K, true><<<(unsigned)blocks, kTraceThreads, 0, s>>>( \
+      nodes, stris, (uint32_t)n_tris, root, rays, n_rays, hits, ray_counter, stats, chunk, refill_min, leaf_min, no_pipe, perm, qn, grid)
+      if (st) { if (any) RT_TRACE_Q(true, true, 0); else RT_TRACE_Q(false, true, 0); }
+      else if (shs > 0) { if (any) RT_TRACE_Q(true, false, 8); else RT_TRACE_Q(false, false, 8); }
+      else { if (any) RT_TRACE_Q(true, false, 0); else RT_TRACE_Q(false, false, 0); }
+#undef RT_TRACE_Q
+    } else if (!st && !wt && shs > 0) {  // experiment: stack top in shared memory
       if (any) { if (shs == 8) RT_TRACE_DYN_K(true, false, false, 8); else if (shs == 16) RT_TRACE_DYN_K(true, false, false, 16); else RT_TRACE_DYN_K(true, false, false, 24); }
       else     { if (shs == 8) RT_TRACE_DYN_K(false, false, false, 8); else if (shs == 16) RT_TRACE_DYN_K(false, false, false, 16); else RT_TRACE_DYN_K(false, false, false, 24); }
     } else {

@@ -77,6 +77,12 @@ extern "C" {
                                  hits, bit for bit.  More than 3 triangles; +48 n bytes (the triangles
                                  in wide-node order) + 80 bytes per wide node.  Wins for incoherent rays */
 
+#define RT_BUILD_COMPACT 16u  /* also pack the binary tree into 32-byte nodes (16-bit child boxes on one
+                                 grid per scene, rounded outwards); trace_rays then walks those with one
+                                 32-byte request per node step instead of two: same hits, bit for bit.
+                                 At least 2 triangles; +32 bytes per node.  Watertight launches and the
+                                 wide layouts, when present, are not affected */
+
 /* scene kinds for rt_gen_scene */
 #define RT_SCENE_CORNELL 0     /* config 1: 1,024 triangles, no parameters       */
 #define RT_SCENE_SOUP 1        /* config 2: p0 = triangle count                  */
@@ -187,6 +193,16 @@ RT_API int bvh_widen(rt_bvh* h);
  * subtrees with <= 4 triangles are unused (unspecified bytes).  root_ref: the
  * reference traversal starts from. */
 RT_API int bvh_read_wide(const rt_bvh* h, void* nodes4, uint32_t* root_ref);
+
+/* The 32-byte binary layout (what RT_BUILD_COMPACT does at build time) of any handle with at
+ * least 2 triangles, also one filled through bvh_device_buffers + bvh_commit or bvh_load. */
+RT_API int bvh_compact(rt_bvh* h);
+/* nodes: host, (n - 1) x 32 bytes (may be NULL); grid6: 6 floats (may be NULL): plane 0 of the
+ * grid on x, y, z, then the step on x, y, z.  Node i is the 64-byte node i of bvh_read_boxes:
+ *   u32 box[6]; i32 child0, child1;     box[3 c + a] = lo | hi << 16 of child c on axis a
+ * with plane q of axis a at grid6[a] + q * grid6[3 + a]; [lo, hi] contains the exact child box
+ * and at least one whole step on either side of it. */
+RT_API int bvh_read_compact(const rt_bvh* h, void* nodes, float* grid6);
 
 /* Compressed 8-wide layout (what RT_BUILD_WIDE8 does at build time) of any handle with more than
  * 3 triangles, also one filled through bvh_device_buffers + bvh_commit or bvh_load. */
@@ -339,7 +355,7 @@ RT_API int rt_trim(int device);
  * "pool.keep_mb" (memory the pool keeps cached per device between calls; 0, the default,
  * keeps everything, which makes repeated builds allocation-free), "sort.variant", "sort.bits",
  * "trace.variant", "trace.blocks_per_sm", "trace.chunk", "trace.refill_min", "trace.leaf_min",
- * "trace.wide", "wide.leaf_max", "trace.streamed" (0 = always stage host batches),
+ * "trace.wide", "trace.compact" (0 = ignore a handle's 32-byte nodes), "wide.leaf_max", "trace.streamed" (0 = always stage host batches),
  * "trace.stage_chunk", "trace.zero_copy", "render.band" (rt_render_ao: log2 of the rays per band,
  * 16..20; 0, the default, = 20), "trace.sh_stack" (0 | 8 | 16 | 24 stack levels in
  * shared memory; -1, the default: 8 for RT_TRACE_REORDER launches, else 0), "build.pdl" (1 = build kernels launched as programmatic dependents, the

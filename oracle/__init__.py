@@ -160,6 +160,35 @@ def shade(tris: np.ndarray, rays: np.ndarray, hits: np.ndarray, ao_hits=None, sp
     return out
 
 
+def compact_grid(bounds: np.ndarray) -> np.ndarray:
+    """Grid of the 32-byte binary layout (DESIGN.md §5 "compact nodes"; no reference counterpart):
+    per axis 65,000 steps across the scene box, never finer than 2^-21 of the box's largest
+    coordinate, the step rounded up to float; plane 0 lies three steps below the box.
+    Returns [origin xyz, step xyz] as float32."""
+    b = np.asarray(bounds, dtype=np.float64)
+    lo, hi = b[:3], b[3:]
+    step = np.maximum(np.maximum((hi - lo) / 65000.0, np.maximum(np.abs(lo), np.abs(hi)) * 2.0 ** -21), 1e-30)
+    sf = step.astype(np.float32)
+    up = sf.astype(np.float64) < step
+    sf[up] = np.nextafter(sf[up], np.float32(np.inf))
+    origin = (lo - 3.0 * sf.astype(np.float64)).astype(np.float32)
+    return np.concatenate([origin, sf]).astype(np.float32)
+
+
+def compact_pack(boxes: np.ndarray, grid: np.ndarray) -> np.ndarray:
+    """16-bit plane pairs of [m, 6] float32 boxes on ``grid``: per axis lo | hi << 16, both rounded
+    outwards by at least one whole step (floor(x - 1e-6) - 1, ceil(x + 1e-6) + 1 in float64, x in
+    steps from plane 0).  Returns uint32 [m, 3]."""
+    boxes = np.asarray(boxes, dtype=np.float32)
+    origin = grid[:3].astype(np.float64)
+    inv = 1.0 / grid[3:].astype(np.float64)
+    xl = (boxes[:, :3].astype(np.float64) - origin) * inv
+    xh = (boxes[:, 3:].astype(np.float64) - origin) * inv
+    ql = np.clip(np.floor(xl - 1e-6).astype(np.int64) - 1, 0, 65535)
+    qh = np.clip(np.ceil(xh + 1e-6).astype(np.int64) + 1, 0, 65535)
+    return (ql | (qh << 16)).astype(np.uint32)
+
+
 def canon8(nodes: np.ndarray, tris: np.ndarray):
     """A compressed 8-wide tree (bvh_read_wide8) renumbered breadth first, the numbering
     ``OracleBvh.collapse8`` uses.  Returns (nodes uint8 [m, 80], tris float32 [n, 12])."""

@@ -1,7 +1,8 @@
 """The trace launches of bench.py's default workload, once each (the command ncu wraps):
 flake10m with the bench camera: 3840x2160 primary rays (closest hit), their 4 AO rays per pixel
 (any-hit), and a 2^24-ray window of config 5's random rays, plain and with RT_TRACE_REORDER.
-usage: prof_bench_trace.py [wide8]   (wide8: trace the compressed 8-wide layout instead of BVH2)"""
+usage: prof_bench_trace.py [wide8 | compact]   (trace the compressed 8-wide layout / the 32-byte
+binary nodes instead of the 64-byte BVH2)"""
 import os
 import sys
 
@@ -16,7 +17,7 @@ wl = WORKLOADS["flake10m"]
 wide8 = "wide8" in sys.argv[1:]
 tris = g.gen_scene(*wl.scene)
 flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
-kw = dict(wide8=True) if wide8 else {}
+kw = dict(wide8=True) if wide8 else (dict(compact=True) if "compact" in sys.argv[1:] else {})
 with g.Bvh.build(tris, **kw) as bvh:
     cam = wl.camera()
     rays = g.gen_primary_rays(cam, wl.width, wl.height)
