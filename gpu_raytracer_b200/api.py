@@ -379,9 +379,11 @@ class MultiBvh:
         self._arr = (C.c_void_p * len(handles))(*[h._h for h in handles])
 
     @classmethod
-    def build(cls, tris, devices, key_bits: int = 30, strategy: int = L.RT_MULTI_REDUNDANT) -> "MultiBvh":
+    def build(cls, tris, devices, key_bits: int = 30, strategy: int = L.RT_MULTI_REDUNDANT,
+              flags: int = 0) -> "MultiBvh":
+        """``flags``: RT_BUILD_* (the wide / compact layouts are derived on every device)."""
         n = _rows(tris, 12)
-        opts = L.BuildOpts(key_bits=key_bits, flags=0, device=-1, reserved=0, stream=None)
+        opts = L.BuildOpts(key_bits=key_bits, flags=flags, device=-1, reserved=0, stream=None)
         devs = (C.c_int32 * len(devices))(*devices)
         out = (C.c_void_p * len(devices))()
         L.check(L.lib().build_bvh_multi(_ptr(tris) if n else None, n, C.byref(opts), devs, len(devices),

@@ -1294,6 +1294,17 @@ int rt::adopt_committed(rt_bvh* dst, const rt_bvh* src) {
   dst->key_bits = src->key_bits;
   memcpy(dst->bounds, src->bounds, sizeof(dst->bounds));
   dst->root = src->root;
+  // the layouts the source holds beside the binary tree are derived again on this device
+  // (cheaper than copying them, and bit-identical: they are functions of the nodes)
+  cudaStream_t s = 0;
+  if (src->is_wide) {
+    dst->wide_leaf_max = src->wide_leaf_max;
+    RT_TRY(widen(dst, s));
+  }
+  dst->wide_root = wide_root_ref(dst->n, dst->root, dst->wide_leaf_max);
+  if (src->wide8.valid) RT_TRY(widen8(dst, s));
+  if (src->compact.valid) RT_TRY(compact(dst, s));
+  RT_CUDA(cudaStreamSynchronize(s));
   return 0;
 }
 
