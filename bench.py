@@ -334,6 +334,20 @@ def run_ours(args):
                 done += c
         return ms / passes, nhit // passes
 
+    def attach_ncu(leg, key):
+        """ncu's view of a config-5 launch (profiles/traffic.json), rescaled to this run's rate"""
+        nc = ncu_record(key)
+        r = leg["roofline"]
+        if nc.get("dram_bytes_per_ray"):
+            r["dram_bytes_per_ray_ncu"] = nc["dram_bytes_per_ray"]
+            r["dram_frac"] = nc["dram_bytes_per_ray"] * leg["mrays_s"] / 1e3 / peak
+        if nc.get("ncu_us") and nc.get("rays"):
+            scale = (nc["ncu_us"] / nc["rays"]) * leg["mrays_s"]
+            if nc.get("l1_lsu_wavefront_pct"):
+                r["l1_frac"] = nc["l1_lsu_wavefront_pct"] / 100.0 * scale
+            if nc.get("issue_pct"):
+                r["issue_frac"] = nc["issue_pct"] / 100.0 * scale
+
     def config5_record(bvh, total, passes):
         rec = {"rays": total, "n_tris": bvh.n_tris, "scaling": "strong",
                "sharding": "contiguous ranges of ONE batch (sharding.shard_range), rays generated per "
@@ -359,13 +373,7 @@ def run_ours(args):
                 gbs = bpr * rec[name]["mrays_s"] / 1e3
                 rec[name]["roofline"] = {"achieved_gbs": gbs, "frac": gbs / peak}
             for name, key in (("plain", "random1b"), ("reorder", "random1b:reorder")):
-                nc = ncu_record(key)
-                if nc.get("dram_bytes_per_ray"):
-                    rec[name]["roofline"]["dram_bytes_per_ray_ncu"] = nc["dram_bytes_per_ray"]
-                    rec[name]["roofline"]["dram_frac"] = nc["dram_bytes_per_ray"] * rec[name]["mrays_s"] / 1e3 / peak
-                if nc.get("l1_lsu_wavefront_pct") and nc.get("ncu_us"):
-                    rec[name]["roofline"]["l1_frac"] = (nc["l1_lsu_wavefront_pct"] / 100.0 *
-                                                        (nc["ncu_us"] / nc["rays"]) * rec[name]["mrays_s"])
+                attach_ncu(rec[name], key)
         # the same batch through the 32-byte nodes (RT_BUILD_COMPACT): packed here, outside the timing
         bvh.compact()
         for name, reorder in (("compact", False), ("compact_reorder", True)):
@@ -377,9 +385,10 @@ def run_ours(args):
             _, nodes_c, tests_c = bvh.trace_stats(rays)
             bpr_c = 48 + 32 * nodes_c / ns + 48 * tests_c / ns
             rec["per_ray_compact"] = {"nodes_fetched": nodes_c / ns, "tris_tested": tests_c / ns, "bytes": bpr_c}
-            for name in ("compact", "compact_reorder"):
+            for name, key in (("compact", "random1b:compact"), ("compact_reorder", "random1b:reorder:compact")):
                 gbs = bpr_c * rec[name]["mrays_s"] / 1e3
                 rec[name]["roofline"] = {"achieved_gbs": gbs, "frac": gbs / peak}
+                attach_ncu(rec[name], key)
         return rec
 
     wl = WORKLOADS[args.workload]
@@ -655,7 +664,10 @@ def run_ours(args):
              # clock and SM): its share of peak under ncu, rescaled to this run's duration
              "l1_sectors": nc.get("l1_sectors"),
              "l1_frac": (nc["l1_lsu_wavefront_pct"] / 100.0 * (nc["ncu_us"] / 1e3) / ms)
-                        if nc.get("l1_lsu_wavefront_pct") and nc.get("ncu_us") else None}
+                        if nc.get("l1_lsu_wavefront_pct") and nc.get("ncu_us") else None,
+             # (iii) the other limit the kernel sits at: issue slots in use (ncu, same rescaling)
+             "issue_frac": (nc["issue_pct"] / 100.0 * (nc["ncu_us"] / 1e3) / ms)
+                           if nc.get("issue_pct") and nc.get("ncu_us") else None}
         return r
     kr = {"primary": kernel_roofline(wl.name + ":primary", "trace_kernel_dyn<closest>", bytes_primary,
                                      trace_ms / K, count, nodes, tests)}
@@ -669,8 +681,8 @@ def run_ours(args):
             "note": "achieved = algorithmic bytes (48 + 64 x nodes fetched + 48 x triangles tested per ray, "
                     "counted by trace_rays_stats) / CUDA-event time.  The BVH of a coherent frame is served "
                     "from L1/L2, so `frac` can exceed 1 and says nothing about distance to a bound; "
-                    "`dram_frac` (ncu dram bytes / time / peak) and `l1_frac` (ncu: LSU data-pipe wavefronts, share of the pipe's peak) "
-                    "are the fractions of real limits, and configs.random1b.*.roofline is the genuine "
+                    "`dram_frac` (ncu dram bytes / time / peak), `l1_frac` (ncu: LSU data-pipe wavefronts, share of the pipe's peak) "
+                    "and `issue_frac` (ncu: issue slots in use) are the fractions of real limits, and configs.random1b.*.roofline is the genuine "
                     "HBM fraction of §8(d) (working set 1.1 GB >> L2)",
             "stages": stages}
     n_img = count
