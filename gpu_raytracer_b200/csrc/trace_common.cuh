@@ -100,16 +100,17 @@ static __device__ __noinline__ bool own_box_admits(const float4* __restrict__ tp
               omax(omax(v0.x, v1.x), v2.x), omax(omax(v0.y, v1.y), v2.y), omax(omax(v0.z, v1.z), v2.z), r, tn) &&
          tn <= t * kSlabPad;
 }
-// RECIP: the caller does not keep r.ix / iy / iz alive (compact layout); they are computed again
-// from the direction, by the same inv_dir(), for the few candidates that get this far.
-__device__ __forceinline__ float inv_dir(float d);
-template <bool RECIP = false>
+// SPILLED: the caller does not keep r.ix / iy / iz in registers (compact layout); `inv` points at
+// this thread's copy of them in shared memory (inv[0], inv[kTraceThreads], inv[2 kTraceThreads]),
+// read by the few candidates that get this far.  (Computing 1/d again instead cost three
+// 20-instruction IEEE reciprocals per candidate: 5 % of the kernel's instructions.)
+template <bool SPILLED = false>
 __device__ __forceinline__ bool accept_hit(float t, float u, float v, int prim, const float4* __restrict__ tp,
-                                           RayState& r) {
+                                           RayState& r, const float* inv = nullptr) {
   bool ok = (t > r.tmin) &&
             ((t < r.best_t) || (t == r.best_t && r.best_prim >= 0 && prim < r.best_prim));
   if (ok) {
-    if (RECIP) ok = own_box_admits(tp, r.ox, r.oy, r.oz, inv_dir(r.dx), inv_dir(r.dy), inv_dir(r.dz), r.tmin, r.best_t, t);
+    if (SPILLED) ok = own_box_admits(tp, r.ox, r.oy, r.oz, inv[0], inv[kTraceThreads], inv[2 * kTraceThreads], r.tmin, r.best_t, t);
     else ok = own_box_admits(tp, r.ox, r.oy, r.oz, r.ix, r.iy, r.iz, r.tmin, r.best_t, t);
   }
   if (ok) {
@@ -124,9 +125,9 @@ __device__ __forceinline__ bool accept_hit(float t, float u, float v, int prim, 
 // Moeller-Trumbore, two-sided.  The triangle record holds the raw vertices
 // {v0 | prim, v1, v2}; the edges are one subtraction each, as in the oracle.
 // Returns true when the hit was accepted.
-template <bool RECIP = false>
+template <bool SPILLED = false>
 __device__ __forceinline__ bool intersect(const SortedTri* __restrict__ stris, uint32_t j,
-                                          RayState& r) {
+                                          RayState& r, const float* sh_inv = nullptr) {
   const float4* tp = reinterpret_cast<const float4*>(stris + j);
   const float4 v0 = __ldg(tp), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
   const float e1x = v1.x - v0.x, e1y = v1.y - v0.y, e1z = v1.z - v0.z;
@@ -145,7 +146,7 @@ __device__ __forceinline__ bool intersect(const SortedTri* __restrict__ stris, u
   const float v = fmaf(r.dx, qx, fmaf(r.dy, qy, r.dz * qz)) * inv;
   const float t = fmaf(e2x, qx, fmaf(e2y, qy, e2z * qz)) * inv;
   if (!((u >= 0.0f) && (v >= 0.0f) && ((u + v) <= 1.0f))) return false;
-  return accept_hit<RECIP>(t, u, v, __float_as_int(v0.w), tp, r);
+  return accept_hit<SPILLED>(t, u, v, __float_as_int(v0.w), tp, r, sh_inv);
 }
 
 // Watertight test (Woop, Benthin & Wald 2013), RT_TRACE_WATERTIGHT: the ray is
@@ -241,9 +242,9 @@ struct QRay {
   float fx, fy, fz;  // B + d
   uint32_t sx, sy, sz;  // PRMT selector of the near plane: 0x7610 (low half) or 0x7632
 };
-__device__ __forceinline__ void q_axis(float origin, float step, float o, float d, float& A, float& Bn, float& Bf,
-                                       uint32_t& sel) {
-  const float c = d == 0.0f ? 18446744073709551616.0f : inv_dir(d);
+__device__ __forceinline__ void q_axis(float origin, float step, float o, float d, float inv, float& A, float& Bn,
+                                       float& Bf, uint32_t& sel) {
+  const float c = d == 0.0f ? 18446744073709551616.0f : inv;  // inv = inv_dir(d), from load_ray
   A = step * c;
   const float B = (origin - o) * c;
   const float e = fabsf(B) * 9.5367431640625e-07f;  // 2^-20
@@ -253,9 +254,9 @@ __device__ __forceinline__ void q_axis(float origin, float step, float o, float 
 }
 __device__ __forceinline__ QRay q_setup(const RayState& r, const QGrid& g) {
   QRay q;
-  q_axis(g.ox, g.sx, r.ox, r.dx, q.ax, q.nx, q.fx, q.sx);
-  q_axis(g.oy, g.sy, r.oy, r.dy, q.ay, q.ny, q.fy, q.sy);
-  q_axis(g.oz, g.sz, r.oz, r.dz, q.az, q.nz, q.fz, q.sz);
+  q_axis(g.ox, g.sx, r.ox, r.dx, r.ix, q.ax, q.nx, q.fx, q.sx);
+  q_axis(g.oy, g.sy, r.oy, r.dy, r.iy, q.ay, q.ny, q.fy, q.sy);
+  q_axis(g.oz, g.sz, r.oz, r.dz, r.iz, q.az, q.nz, q.fz, q.sz);
   return q;
 }
 __device__ __forceinline__ float q_plane(uint32_t w, uint32_t sel) {

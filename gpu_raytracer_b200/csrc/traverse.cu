@@ -166,6 +166,8 @@ trace_kernel_dyn(const Node* __restrict__ nodes, const SortedTri* __restrict__ s
   // the first SHS stack levels live in shared memory ([level][thread]: bank = lane, one
   // wavefront whatever the lanes' depths), the rest in local memory
   __shared__ int sh_stack[SHS > 0 ? SHS : 1][kTraceThreads];
+  // Q: 1/d of the thread's ray, for the acceptance rule's box test (the node loop does not use it)
+  __shared__ float sh_inv[Q ? 3 : 1][kTraceThreads];
   int stack[kStack - SHS];
   int sp = 0;
   auto push = [&](int v) {
@@ -293,7 +295,12 @@ trace_kernel_dyn(const Node* __restrict__ nodes, const SortedTri* __restrict__ s
         const float4 rd = PIPE ? ld_cg_f4(rays + 2 * my_ray + 1) : ld_stream(rays + 2 * my_ray + 1);
         load_ray(r, ro, rd);
         if (WT) wr = wt_setup(r);
-        if (Q) qr = q_setup(r, grid);
+        if (Q) {
+          qr = q_setup(r, grid);
+          sh_inv[0][threadIdx.x] = r.ix;
+          sh_inv[Q ? 1 : 0][threadIdx.x] = r.iy;
+          sh_inv[Q ? 2 : 0][threadIdx.x] = r.iz;
+        }
         has_ray = true;
         sp = 0;
         node = (n_tris != 0) ? root : kEmpty;
@@ -352,7 +359,7 @@ trace_kernel_dyn(const Node* __restrict__ nodes, const SortedTri* __restrict__ s
     if (has_ray && node < 0 && node != kEmpty) {
       if (STATS) ++n_tests;
       const bool hit = WT ? intersect_wt(stris, (uint32_t)(~node), r, wr)
-                          : intersect<Q>(stris, (uint32_t)(~node), r);
+                          : intersect<Q>(stris, (uint32_t)(~node), r, &sh_inv[0][threadIdx.x]);
       if (ANY && hit) {
         node = kEmpty;
         sp = 0;
