@@ -1001,10 +1001,32 @@ extern "C" int rt_render_ao(const rt_bvh* h, const float* tris, const float* ray
   uint64_t band_max = band_log2 >= 16 && band_log2 <= 20 ? 1ull << band_log2 : Pipeline::kChunk;
   while (spp && band_max * spp > (8ull << 20) && band_max > (1ull << 16)) band_max >>= 1;
   const uint64_t band = n_rays < band_max ? n_rays : band_max;
-  // the first bands are a quarter and a half of a band: the first launch waits for less
-  const bool taper = !rays_dev && n_rays >= 4 * band && params().render_taper != 0;
-  const uint64_t head = taper ? band / 4 + band / 2 : 0;
-  const uint64_t bands = (n_rays - head + band - 1) / band + (taper ? 2 : 0);
+  // The frame's first bands are a quarter and a half of a band (host rays: the first launch
+  // waits for 8 MB, not 32) and so are its last ones (host results: what is still to go down
+  // when the last launch ends is a quarter band).  render.taper: bit 0 = head, bit 1 = tail.
+  const int taper_knob = params().render_taper;
+  const bool big = n_rays >= 6 * band;
+  const bool taper_in = big && !rays_dev && (taper_knob & 1) != 0;
+  const bool taper_out = big && (!rgb_dev || (hits && !hits_dev)) && (taper_knob & 2) != 0;
+  std::vector<uint64_t> cuts;  // band k = [cuts[k], cuts[k + 1])
+  {
+    const uint64_t head[2] = {band / 4, band / 2}, tail[2] = {band / 2, band / 4};
+    const uint64_t tail_sum = taper_out ? tail[0] + tail[1] : 0;
+    uint64_t at = 0;
+    cuts.push_back(0);
+    if (taper_in)
+      for (uint64_t h : head) cuts.push_back(at += h);
+    while (n_rays - at > band + tail_sum) cuts.push_back(at += band);
+    if (taper_out) {
+      // what is left (between tail_sum and band + tail_sum rays): one middle band, then the tail
+      const uint64_t rest = n_rays - at;
+      if (rest > tail_sum) cuts.push_back(at += rest - tail_sum);
+      for (uint64_t t : tail) cuts.push_back(at += t);
+    } else {
+      cuts.push_back(n_rays);
+    }
+  }
+  const uint64_t bands = cuts.size() - 1;
   const int slots = bands < (uint64_t)kSlots ? (int)bands : kSlots;
   TempPool tmp(p.s_run);
   float4 *d_rays[kSlots] = {}, *d_hits[kSlots] = {}, *d_ao[kSlots] = {}, *d_aoh[kSlots] = {};
@@ -1061,12 +1083,7 @@ extern "C" int rt_render_ao(const rt_bvh* h, const float* tris, const float* ray
     const int b = (int)(k % (uint64_t)slots), c = (int)(k & 1);
     cudaStream_t sc = s_cmp[c];
     const bool reused = k >= (uint64_t)slots;
-    uint64_t first = k * band, cnt = band;
-    if (taper) {
-      first = k == 0 ? 0 : k == 1 ? band / 4 : head + (k - 2) * band;
-      cnt = k == 0 ? band / 4 : k == 1 ? band / 2 : band;
-    }
-    if (n_rays - first < cnt) cnt = n_rays - first;
+    const uint64_t first = cuts[k], cnt = cuts[k + 1] - first;
     const float4* r4;
     if (rays_dev) {
       r4 = reinterpret_cast<const float4*>(rays) + 2 * first;

@@ -33,7 +33,7 @@ def main():
     d_rgb = torch.empty((n, 3), device="cuda")
     cases = {"all host": (h_rays, h_hits, h_rgb), "rays host, out device": (h_rays, d_hits, d_rgb),
              "rays device, out host": (rays, h_hits, h_rgb), "all device": (rays, d_hits, d_rgb)}
-    for band, taper in ((20, 1), (20, 0), (19, 1), (19, 0), (18, 0)):
+    for band, taper in ((20, 3), (20, 1), (20, 0), (19, 3), (19, 0)):
         g.set_param("render.band", band)
         g.set_param("render.taper", taper)
         for name, (r, hh, gg) in cases.items():
