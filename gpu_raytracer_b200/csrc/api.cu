@@ -1074,6 +1074,17 @@ extern "C" int rt_render_ao(const rt_bvh* h, const float* tris, const float* ray
     }
   } ev;
   RT_TRY(ev.create(slots));
+  // development aid (RT_RENDER_TIMELINE=1): when each band's upload, first launch, last launch
+  // and download ended, in ms from the start of the call, printed to stderr
+  const bool timeline = getenv("RT_RENDER_TIMELINE") != nullptr;
+  std::vector<cudaEvent_t> tl;
+  cudaEvent_t tl0 = nullptr;
+  if (timeline) {
+    tl.resize(bands * 5);
+    for (auto& e : tl) RT_CUDA(cudaEventCreate(&e));
+    RT_CUDA(cudaEventCreate(&tl0));
+    RT_CUDA(cudaEventRecord(tl0, p.s_in));
+  }
   const float4* tris4 = reinterpret_cast<const float4*>(tris);
   // Even and odd bands compute on their own streams: every trace launch is a persistent grid
   // that fills the GPU, so the next band's blocks start as the blocks of this band's launch
@@ -1089,7 +1100,9 @@ extern "C" int rt_render_ao(const rt_bvh* h, const float* tris, const float* ray
       r4 = reinterpret_cast<const float4*>(rays) + 2 * first;
     } else {
       if (reused) RT_CUDA(cudaStreamWaitEvent(p.s_in, ev.run[b], 0));  // the slot's last reader (shade)
+      if (timeline) RT_CUDA(cudaEventRecord(tl[k * 5 + 0], p.s_in));
       RT_CUDA(cudaMemcpyAsync(d_rays[b], rays + 8 * first, cnt * 32, cudaMemcpyHostToDevice, p.s_in));
+      if (timeline) RT_CUDA(cudaEventRecord(tl[k * 5 + 1], p.s_in));
       RT_CUDA(cudaEventRecord(ev.in[b], p.s_in));
       RT_CUDA(cudaStreamWaitEvent(sc, ev.in[b], 0));
       r4 = d_rays[b];
@@ -1101,6 +1114,7 @@ extern "C" int rt_render_ao(const rt_bvh* h, const float* tris, const float* ray
     }
     float4* h4 = hits_dev ? reinterpret_cast<float4*>(hits) + first : d_hits[b];
     float* g3 = rgb_dev ? rgb + 3 * first : d_rgb[b];
+    if (timeline) RT_CUDA(cudaEventRecord(tl[k * 5 + 2], sc));
     RT_TRY(launch_trace_h(h, r4, cnt, flags, h4, p.counters + 2 * c, sc));
     RT_CUDA(cudaEventRecord(ev.hit[b], sc));
     if (spp) {
@@ -1109,6 +1123,7 @@ extern "C" int rt_render_ao(const rt_bvh* h, const float* tris, const float* ray
     }
     RT_TRY(launch_shade(tris4, r4, h4, spp ? d_aoh[b] : nullptr, cnt, spp, g3, sc));
     RT_CUDA(cudaEventRecord(ev.run[b], sc));
+    if (timeline) RT_CUDA(cudaEventRecord(tl[k * 5 + 3], sc));
     if (hits && !hits_dev) {
       RT_CUDA(cudaStreamWaitEvent(p.s_out, ev.hit[b], 0));
       RT_CUDA(cudaMemcpyAsync(hits + 4 * first, h4, cnt * 16, cudaMemcpyDeviceToHost, p.s_out));
@@ -1118,6 +1133,19 @@ extern "C" int rt_render_ao(const rt_bvh* h, const float* tris, const float* ray
       RT_CUDA(cudaMemcpyAsync(rgb + 3 * first, g3, cnt * 12, cudaMemcpyDeviceToHost, p.s_out));
     }
     RT_CUDA(cudaEventRecord(ev.out[b], p.s_out));
+    if (timeline) RT_CUDA(cudaEventRecord(tl[k * 5 + 4], p.s_out));
+  }
+  if (timeline) {
+    cudaStreamSynchronize(p.s_in); cudaStreamSynchronize(p.s_run); cudaStreamSynchronize(p.s_run2); cudaStreamSynchronize(p.s_out);
+    for (uint64_t k = 0; k < bands; ++k) {
+      float t[5] = {0, 0, 0, 0, 0};
+      for (int i = 0; i < 5; ++i)
+        if (cudaEventElapsedTime(&t[i], tl0, tl[k * 5 + i]) != cudaSuccess) { cudaGetLastError(); t[i] = -1; }
+      fprintf(stderr, "band %2llu rays %8llu  up %.3f..%.3f  run %.3f..%.3f  down %.3f\n", (unsigned long long)k,
+              (unsigned long long)(cuts[k + 1] - cuts[k]), t[0], t[1], t[2], t[3], t[4]);
+    }
+    for (auto& e : tl) cudaEventDestroy(e);
+    cudaEventDestroy(tl0);
   }
   RT_CUDA(cudaStreamSynchronize(p.s_run2));
   RT_CUDA(cudaStreamSynchronize(p.s_run));
