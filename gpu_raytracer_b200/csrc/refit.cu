@@ -632,6 +632,8 @@ static int build_tree_impl(const float4* tris, const uint32_t* sorted_idx, const
 #define RT_WALK(T, L) launch_walk<KeyT, T, L>(tris, sorted_idx, keys, n, flags, nodes, stris, header, queue, \
                                                queue_count, capacity, s, abort_flag)
   switch (g_build_walk_shape.load(std::memory_order_relaxed)) {
+    case 128 * 16 + 1: RT_TRY(RT_WALK(128, 1)); break;
+    case 512 * 16 + 1: RT_TRY(RT_WALK(512, 1)); break;
     case 256 * 16 + 2: RT_TRY(RT_WALK(256, 2)); break;
     case 256 * 16 + 4: RT_TRY(RT_WALK(256, 4)); break;
     case 128 * 16 + 2: RT_TRY(RT_WALK(128, 2)); break;

@@ -5,8 +5,10 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import gpu_raytracer_b200 as g
 from gpu_raytracer_b200.configs import WORKLOADS
 from tools.bench_sort import peak
-shapes = [(256, 1), (256, 2), (128, 2), (128, 4), (256, 4), (64, 4)]
-for name in ("soup1m", "flake10m", "terrain100m"):
+shapes = [(256, 1), (128, 1), (512, 1), (256, 2), (128, 2), (128, 4), (256, 4), (64, 4)]
+if len(sys.argv) > 1:  # e.g. 256x1,128x1,512x1
+    shapes = [tuple(int(v) for v in a.split("x")) for a in sys.argv[1].split(",")]
+for name in (sys.argv[2].split(",") if len(sys.argv) > 2 else ("soup1m", "flake10m", "terrain100m")):
     wl = WORKLOADS[name]
     tris = g.gen_scene(*wl.scene)
     n = int(tris.shape[0])
