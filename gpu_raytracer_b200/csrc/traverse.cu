@@ -147,10 +147,13 @@ __device__ __forceinline__ float4 ld_cg_f4(const float4* p) {
   return r;
 }
 
+#ifndef RT_TRACE_MINB
+#define RT_TRACE_MINB 5  // resident CTAs per SM the register allocation is held to
+#endif
 // Q: the nodes are the 32-byte NodeQ records of the compact layout (qnodes, grid); one request
 // per node step, the slab test on 16-bit planes (trace_common.cuh slab_q).
 template <bool ANY, bool STATS, bool WT, bool PIPE, int SHS, bool Q = false>
-__global__ void __launch_bounds__(kTraceThreads, (PIPE || WT || STATS) ? 1 : 5)
+__global__ void __launch_bounds__(kTraceThreads, (PIPE || WT || STATS) ? 1 : RT_TRACE_MINB)
 trace_kernel_dyn(const Node* __restrict__ nodes, const SortedTri* __restrict__ stris,
                  uint32_t n_tris, int root, const float4* __restrict__ rays,
                  unsigned long long n_rays, float4* __restrict__ hits,
