@@ -73,6 +73,23 @@ def test_header_compiles_and_links_as_c99(rt, tmp_path):
     assert ("no device" in res.stdout) or ("ok" in res.stdout)
 
 
+def test_cpp_bench_main_compiles_and_links(rt, tmp_path):
+    """tools/cpp/bench_main.cpp (SURVEY.md §8b "a small C++ bench main") builds against the header
+    and the library with nothing from Python in it; without a device it says so and exits 0."""
+    import json
+    exe = tmp_path / "bench_main"
+    lib_dir = os.path.dirname(rt.SO_PATH)
+    cuda = os.environ.get("CUDA_HOME", "/usr/local/cuda")
+    subprocess.run(["g++", "-std=c++17", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"), "-I", os.path.join(cuda, "include"),
+                    os.path.join(ROOT, "tools", "cpp", "bench_main.cpp"), "-o", str(exe), rt.SO_PATH,
+                    "-L", os.path.join(cuda, "lib64"), "-lcudart", f"-Wl,-rpath,{lib_dir}", f"-Wl,-rpath,{os.path.join(cuda, 'lib64')}"],
+                   check=True)
+    res = subprocess.run([str(exe), "cornell", "64", "64", "1"], capture_output=True, text=True)
+    assert res.returncode == 0, res.stdout + res.stderr
+    out = json.loads(res.stdout)
+    assert out.get("error") == "no CUDA device" or out["n_tris"] == 1024
+
+
 def _grid_plane(k=8):
     """[0,1]^2 at z = 0 as k x k x 2 triangles on exact binary fractions."""
     t = []

@@ -488,6 +488,33 @@ def test_c99_program_runs_on_the_device(rt, tmp_path):
     assert res.returncode == 0 and res.stdout.strip() == "ok", res.stdout + res.stderr
 
 
+def test_cpp_bench_main_gives_the_python_paths_hits(rt, tmp_path):
+    """tools/cpp/bench_main.cpp (SURVEY.md §8b "a small C++ bench main"): no Python, no PyTorch,
+    cudaMalloc'd buffers -> rt_gen_scene / build_bvh / trace_rays.  Same camera, same hit bytes."""
+    exe = tmp_path / "bench_main"
+    lib_dir = os.path.dirname(rt.SO_PATH)
+    cuda = os.environ.get("CUDA_HOME", "/usr/local/cuda")
+    subprocess.run(["g++", "-std=c++17", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"), "-I", os.path.join(cuda, "include"),
+                    os.path.join(ROOT, "tools", "cpp", "bench_main.cpp"), "-o", str(exe), rt.SO_PATH,
+                    "-L", os.path.join(cuda, "lib64"), "-lcudart", f"-Wl,-rpath,{lib_dir}", f"-Wl,-rpath,{os.path.join(cuda, 'lib64')}"],
+                   check=True)
+    w, h = 320, 200
+    cam = rt.camera.cornell_camera(w, h)
+    res = subprocess.run([str(exe), "cornell", str(w), str(h), "2", "cam=" + ",".join(repr(float(v)) for v in cam)],
+                         capture_output=True, text=True)
+    assert res.returncode == 0, res.stdout + res.stderr
+    out = json.loads(res.stdout)
+    with rt.Bvh.build(rt.gen_scene(rt.RT_SCENE_CORNELL)) as gb:
+        hits = gb.trace(rt.gen_primary_rays(cam, w, h)).cpu().numpy()
+    fnv = 1469598103934665603
+    for b in hits.tobytes():
+        fnv = ((fnv ^ b) * 1099511628211) & 0xFFFFFFFFFFFFFFFF
+    assert out["n_tris"] == 1024 and out["n_rays"] == w * h and out["host_path_equal"] is True
+    assert out["hits"] == int((hits.view(np.int32)[:, 3] >= 0).sum()) > 0
+    assert out["hits_fnv1a"] == f"{fnv:016x}"
+    assert out["build_ms"] > 0 and out["trace_ms"] > 0 and out["kernel_launches"] > 10
+
+
 # ---- sharded BUILD (§8f.4) -------------------------------------------------------------------------------
 @pytest.mark.parametrize("parts", [1, 2, 3, 5])
 def test_sharded_build_merges_to_the_single_bvh(rt, oracle, parts):
