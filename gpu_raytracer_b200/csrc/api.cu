@@ -1650,6 +1650,7 @@ extern "C" int rt_set_param(const char* name, int64_t value) {
   else if (!strcmp(name, "build.walk")) g_build_walk_shape = (int)value;
   else if (!strcmp(name, "render.band")) p.render_band = (int)value;
   else if (!strcmp(name, "render.taper")) p.render_taper = (int)value;
+  else if (!strcmp(name, "merge.fused")) p.merge_fused = (int)value;
   else if (!strcmp(name, "pool.keep_mb")) {
     p.pool_keep_mb = (int)value;
     std::lock_guard<std::mutex> lock(g_pool_mu);

@@ -293,6 +293,7 @@ struct Params {
   Knob stage_chunk{0};          // rays per staged chunk (0 = 1M)
   Knob streamed{1};             // 1 = pinned host batches go through the single-launch streamed mode
   Knob render_band{0};          // rt_render_ao: log2 of the rays per band (16..20); 0 = 20
+  Knob merge_fused{1};          // trace_rays_merged: 1 = every device merges its slice out of peer memory, 0 = gather on the first device
   Knob render_taper{3};         // rt_render_ao: bit 0 = the first two bands are 1/4 and 1/2 of a band, bit 1 = the last two
   Knob pool_keep_mb{0};         // build/trace temporaries kept cached per device after a call; 0 = all
 };

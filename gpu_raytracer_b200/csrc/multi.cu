@@ -59,6 +59,12 @@ int for_each_device(int n, Fn fn) {
   return RT_OK;
 }
 
+template <typename Fn, typename Pre>
+int for_each_device(int n, Fn fn, Pre pre) {  // pre(i) runs for every slot on the calling thread first
+  for (int i = 0; i < n; ++i) RT_TRY(pre(i));
+  return for_each_device(n, fn);
+}
+
 // lets `device` read memory of the library's pool on `owner` directly (peer copies then go
 // over NVLink instead of bouncing through the host); failure only costs bandwidth
 void allow_peer(int owner, int device) {
@@ -375,6 +381,44 @@ extern "C" int build_bvh_sharded(const float* tris, uint64_t n_tris, const rt_bu
   return RT_OK;
 }
 
+namespace {
+
+// device buffers of several devices that do not outlive an early return
+struct PartBuffers {
+  std::vector<std::pair<int, void*>> held;  // (device, pointer)
+  int alloc(int device, void** out, size_t bytes, cudaStream_t s) {
+    RT_TRY(pool_alloc(out, bytes, s));  // the caller has made `device` current
+    held.emplace_back(device, *out);
+    return 0;
+  }
+  ~PartBuffers() {
+    int prev = -1;
+    cudaGetDevice(&prev);
+    for (auto& e : held) {
+      cudaSetDevice(e.first);
+      cudaFreeAsync(e.second, 0);
+    }
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+
+// can every device of the list read every other one's memory directly?
+bool all_peers(rt_bvh* const* handles, int n) {
+  for (int i = 0; i < n; ++i)
+    for (int j = 0; j < n; ++j) {
+      const int a = handles[i]->device, b = handles[j]->device;
+      if (a == b) continue;
+      int can = 0;
+      if (cudaDeviceCanAccessPeer(&can, a, b) != cudaSuccess || !can) {
+        cudaGetLastError();
+        return false;
+      }
+    }
+  return true;
+}
+
+}  // namespace
+
 extern "C" int trace_rays_merged(rt_bvh* const* handles, const uint32_t* prim_base, int n_devices,
                                  const float* rays, uint64_t n_rays, uint32_t flags, float* hits) {
   if (!handles || n_devices <= 0 || n_devices > kMaxParts)
@@ -388,8 +432,76 @@ extern "C" int trace_rays_merged(rt_bvh* const* handles, const uint32_t* prim_ba
     return fail(RT_ERR_INVALID, "trace_rays_merged: rays and hits are host buffers");
   const int dev0 = handles[0]->device;
   const uint64_t kBatch = 1ull << 22;  // rays per round: 128 MiB up, 64 MiB of hits per part
+  // With peer access between all the devices nothing crosses PCIe twice and nothing is staged:
+  // device j owns slice j of the batch (rt_shard_range).  It uploads that slice of the rays, all
+  // devices pull each other's slices over NVLink (an all-gather over peer memory), every part
+  // traces the whole batch, and device j's merge kernel LOADS the candidates of its slice from
+  // every part's memory (a reduce-scatter by (t, prim) over peer memory, exchange and merge in one
+  // kernel), then sends its slice to the host over its own PCIe link.
+  // Without peer access: the parts' hits are copied to the first device and merged there.
+  const bool fused = all_peers(handles, n_devices) && params().merge_fused != 0;
+  if (fused)
+    for (int i = 0; i < n_devices; ++i)
+      for (int j = 0; j < n_devices; ++j) allow_peer(handles[i]->device, handles[j]->device);
   for (uint64_t first = 0; first < n_rays; first += kBatch) {
     const uint64_t cnt = n_rays - first < kBatch ? n_rays - first : kBatch;
+    if (fused) {
+      PartBuffers bufs;
+      float4* part_hits[kMaxParts] = {};
+      float4* part_rays[kMaxParts] = {};
+      uint64_t sf[kMaxParts], sc[kMaxParts];  // slice j of the batch
+      for (int j = 0; j < n_devices; ++j) RT_TRY(rt_shard_range(cnt, j, n_devices, &sf[j], &sc[j]));
+      // phase 0: device i takes slice i of the rays from the host (1/n of the batch over its own
+      // PCIe link, not the whole batch over every link)
+      RT_TRY(for_each_device(n_devices, [&](int i) -> int {
+        if (sc[i] == 0) return 0;
+        DeviceScope scope;
+        RT_TRY(scope.enter(handles[i]->device));
+        RT_CUDA(cudaMemcpyAsync(part_rays[i] + 2 * sf[i], rays + 8 * (first + sf[i]), sc[i] * 32, cudaMemcpyHostToDevice, 0));
+        RT_CUDA(cudaStreamSynchronize(0));
+        return 0;
+      }, [&](int i) -> int {  // before the threads start: the buffers (PartBuffers is not thread-safe)
+        DeviceScope scope;
+        RT_TRY(scope.enter(handles[i]->device));
+        RT_TRY(bufs.alloc(handles[i]->device, (void**)&part_hits[i], cnt * 16, 0));
+        RT_TRY(bufs.alloc(handles[i]->device, (void**)&part_rays[i], cnt * 32, 0));
+        RT_CUDA(cudaStreamSynchronize(0));
+        return 0;
+      }));
+      // phase 1: every part pulls the other slices from their owners (NVLink: an all-gather over
+      // peer memory) and traces the whole batch into its own memory
+      RT_TRY(for_each_device(n_devices, [&](int i) -> int {
+        const rt_bvh* h = handles[i];
+        DeviceScope scope;
+        RT_TRY(scope.enter(h->device));
+        cudaStream_t s = 0;
+        for (int k = 0; k < n_devices; ++k)
+          if (k != i && sc[k] != 0)
+            RT_CUDA(cudaMemcpyPeerAsync(part_rays[i] + 2 * sf[k], h->device, part_rays[k] + 2 * sf[k],
+                                        handles[k]->device, sc[k] * 32, s));
+        RT_TRY(trace_device(h, part_rays[i], cnt, flags, part_hits[i], s));
+        RT_CUDA(cudaStreamSynchronize(s));
+        return 0;
+      }));
+      // phase 2: device j merges slice j out of everybody's memory and sends it down
+      RT_TRY(for_each_device(n_devices, [&](int j) -> int {
+        const uint64_t f = sf[j], c = sc[j];
+        if (c == 0) return 0;
+        DeviceScope scope;
+        RT_TRY(scope.enter(handles[j]->device));
+        cudaStream_t s = 0;
+        TempPool tmp(s);
+        float4* merged = nullptr;
+        RT_TRY(tmp.alloc((void**)&merged, c * 16));
+        const float* parts[kMaxParts];
+        for (int k = 0; k < n_devices; ++k) parts[k] = reinterpret_cast<const float*>(part_hits[k] + f);
+        RT_TRY(rt_merge_hits(parts, prim_base, n_devices, c, flags, reinterpret_cast<float*>(merged), s));
+        RT_CUDA(cudaMemcpyAsync(hits + 4 * (first + f), merged, c * 16, cudaMemcpyDeviceToHost, s));
+        RT_CUDA(cudaStreamSynchronize(s));
+        return 0;
+      }));
+      continue;
+    }
     // the parts' hits, gathered on the first handle's device
     DeviceScope scope0;
     RT_TRY(scope0.enter(dev0));

@@ -357,7 +357,9 @@ RT_API int rt_trim(int device);
  * "trace.variant", "trace.blocks_per_sm", "trace.chunk", "trace.refill_min", "trace.leaf_min",
  * "trace.wide", "trace.compact" (0 = ignore a handle's 32-byte nodes), "wide.leaf_max", "trace.streamed" (0 = always stage host batches),
  * "trace.stage_chunk", "trace.zero_copy", "render.band" (rt_render_ao: log2 of the rays per band,
- * 16..20; 0, the default, = 20), "render.taper" (bit 0: the frame's first two bands are a quarter and
+ * 16..20; 0, the default, = 20), "merge.fused" (trace_rays_merged: 1, the default, = with peer access every device merges its slice of
+ * the batch straight out of the other devices' memory; 0 = the parts' hits are copied to the first device),
+ * "render.taper" (bit 0: the frame's first two bands are a quarter and
  * a half band, bit 1: so are its last two; default 3), "trace.sh_stack" (0 | 8 | 16 | 24 stack levels in
  * shared memory; -1, the default: 8 for RT_TRACE_REORDER launches, else 0), "build.pdl" (1 = build kernels launched as programmatic dependents, the
  * default), "sort.hybrid" (63-bit builds: 1 = packed passes on the top 30 bits, then ranks inside

@@ -536,8 +536,15 @@ def test_sharded_build_merges_to_the_single_bvh(rt, oracle, parts):
         assert sum(h.n_tris for h in sb.handles) == ob.n
         for flags in (0, rt.RT_TRACE_ANY, rt.RT_TRACE_WATERTIGHT):
             want = ob.trace(rays, flags)
-            got = sb.trace(rays, flags)
-            assert np.array_equal(bits(got), bits(want)), (parts, flags)
+            # fused: every device merges its slice of the batch out of the parts' (peer) memory;
+            # 0: the parts' hits are copied to the first device and merged there
+            for fused in (1, 0):
+                rt.set_param("merge.fused", fused)
+                try:
+                    got = sb.trace(rays, flags)
+                finally:
+                    rt.set_param("merge.fused", 1)
+                assert np.array_equal(bits(got), bits(want)), (parts, flags, fused)
         # the exchange step alone: device hits of every part, merged by the kernel == numpy statement
         d_rays = dev(rays)
         local = [h.trace(d_rays) for h in sb.handles if h.info().device == 0]
