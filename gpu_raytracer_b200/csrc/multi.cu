@@ -104,6 +104,49 @@ int check_devices(const int* devices, int n_devices, const char* who) {
 
 }  // namespace
 
+namespace {
+
+// device buffers of several devices that do not outlive an early return
+struct PartBuffers {
+  std::vector<std::pair<int, void*>> held;  // (device, pointer)
+  int alloc(int device, void** out, size_t bytes, cudaStream_t s) {
+    RT_TRY(pool_alloc(out, bytes, s));  // the caller has made `device` current
+    held.emplace_back(device, *out);
+    return 0;
+  }
+  ~PartBuffers() {
+    int prev = -1;
+    cudaGetDevice(&prev);
+    for (auto& e : held) {
+      cudaSetDevice(e.first);
+      cudaFreeAsync(e.second, 0);
+    }
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+
+// can every device of the list read every other one's memory directly?
+bool all_peers(const int* devices, int n) {
+  for (int i = 0; i < n; ++i)
+    for (int j = 0; j < n; ++j) {
+      const int a = devices[i], b = devices[j];
+      if (a == b) continue;
+      int can = 0;
+      if (cudaDeviceCanAccessPeer(&can, a, b) != cudaSuccess || !can) {
+        cudaGetLastError();
+        return false;
+      }
+    }
+  return true;
+}
+bool all_peers(rt_bvh* const* handles, int n) {
+  std::vector<int> d((size_t)n);
+  for (int i = 0; i < n; ++i) d[(size_t)i] = handles[i]->device;
+  return all_peers(d.data(), n);
+}
+
+}  // namespace
+
 extern "C" int build_bvh_multi(const float* tris, uint64_t n_tris, const rt_build_opts* opts,
                                const int* devices, int n_devices, int strategy, rt_bvh** out) {
   if (!out) return fail(RT_ERR_INVALID, "build_bvh_multi: out is NULL");
@@ -142,7 +185,44 @@ extern "C" int build_bvh_multi(const float* tris, uint64_t n_tris, const rt_buil
   };
 
   int rc;
-  if (strategy == RT_MULTI_REDUNDANT || n_devices == 1) {
+  if (strategy == RT_MULTI_REDUNDANT && n_devices > 1 && !tris_on_device && n_tris >= (1ull << 16) &&
+      all_peers(devices, n_devices) && params().merge_fused != 0) {
+    // host triangles, devices that see each other: every device takes 1/n of the array over its
+    // own PCIe link and pulls the rest from its peers over NVLink (an all-gather over peer
+    // memory), then builds from its device copy.  The array crosses PCIe once, not n times.
+    PartBuffers bufs;
+    std::vector<float*> d_tris((size_t)n_devices, nullptr);
+    auto lo = [&](int i) { return n_tris * (uint64_t)i / (uint64_t)n_devices; };
+    for (int i = 0; i < n_devices; ++i)
+      for (int j = 0; j < n_devices; ++j) allow_peer(devices[i], devices[j]);
+    rc = for_each_device(n_devices, [&](int i) -> int {
+      DeviceScope scope;
+      RT_TRY(scope.enter(devices[i]));
+      const uint64_t f = lo(i), c = lo(i + 1) - f;
+      if (c) RT_CUDA(cudaMemcpyAsync(d_tris[(size_t)i] + 12 * f, tris + 12 * f, c * 48, cudaMemcpyHostToDevice, 0));
+      RT_CUDA(cudaStreamSynchronize(0));
+      return 0;
+    }, [&](int i) -> int {
+      DeviceScope scope;
+      RT_TRY(scope.enter(devices[i]));
+      RT_TRY(bufs.alloc(devices[i], (void**)&d_tris[(size_t)i], n_tris * 48, 0));
+      RT_CUDA(cudaStreamSynchronize(0));
+      return 0;
+    });
+    if (rc == 0)
+      rc = for_each_device(n_devices, [&](int i) -> int {
+        DeviceScope scope;
+        RT_TRY(scope.enter(devices[i]));
+        for (int k = 0; k < n_devices; ++k) {
+          const uint64_t f = lo(k), c = lo(k + 1) - f;
+          if (k != i && c)
+            RT_CUDA(cudaMemcpyPeerAsync(d_tris[(size_t)i] + 12 * f, devices[i], d_tris[(size_t)k] + 12 * f, devices[k],
+                                        c * 48, 0));
+        }
+        RT_CUDA(cudaStreamSynchronize(0));
+        return build_on(i, d_tris[(size_t)i]);
+      });
+  } else if (strategy == RT_MULTI_REDUNDANT || n_devices == 1) {
     rc = for_each_device(n_devices, build_from_peer);
   } else {
     rc = build_from_peer(0);
@@ -380,44 +460,6 @@ extern "C" int build_bvh_sharded(const float* tris, uint64_t n_tris, const rt_bu
   }
   return RT_OK;
 }
-
-namespace {
-
-// device buffers of several devices that do not outlive an early return
-struct PartBuffers {
-  std::vector<std::pair<int, void*>> held;  // (device, pointer)
-  int alloc(int device, void** out, size_t bytes, cudaStream_t s) {
-    RT_TRY(pool_alloc(out, bytes, s));  // the caller has made `device` current
-    held.emplace_back(device, *out);
-    return 0;
-  }
-  ~PartBuffers() {
-    int prev = -1;
-    cudaGetDevice(&prev);
-    for (auto& e : held) {
-      cudaSetDevice(e.first);
-      cudaFreeAsync(e.second, 0);
-    }
-    if (prev >= 0) cudaSetDevice(prev);
-  }
-};
-
-// can every device of the list read every other one's memory directly?
-bool all_peers(rt_bvh* const* handles, int n) {
-  for (int i = 0; i < n; ++i)
-    for (int j = 0; j < n; ++j) {
-      const int a = handles[i]->device, b = handles[j]->device;
-      if (a == b) continue;
-      int can = 0;
-      if (cudaDeviceCanAccessPeer(&can, a, b) != cudaSuccess || !can) {
-        cudaGetLastError();
-        return false;
-      }
-    }
-  return true;
-}
-
-}  // namespace
 
 extern "C" int trace_rays_merged(rt_bvh* const* handles, const uint32_t* prim_base, int n_devices,
                                  const float* rays, uint64_t n_rays, uint32_t flags, float* hits) {

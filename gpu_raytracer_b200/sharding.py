@@ -69,6 +69,38 @@ def broadcast_bvh(bvh, src: int = 0, group=None):
     return bvh
 
 
+def upload_scene(host_tris, rank: int, world: int, group=None, device=None):
+    """The whole triangle array [n, 12] on every rank's device, with the array crossing PCIe ONCE
+    in total: every rank uploads rows ``tri_range(n, rank, world)`` of the (identical) host array
+    and one all-gather (NCCL over NVLink on GPUs; gloo on CPU tensors in the tests) hands every
+    rank the rest.  Against every rank uploading everything, the ranks of one host stop competing
+    for its PCIe bandwidth (8 x 479 MB at 10M triangles).  Returns a tensor on ``device``."""
+    import torch
+    import torch.distributed as dist
+
+    n = int(host_tris.shape[0])
+    device = torch.device(device if device is not None else ("cuda" if torch.cuda.is_available() else "cpu"))
+    if world == 1:
+        return host_tris.to(device, non_blocking=True)
+    counts = [n * (r + 1) // world - n * r // world for r in range(world)]
+    first = n * rank // world
+    full = torch.empty((n, 12), dtype=torch.float32, device=device)
+    mine = host_tris[first:first + counts[rank]].to(device, non_blocking=True)
+    if len(set(counts)) == 1:
+        dist.all_gather_into_tensor(full, mine.contiguous(), group=group)
+    else:  # ragged: equal-size padded pieces, trimmed into place
+        mx = max(counts)
+        pad = torch.zeros((mx, 12), dtype=torch.float32, device=device)
+        pad[:counts[rank]] = mine
+        pieces = [torch.empty_like(pad) for _ in range(world)]
+        dist.all_gather(pieces, pad, group=group)
+        at = 0
+        for r in range(world):
+            full[at:at + counts[r]] = pieces[r][:counts[r]]
+            at += counts[r]
+    return full
+
+
 def trace_sharded(trace_fn: Callable, make_rays: Callable, n_rays: int, rank: int, world: int,
                   batch: Optional[int] = None):
     """Traces this rank's range of a global batch of ``n_rays`` rays.

@@ -109,6 +109,31 @@ def test_sharded_scene_two_ranks_equal_one_bvh(tmp_path, oracle):
     assert [sharding.tri_range(10, r, 3) for r in range(3)] == [(0, 3), (3, 3), (6, 4)]
 
 
+# ---- the scene crosses PCIe once: every rank uploads 1/world of it, one all-gather ----------------
+def _upload_worker(rank, world, port, n_tris, out_dir):
+    sys.path.insert(0, ROOT)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import torch
+        import oracle as O
+        from gpu_raytracer_b200 import sharding
+        tris = torch.from_numpy(O.gen_scene(O.SCENE_SOUP, n_tris, 0, seed=1))
+        full = sharding.upload_scene(tris, rank, world, device="cpu")
+        np.save(os.path.join(out_dir, f"t{n_tris}_{rank}.npy"), full.numpy())
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("n_tris", [4000, 4001])     # equal shares, ragged shares
+def test_upload_scene_gathers_the_whole_array_on_every_rank(tmp_path, oracle, n_tris):
+    mp.spawn(_upload_worker, args=(2, _free_port(), n_tris, str(tmp_path)), nprocs=2, join=True)
+    want = oracle.gen_scene(oracle.SCENE_SOUP, n_tris, 0, seed=1)
+    for r in range(2):
+        got = np.load(str(tmp_path / f"t{n_tris}_{r}.npy"))
+        assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), r
+
+
 def test_merge_of_parts_equals_the_whole(oracle):
     """The property the sharded build rests on: a ray's hit is min over ALL triangles by (t, prim),
     so the parts of any partition of the triangle array merge to the single-BVH hits exactly."""

@@ -37,4 +37,17 @@ with g.ShardedBvh.build(tris, list(range(n_dev))) as sb:
         print(json.dumps({"n_gpus": n_dev, "n_rays": n_rays, "fused": fused, "ms": min(ts[1:]) * 1e3,
                           "mrays_s": n_rays / min(ts[1:]) / 1e6,
                           "equal": bool(torch.equal(ref.view(torch.int32), hits.view(torch.int32)))}), flush=True)
+# build_bvh_multi, redundant strategy, pinned host triangles: every device uploads the whole
+# array (0) against 1/n each + an all-gather over peer memory (1)
+h_tris = torch.from_numpy(tris).pin_memory()
+for fused in (1, 0, 1, 0):
+    g.set_param("merge.fused", fused)
+    ts = []
+    for _ in range(4):
+        t0 = time.perf_counter()
+        mb = g.MultiBvh.build(h_tris, list(range(n_dev)))
+        ts.append(time.perf_counter() - t0)
+        mb.close()
+    print(json.dumps({"n_gpus": n_dev, "call": "build_bvh_multi (redundant, host triangles)", "n_tris": int(tris.shape[0]),
+                      "fused": fused, "ms": min(ts[1:]) * 1e3}), flush=True)
 g.set_param("merge.fused", 1)
