@@ -104,3 +104,22 @@ def test_every_layout_equals_brute_force(rt, oracle, seed):
                 assert np.array_equal(bits(got), bits(want[0])), (seed, key_bits, layout, "reorder")
     got = rt.Bvh.build(tris).trace(rays)                    # host buffers
     assert np.array_equal(bits(np.asarray(got)), bits(want[0]))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("seed", SEEDS)
+def test_degenerate_scenes_build_the_oracles_tree(rt, oracle, seed):
+    """keys, order (duplicates and equal centroids: ties by index), topology and boxes of the
+    fuzz scenes, both key widths, byte for byte"""
+    _, tris = fuzz_scene(seed)
+    for key_bits in (30, 63):
+        ob = oracle.OracleBvh(tris, key_bits)
+        with rt.Bvh.build(dev(tris), key_bits=key_bits, keep_keys=True) as gb:
+            keys, idx = gb.read_sorted()
+            left, right, parent = gb.read_topology()
+            boxes = gb.read_boxes()
+            assert np.array_equal(bits(gb.bounds), bits(ob.bounds))
+        assert np.array_equal(keys, ob.keys) and np.array_equal(idx, ob.idx), (seed, key_bits)
+        assert np.array_equal(left, ob.left) and np.array_equal(right, ob.right) and np.array_equal(parent, ob.parent)
+        assert np.array_equal(bits(boxes), bits(ob.boxes)), (seed, key_bits)
+        ob.close()
