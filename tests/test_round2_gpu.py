@@ -478,6 +478,32 @@ def test_knobs_may_change_while_other_threads_trace(rt, oracle):
     ob.close()
 
 
+def test_frames_rendered_from_several_host_threads_at_once(rt):
+    """rt_render_ao keeps its streams, slots and counters per host thread: four threads render
+    different frames against one handle at the same time (pinned host buffers, compact nodes in
+    two of them), each gets the bytes of its own sequential frame."""
+    d_tris = rt.gen_scene(rt.RT_SCENE_SPHEREFLAKE, 3, 4, 0)
+    w, h, spp = 1280, 900, 2                                   # 1.15M rays: several bands
+    with rt.Bvh.build(d_tris, compact=True) as gb:
+        radius = float(np.float32(0.05) * np.float32(np.linalg.norm(gb.bounds[3:] - gb.bounds[:3])))
+        cams = [rt.camera.frame_box(gb.bounds, w, h, direction=d) for d in ((0.3, 0.25, -1.0), (1.0, 0.2, 0.1), (-0.5, 0.8, 0.4), (0.0, -1.0, 0.2))]
+        rays = [rt.gen_primary_rays(c, w, h).cpu().pin_memory() for c in cams]
+        want = [gb.render_ao(d_tris, r, spp, 11 + k, radius) for k, r in enumerate(rays)]
+        want = [(a.clone(), b.clone()) for a, b in want]
+        got = [None] * 4
+
+        def work(k):
+            for _ in range(5):
+                got[k] = gb.render_ao(d_tris, rays[k], spp, 11 + k, radius)
+        ts = [threading.Thread(target=work, args=(k,)) for k in range(4)]
+        [t.start() for t in ts]
+        [t.join() for t in ts]
+        for k in range(4):
+            assert torch.equal(got[k][0].view(torch.int32), want[k][0].view(torch.int32)), k
+            assert torch.equal(got[k][1].view(torch.int32), want[k][1].view(torch.int32)), k
+        assert (rt.hit_prims(want[0][0]) >= 0).float().mean() > 0.05
+
+
 def test_c99_program_runs_on_the_device(rt, tmp_path):
     exe = tmp_path / "smoke"
     lib_dir = os.path.dirname(rt.SO_PATH)
