@@ -23,6 +23,10 @@
  *     given; calls are synchronous on return unless named *_async.
  *   - there is no CPU fallback: without a CUDA device every compute call fails
  *     with RT_ERR_NO_DEVICE.
+ *   - threads: calls that take a `const rt_bvh*` (trace_rays, trace_camera, rt_render_ao,
+ *     the readers) may run on one handle from several host threads at once; calls that take
+ *     an `rt_bvh*` (refit_bvh, bvh_widen, bvh_widen8, bvh_compact, bvh_commit, free_bvh)
+ *     change the handle and need it to themselves.  build_bvh calls are independent.
  *
  * Data layouts
  *   triangle  12 floats  v0.xyz,_, v1.xyz,_, v2.xyz,_      (3 x float4, w ignored)
