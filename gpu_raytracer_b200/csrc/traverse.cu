@@ -177,8 +177,9 @@ trace_kernel_dyn(const Node* __restrict__ nodes, const SortedTri* __restrict__ s
   // Compact layout: what only the leaf test and the retire need (direction, barycentrics, the
   // ray's index) waits in shared memory too; the per-ray plane constants take its registers
   // (62 -> 24 bytes of spills at 48 registers; measured -2 % on frames, -5..-9 % on incoherent
-  // and reordered rays; the same parking costs the 64-byte kernel 1-5 %, which has no spills to save)
-  constexpr bool PARK = RT_TRACE_PARK && Q && !PIPE && !WT && !STATS;
+  // and reordered rays; the same parking costs the plain 64-byte kernel 1-5 %, which has no spills
+  // to save, and gains its RT_TRACE_REORDER variant (stack top in shared memory, 16 bytes of spills) 2.7 %)
+  constexpr bool PARK = RT_TRACE_PARK && (Q || SHS > 0) && !PIPE && !WT && !STATS;
   __shared__ float sh_park[PARK ? 5 : 1][kTraceThreads];
   __shared__ unsigned long long sh_idx[PARK ? kTraceThreads : 1];
   int stack[kStack - SHS];
