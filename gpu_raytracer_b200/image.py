@@ -1,5 +1,9 @@
-"""Image output: float RGB → binary PPM, no dependencies."""
+"""Image output (SURVEY.md §8f.1 "PPM/PNG writer"): float RGB → binary PPM or PNG; numpy and the
+standard library only."""
 from __future__ import annotations
+
+import struct
+import zlib
 
 import numpy as np
 
@@ -23,3 +27,20 @@ def write_ppm(path: str, rgb, width: int, height: int) -> None:
     with open(path, "wb") as f:
         f.write(f"P6\n{width} {height}\n255\n".encode())
         f.write(a.tobytes())
+
+
+def write_png(path: str, rgb, width: int, height: int, level: int = 6) -> None:
+    """The same pixels as write_ppm in an 8-bit RGB PNG (filter type 0 rows, one IDAT chunk)."""
+    if hasattr(rgb, "detach"):
+        rgb = rgb.detach().cpu().numpy()
+    a = quantize(np.asarray(rgb, dtype=np.float32).reshape(height, width, 3))
+    rows = np.concatenate([np.zeros((height, 1), dtype=np.uint8), a.reshape(height, width * 3)], axis=1)
+
+    def chunk(tag: bytes, data: bytes) -> bytes:
+        return struct.pack(">I", len(data)) + tag + data + struct.pack(">I", zlib.crc32(tag + data) & 0xFFFFFFFF)
+
+    with open(path, "wb") as f:
+        f.write(b"\x89PNG\r\n\x1a\n")
+        f.write(chunk(b"IHDR", struct.pack(">IIBBBBB", width, height, 8, 2, 0, 0, 0)))
+        f.write(chunk(b"IDAT", zlib.compress(rows.tobytes(), level)))
+        f.write(chunk(b"IEND", b""))

@@ -59,6 +59,38 @@ def test_write_ppm_golden_frame(rt, oracle, tmp_path):
     assert (px[..., 0] == px[..., 1]).all() and px.max() > 200 and (px == 0).any()
 
 
+def test_write_png_holds_the_ppm_pixels(rt, tmp_path):
+    """image.write_png: a valid 8-bit RGB PNG (signature, IHDR, CRCs) whose decoded pixels are
+    write_ppm's; checked with the standard library, and with Pillow where it is installed."""
+    import struct
+    import zlib
+    rng = np.random.default_rng(3)
+    w, h = 37, 21
+    rgb = rng.random((w * h, 3)).astype(np.float32) * 1.2 - 0.1
+    rt.image.write_ppm(str(tmp_path / "a.ppm"), rgb, w, h)
+    rt.image.write_png(str(tmp_path / "a.png"), rgb, w, h)
+    ppm = (tmp_path / "a.ppm").read_bytes()
+    want = np.frombuffer(ppm[len(f"P6\n{w} {h}\n255\n"):], dtype=np.uint8).reshape(h, w, 3)
+    data = (tmp_path / "a.png").read_bytes()
+    assert data[:8] == b"\x89PNG\r\n\x1a\n"
+    at, chunks = 8, []
+    while at < len(data):
+        (n,) = struct.unpack(">I", data[at:at + 4])
+        tag, body = data[at + 4:at + 8], data[at + 8:at + 8 + n]
+        assert struct.unpack(">I", data[at + 8 + n:at + 12 + n])[0] == zlib.crc32(tag + body) & 0xFFFFFFFF
+        chunks.append((tag, body))
+        at += 12 + n
+    assert [t for t, _ in chunks] == [b"IHDR", b"IDAT", b"IEND"]
+    assert struct.unpack(">IIBBBBB", chunks[0][1]) == (w, h, 8, 2, 0, 0, 0)
+    rows = np.frombuffer(zlib.decompress(chunks[1][1]), dtype=np.uint8).reshape(h, 1 + 3 * w)
+    assert (rows[:, 0] == 0).all() and np.array_equal(rows[:, 1:].reshape(h, w, 3), want)
+    try:
+        from PIL import Image
+    except ImportError:
+        return
+    assert np.array_equal(np.asarray(Image.open(str(tmp_path / "a.png")).convert("RGB")), want)
+
+
 def test_header_compiles_and_links_as_c99(rt, tmp_path):
     """include/gpu_raytracer.h is a C header: a C99 translation unit includes it, links against
     the library and drives build_bvh / trace_rays / free_bvh (tests/c99/smoke.c)."""

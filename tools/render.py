@@ -1,7 +1,8 @@
-"""Renders a scene to a PPM file through the public API: build_bvh,
-primary rays, 4 ambient-occlusion rays per pixel, rt_shade, image.write_ppm.
+"""Renders a scene to a PPM or PNG file (by the name's ending) through the public API (SURVEY.md
+§8f.1): build_bvh, then the whole frame in one call (rt_render_ao: primary rays, 4 ambient-occlusion
+rays per pixel, shading), image.write_ppm / write_png.
 
-  python tools/render.py cornell|soup1m|flake10m|<file.obj>|<file.tri> [out.ppm] [width height]
+  python tools/render.py cornell|soup1m|flake10m|<file.obj>|<file.tri> [out.ppm|out.png] [width height]
 """
 import os
 import sys
@@ -37,15 +38,12 @@ def main():
         if cam is None:
             cam = g.camera.frame_box(box, w, h)
         rays = g.gen_primary_rays(cam, w, h)
-        hits = bvh.trace(rays)
-        radius = 0.05 * float(np.linalg.norm(box[3:] - box[:3]))
-        ao = g.gen_ao_rays(tris, rays, hits, 4, 2, radius)
-        occ = bvh.trace(ao, g.RT_TRACE_ANY)
-        rgb = g.shade(tris, rays, hits, occ, 4)
+        radius = float(np.float32(0.05) * np.float32(np.linalg.norm(box[3:] - box[:3])))
+        hits, rgb = bvh.render_ao(tris, rays, 4, 2, radius)
     torch.cuda.synchronize()
     dt = time.perf_counter() - t0
     os.makedirs(os.path.dirname(os.path.abspath(out)), exist_ok=True)
-    g.image.write_ppm(out, rgb, w, h)
+    (g.image.write_png if out.lower().endswith(".png") else g.image.write_ppm)(out, rgb, w, h)
     cover = float((g.hit_prims(hits) >= 0).float().mean())
     print(f"{what}: {tris.shape[0]} triangles, {w}x{h}, coverage {cover:.3f}, "
           f"build+trace+shade {dt * 1e3:.1f} ms -> {out}")
