@@ -547,7 +547,7 @@ def run_ours(args):
     Ke = max(3, min(K, 10))
     s_down = torch.cuda.Stream()
     ev_hits = torch.cuda.Event()
-    eb = et = ec = es = 0.0
+    eb = et = ec = es = eca = 0.0
     d_rgb = None
     one_call_rgb = None
     for it in range(2 + Ke):
@@ -590,15 +590,20 @@ def run_ours(args):
             h_rgb.copy_(d_rgb, non_blocking=True)
             torch.cuda.synchronize()
         t4 = time.perf_counter()
+        if wl.ao_spp:
+            # and from the camera alone: primary rays made on the device, hits + frame down
+            bvh.render_camera_ao(d_tris, cam, wl.width, wl.height, wl.ao_spp, wl.ao_seed, radius, hits=h_hits, rgb=h_rgb)
+        t5 = time.perf_counter()
         bvh.close()
         if it >= 2:
             eb, et, ec, es = eb + (t1 - t0), et + (t2 - t1), ec + (t3 - t2), es + (t4 - t3)
+            eca += t5 - t4
     e2e_ok = bool(torch.equal(h_hits.view(torch.int32), hits.cpu().view(torch.int32)))  # bit compare: miss prim = -1 is a NaN pattern
     if one_call_rgb is not None:                                # rt_render_ao's frame == the separate calls' frame
         e2e_ok = e2e_ok and bool(torch.equal(one_call_rgb.view(torch.int32), h_rgb.view(torch.int32)))
     del h_tris, h_rays
 
-    build_ms, trace_ms, ao_ms, wall, eb, et, ec, es = max_over_ranks([build_ms, trace_ms, ao_ms, wall, eb, et, ec, es])
+    build_ms, trace_ms, ao_ms, wall, eb, et, ec, es, eca = max_over_ranks([build_ms, trace_ms, ao_ms, wall, eb, et, ec, es, eca])
 
     # ---- sub-records: config 5 at every N (strong scaling), config 4 at N = 1 ----
     configs = {}
@@ -735,7 +740,11 @@ def run_ours(args):
                                    if wl.ao_spp else None),
                 "camera": {"mrays_s": count * world * Ke / ec / 1e6, "ms": ec / Ke * 1e3,
                            "h2d_bytes": 48, "d2h_bytes": int(count * 16),
-                           "note": "trace_camera: primary rays generated on the device, hits to pinned host"},
+                           "note": "trace_camera: primary rays generated on the device, hits to pinned host",
+                           "frame": ({"mrays_s": e2e_rays * world * Ke / eca / 1e6, "ms": eca / Ke * 1e3,
+                                      "d2h_bytes": int(count * 28),
+                                      "note": "rt_render_camera_ao: the whole frame (primary + AO + shading) from the "
+                                              "12-float camera, hits + frame to pinned host"} if wl.ao_spp else None)},
                 "note": ("pinned host triangles -> build_bvh; pinned host primary rays up, primary hits + shaded "
                          "frame down, AO rays are device intermediates.  Both public paths are timed every step and "
                          "`value` is the one INTEGRATION.md recommends for this many ranks per host: rt_render_ao "

@@ -70,6 +70,7 @@ SIGNATURES = {
     "rt_gen_ao_rays": (_i32, [_vp, _vp, _vp, _u64, _u32, _u64, _f, _vp]),
     "rt_shade": (_i32, [_vp, _vp, _vp, _vp, _u64, _u32, _vp]),
     "rt_render_ao": (_i32, [_vp, _vp, _vp, _u64, _u32, _u64, _f, _u32, _vp, _vp]),
+    "rt_render_camera_ao": (_i32, [_vp, _vp, _vp, _u32, _u32, _u32, _u64, _f, _u32, _vp, _vp]),
     "rt_device_count": (_i32, []),
     "rt_kernel_launches": (_u64, []),
     "rt_set_param": (_i32, [C.c_char_p, C.c_int64]),

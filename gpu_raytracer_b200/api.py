@@ -238,6 +238,21 @@ class Bvh:
                                      _ptr(hits), _ptr(rgb)))
         return hits, rgb
 
+    def render_camera_ao(self, tris, cam, width: int, height: int, spp: int, seed: int, radius: float,
+                         flags: int = 0, hits=None, rgb=None, device: Optional[str] = None):
+        """The frame of ``cam`` in one call (rt_render_camera_ao): primary rays generated on the
+        device, spp AO rays per pixel, the shaded frame.  Returns (hits [n, 4], rgb [n, 3]): numpy
+        unless ``device`` or the buffers say otherwise."""
+        cam = np.ascontiguousarray(cam, dtype=np.float32).reshape(12)
+        n = width * height
+        if hits is None:
+            hits = _empty_like_kind(cam, (n, 4), device)
+        if rgb is None:
+            rgb = _empty_like_kind(cam, (n, 3), device)
+        L.check(L.lib().rt_render_camera_ao(self._h, _ptr(tris), cam.ctypes.data, width, height, spp, seed,
+                                            C.c_float(radius), flags, _ptr(hits), _ptr(rgb)))
+        return hits, rgb
+
     def trace_async(self, rays, out, flags: int = L.RT_TRACE_CLOSEST, stream: int = 0):
         n = _rows(rays, 8)
         L.check(L.lib().trace_rays_async(self._h, _ptr(rays), n, flags, _ptr(out), stream or None))

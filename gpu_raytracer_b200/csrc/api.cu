@@ -974,12 +974,15 @@ extern "C" int trace_rays(const rt_bvh* h, const float* rays, uint64_t n_rays, u
 // of 1M rays that flow through three streams: band k+1 is uploaded while band k is traced, and
 // band k's hits and pixels go down while band k+1 is traced; the occlusion rays and their hits
 // never leave the device.  Host buffers should be page-locked for the copies to overlap.
-extern "C" int rt_render_ao(const rt_bvh* h, const float* tris, const float* rays, uint64_t n_rays,
-                            uint32_t spp, uint64_t seed, float radius, uint32_t flags, float* hits,
-                            float* rgb) {
+namespace {
+// cam != NULL: the primary rays are those of the width x height pinhole image (n_rays = width *
+// height) and are generated on the device band by band; rays is ignored
+int render_ao_impl(const rt_bvh* h, const float* tris, const float* rays, const float* cam, uint32_t width,
+                   uint32_t height, uint64_t n_rays, uint32_t spp, uint64_t seed, float radius, uint32_t flags,
+                   float* hits, float* rgb) {
   if (!h) return fail(RT_ERR_INVALID, "rt_render_ao: handle is NULL");
   if (n_rays == 0) return RT_OK;
-  if (!tris || !rays || !rgb) return fail(RT_ERR_INVALID, "rt_render_ao: tris, rays or rgb is NULL");
+  if (!tris || (!rays && !cam) || !rgb) return fail(RT_ERR_INVALID, "rt_render_ao: tris, rays or rgb is NULL");
   if (flags & ~(uint32_t)RT_TRACE_WATERTIGHT) return fail(RT_ERR_INVALID, "rt_render_ao: flags may only hold RT_TRACE_WATERTIGHT");
   if (spp > 64) return fail(RT_ERR_LIMIT, "rt_render_ao: at most 64 occlusion rays per pixel");
   DeviceScope scope;
@@ -987,7 +990,8 @@ extern "C" int rt_render_ao(const rt_bvh* h, const float* tris, const float* ray
   int dt = -1, dr = -1, dh = -1, dg = -1;
   if (!classify(tris, &dt) || dt != h->device)
     return fail(RT_ERR_INVALID, "rt_render_ao: tris (original order) must be device memory of the handle's device");
-  const bool rays_dev = classify(rays, &dr) != 0, hits_dev = hits && classify(hits, &dh) != 0,
+  const bool gen = cam != nullptr;  // rays made on the device: nothing to upload, one staging slot per band
+  const bool rays_dev = !gen && classify(rays, &dr) != 0, hits_dev = hits && classify(hits, &dh) != 0,
              rgb_dev = classify(rgb, &dg) != 0;
   if ((rays_dev && dr != h->device) || (hits_dev && dh != h->device) || (rgb_dev && dg != h->device))
     return fail(RT_ERR_INVALID, "rt_render_ao: device buffers are not on the handle's device %d", h->device);
@@ -1006,7 +1010,7 @@ extern "C" int rt_render_ao(const rt_bvh* h, const float* tris, const float* ray
   // when the last launch ends is a quarter band).  render.taper: bit 0 = head, bit 1 = tail.
   const int taper_knob = params().render_taper;
   const bool big = n_rays >= 6 * band;
-  const bool taper_in = big && !rays_dev && (taper_knob & 1) != 0;
+  const bool taper_in = big && !rays_dev && !gen && (taper_knob & 1) != 0;
   const bool taper_out = big && (!rgb_dev || (hits && !hits_dev)) && (taper_knob & 2) != 0;
   std::vector<uint64_t> cuts;  // band k = [cuts[k], cuts[k + 1])
   {
@@ -1098,6 +1102,11 @@ extern "C" int rt_render_ao(const rt_bvh* h, const float* tris, const float* ray
     const float4* r4;
     if (rays_dev) {
       r4 = reinterpret_cast<const float4*>(rays) + 2 * first;
+    } else if (gen) {
+      // the slot's last reader (shade) ran on either compute stream
+      if (reused) RT_CUDA(cudaStreamWaitEvent(sc, ev.run[b], 0));
+      RT_TRY(launch_gen_primary(cam, width, height, first, cnt, d_rays[b], sc));
+      r4 = d_rays[b];
     } else {
       if (reused) RT_CUDA(cudaStreamWaitEvent(p.s_in, ev.run[b], 0));  // the slot's last reader (shade)
       if (timeline) RT_CUDA(cudaEventRecord(tl[k * 5 + 0], p.s_in));
@@ -1151,6 +1160,24 @@ extern "C" int rt_render_ao(const rt_bvh* h, const float* tris, const float* ray
   RT_CUDA(cudaStreamSynchronize(p.s_run));
   RT_CUDA(cudaStreamSynchronize(p.s_out));
   return RT_OK;
+}
+}  // namespace
+
+extern "C" int rt_render_ao(const rt_bvh* h, const float* tris, const float* rays, uint64_t n_rays,
+                            uint32_t spp, uint64_t seed, float radius, uint32_t flags, float* hits,
+                            float* rgb) {
+  if (n_rays != 0 && !rays) return fail(RT_ERR_INVALID, "rt_render_ao: rays is NULL");
+  return render_ao_impl(h, tris, rays, nullptr, 0, 0, n_rays, spp, seed, radius, flags, hits, rgb);
+}
+
+// The same frame from the 12-float camera: the primary rays are generated on the device band by
+// band (the bytes of rt_gen_primary_rays), so nothing but the camera goes up.
+extern "C" int rt_render_camera_ao(const rt_bvh* h, const float* tris, const float* cam, uint32_t width,
+                                   uint32_t height, uint32_t spp, uint64_t seed, float radius, uint32_t flags,
+                                   float* hits, float* rgb) {
+  if (!cam || width == 0 || height == 0) return fail(RT_ERR_INVALID, "rt_render_camera_ao: bad camera or image size");
+  return render_ao_impl(h, tris, nullptr, cam, width, height, (uint64_t)width * height, spp, seed, radius, flags,
+                        hits, rgb);
 }
 
 // Primary rays never cross PCIe: the 12-float camera goes in, the rays are generated on the

@@ -344,6 +344,12 @@ RT_API int rt_shade(const float* tris, const float* rays, const float* hits, con
  * the device.  Synchronous on return. */
 RT_API int rt_render_ao(const rt_bvh* h, const float* tris, const float* rays, uint64_t n_rays, uint32_t spp,
                         uint64_t seed, float radius, uint32_t flags, float* hits, float* rgb);
+/* The same frame from the 12-float camera of rt_gen_primary_rays: the primary rays of the
+ * width x height image are generated on the device band by band, so only the camera goes up and
+ * hits (width * height x 4, may be NULL) and rgb (width * height x 3) come down: the bytes of
+ * rt_gen_primary_rays followed by rt_render_ao.  cam: host. */
+RT_API int rt_render_camera_ao(const rt_bvh* h, const float* tris, const float* cam, uint32_t width, uint32_t height,
+                               uint32_t spp, uint64_t seed, float radius, uint32_t flags, float* hits, float* rgb);
 
 /* ---- runtime --------------------------------------------------------------*/
 

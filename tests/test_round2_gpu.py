@@ -277,6 +277,17 @@ def test_render_ao_equals_the_separate_calls(rt):
             assert np.array_equal(bits(d_rgb.cpu().numpy()), want_g)
             _, plain = gb.render_ao(d_tris, pinned, 0, seed, radius, flags)
             assert np.array_equal(bits(plain.numpy()), bits(rt.shade(d_tris, rays, hits).cpu().numpy()))
+            # the same frame from the camera alone: numpy out, pinned out, device out
+            ch, cg = gb.render_camera_ao(d_tris, cam, w, h, spp, seed, radius, flags)
+            assert isinstance(cg, np.ndarray) and np.array_equal(bits(ch), want_h) and np.array_equal(bits(cg), want_g)
+            ph = torch.empty((w * h, 4), dtype=torch.float32).pin_memory()
+            pg = torch.empty((w * h, 3), dtype=torch.float32).pin_memory()
+            gb.render_camera_ao(d_tris, cam, w, h, spp, seed, radius, flags, hits=ph, rgb=pg)
+            assert np.array_equal(bits(ph.numpy()), want_h) and np.array_equal(bits(pg.numpy()), want_g)
+            ch, cg = gb.render_camera_ao(d_tris, cam, w, h, spp, seed, radius, flags, device="cuda")
+            assert cg.is_cuda and np.array_equal(bits(ch.cpu().numpy()), want_h) and np.array_equal(bits(cg.cpu().numpy()), want_g)
+            with pytest.raises(rt.RtError):
+                gb.render_camera_ao(d_tris, cam, 0, h, spp, seed, radius)
             with pytest.raises(rt.RtError):
                 gb.render_ao(d_tris.cpu().numpy(), pinned, spp, seed, radius)                   # tris must be on the device
             with pytest.raises(rt.RtError):
