@@ -1,6 +1,6 @@
 """Renders a scene to a PPM or PNG file (by the name's ending) through the public API (SURVEY.md
-§8f.1): build_bvh, then the whole frame in one call (rt_render_ao: primary rays, 4 ambient-occlusion
-rays per pixel, shading), image.write_ppm / write_png.
+§8f.1): build_bvh, then the whole frame in one call (rt_render_camera_ao: primary rays from the camera,
+4 ambient-occlusion rays per pixel, shading), image.write_ppm / write_png.
 
   python tools/render.py cornell|soup1m|flake10m|<file.obj>|<file.tri> [out.ppm|out.png] [width height]
 """
@@ -37,9 +37,8 @@ def main():
         box = bvh.bounds
         if cam is None:
             cam = g.camera.frame_box(box, w, h)
-        rays = g.gen_primary_rays(cam, w, h)
         radius = float(np.float32(0.05) * np.float32(np.linalg.norm(box[3:] - box[:3])))
-        hits, rgb = bvh.render_ao(tris, rays, 4, 2, radius)
+        hits, rgb = bvh.render_camera_ao(tris, cam, w, h, 4, 2, radius, device="cuda")
     torch.cuda.synchronize()
     dt = time.perf_counter() - t0
     os.makedirs(os.path.dirname(os.path.abspath(out)), exist_ok=True)
